@@ -1,0 +1,439 @@
+#!/usr/bin/env python
+"""Benchmark of the ALS /recommend hot path on B200: BASELINE.json's metric on BASELINE.json's config.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (config[1] of BASELINE.json): one top-10 /recommend query (DotsFunction) scored against
+10 M item vectors x 128 features fp32 per GPU, LSH sample-rate 1.0 (the reference's sizing rule for
+32 cores: 5 hashes, all partitions candidates), synthetic N(0,1) model (LoadTestALSModelFactory's
+recipe).  One step = one query.  With N GPUs the model holds N x 10 M items sharded by rows (weak
+scaling); every query scans all shards, each GPU selects a local top-10, an NCCL all-gather over
+NVLink exchanges the N x 10 pairs and a merge kernel orders them.  `value` counts 10 M-item scans
+per second over the whole job (= queries/s at N=1).
+
+Prints ONE JSON line on rank 0.  See DESIGN.md section "Measurement" for the roofline arithmetic.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ITEMS_PER_GPU = 10_000_000
+FEATURES = 128
+HOW_MANY = 10
+LSH_CORES = 32          # LocalitySensitiveHash(1.0, features, 32 cores) -> 5 hashes, 5 bits differing
+N_QUERIES = 64          # distinct query vectors cycled through the timed steps
+SEED_Y, SEED_Q, SEED_H = 0x0B2000001, 0x0B2000003, 0x0B2000004
+METRIC = "als_recommend_top10_queries_per_sec_10M_items_x_128f"
+UNIT = "queries/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--items", type=int, default=ITEMS_PER_GPU, help="items per GPU (parity/debug runs only)")
+    ap.add_argument("--features", type=int, default=FEATURES)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------ helpers
+
+def mem_available_gb() -> float:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def gen_host_matrix(n: int, f: int, seed: int, threads: int) -> np.ndarray:
+    """N(0,1) fp32 matrix, generated in parallel slices with independent streams."""
+    out = np.empty((n, f), dtype=np.float32)
+    pieces = max(1, min(threads, 16))
+    bounds = np.linspace(0, n, pieces + 1).astype(np.int64)
+    seeds = np.random.SeedSequence(seed).spawn(pieces)
+
+    def fill(i):
+        rng = np.random.default_rng(seeds[i])
+        rng.standard_normal(out=out[bounds[i]:bounds[i + 1]], dtype=np.float32)
+
+    with ThreadPoolExecutor(pieces) as ex:
+        list(ex.map(fill, range(pieces)))
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                smax.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks() -> tuple[float, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except (KeyError, ValueError, OSError):
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_leg(y_host: np.ndarray, queries: np.ndarray, threads: int, budget_s: float, scale_items: int):
+    """The oracle's multi-threaded ALSServingModel.topN restatement timed on the host cores."""
+    import oracle
+    n = y_host.shape[0]
+    oracle.topn_mt(oracle.DOT, queries[0], y_host[: min(n, 100000)], HOW_MANY, threads)  # page in / warm
+    times = []
+    t_start = time.perf_counter()
+    i = 0
+    while True:
+        t0 = time.perf_counter()
+        oracle.topn_mt(oracle.DOT, queries[i % len(queries)], y_host, HOW_MANY, threads)
+        times.append(time.perf_counter() - t0)
+        i += 1
+        if time.perf_counter() - t_start > budget_s and i >= 3:
+            break
+        if i >= 200:
+            break
+    per_query = statistics.median(times) * (scale_items / n)
+    return 1.0 / per_query, i, per_query
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = host_threads()
+    n_items = args.items
+    avail = mem_available_gb()
+    need_gb = n_items * args.features * 4 / 1e9
+    sample_rows = n_items if avail > need_gb * 1.6 + 4 else max(1_000_000, int((avail - 4) / 1.6 * 1e9 / (args.features * 4)))
+    sample_rows = min(sample_rows, n_items)
+    y = gen_host_matrix(sample_rows, args.features, SEED_Y, threads)
+    q = np.random.default_rng(SEED_Q).standard_normal((N_QUERIES, args.features), dtype=np.float32)
+    import oracle
+    scale = n_items / sample_rows
+    for i in range(args.warmup):
+        oracle.topn_mt(oracle.DOT, q[i % N_QUERIES], y, HOW_MANY, threads)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        oracle.topn_mt(oracle.DOT, q[i % N_QUERIES], y, HOW_MANY, threads)
+    dt = (time.perf_counter() - t0) * scale
+    qps = args.steps / dt
+    sample = (f"every step = one full top-{HOW_MANY} query over {sample_rows} x {args.features} rows"
+              + ("" if sample_rows == n_items else f", time scaled x{scale:.2f} to {n_items} rows (linear in items)"))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 products, f64 accumulate",
+        "data": "synthetic",
+        "config": {"workload": f"single-query /recommend top-{HOW_MANY}, {n_items} items x {args.features} f per 10M-item scan, "
+                               "CPU restatement of ALSServingModel.topN (oracle port; the Java reference has no JVM here)",
+                   "items_per_scan": n_items, "features": args.features, "how_many": HOW_MANY},
+        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ our arm
+
+def run_ours(args):
+    import torch
+    import oryx_b200 as ob
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: oryx_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    n_items, F = args.items, args.features
+    H, bits = ob.lsh_plan(1.0, LSH_CORES)
+    hv = np.random.default_rng(SEED_H).standard_normal((H, F), dtype=np.float32)
+    model = ob.Model(F, implicit=True, hash_vectors=hv, max_bits_differing=bits, device=local_rank,
+                     capacity_hint=n_items)
+
+    # ---- synthetic model, generated on the device shard-locally and bulk-loaded through the C ABI
+    want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)
+    keep_host = want_cpu and mem_available_gb() > n_items * F * 4 / 1e9 * 1.5 + 4
+    y_host = np.empty((n_items, F), dtype=np.float32) if keep_host else None
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(SEED_Y + rank)
+    chunk = 1_000_000
+    t_load = time.perf_counter()
+    for off in range(0, n_items, chunk):
+        c = min(chunk, n_items - off)
+        block = torch.randn((c, F), generator=gen, device=dev, dtype=torch.float32)
+        torch.cuda.synchronize()
+        model.upsert_device(ob.Y, off, block.data_ptr(), c)
+        if y_host is not None:
+            y_host[off:off + c] = block.cpu().numpy()
+        del block
+    t_load = time.perf_counter() - t_load
+
+    q_host = np.random.default_rng(SEED_Q).standard_normal((N_QUERIES, F), dtype=np.float32)
+    d_q = torch.from_numpy(q_host).to(dev)
+    d_rows = torch.zeros(HOW_MANY, dtype=torch.int32, device=dev)
+    d_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
+    d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+    if world > 1:
+        g_rows = torch.zeros((world, HOW_MANY), dtype=torch.int32, device=dev)
+        g_scores = torch.zeros((world, HOW_MANY), dtype=torch.float64, device=dev)
+        g_n = torch.zeros(world, dtype=torch.int32, device=dev)
+        m_rows = torch.zeros(HOW_MANY, dtype=torch.int64, device=dev)
+        m_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
+        m_n = torch.zeros(1, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    launches_extra = 0
+
+    def step_device(i: int):
+        """One query with inputs resident in HBM, enqueued on torch's current stream."""
+        nonlocal launches_extra
+        model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
+                          d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
+        if world > 1:
+            # the one exchange step: N x (10 scores, 10 rows, count) over NCCL / NVLink, then merge
+            dist.all_gather_into_tensor(g_scores, d_scores)
+            dist.all_gather_into_tensor(g_rows, d_rows)
+            dist.all_gather_into_tensor(g_n, d_n)
+            ob.merge_topn_device(g_scores.data_ptr(), g_rows.data_ptr(), g_n.data_ptr(), world, HOW_MANY,
+                                 n_items, m_rows.data_ptr(), m_scores.data_ptr(), m_n.data_ptr(),
+                                 stream.cuda_stream)
+            launches_extra += 1
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- parity spot-check against the oracle at full size (rank 0, N=1, when the host copy exists)
+    parity = None
+    if y_host is not None:
+        import oracle
+        ok = True
+        for i in range(2):
+            rows, scores = model.topn(ob.DOT, q_host[i], HOW_MANY)
+            erows, escores = oracle.topn_mt(oracle.DOT, q_host[i], y_host, HOW_MANY, host_threads())
+            ok = ok and np.array_equal(rows, erows) and np.array_equal(scores, escores)
+        parity = bool(ok)
+
+    # ---- warm-up
+    for i in range(max(args.warmup, 3)):
+        step_device(i)
+    barrier()
+    launches0 = model.stats()["kernel_launches"]
+    launches_extra = 0
+
+    # ---- timed region 1: kernel-resident throughput (`value`)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for i in range(args.steps):
+        step_device(i)
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    gpu_launches = model.stats()["kernel_launches"] - launches0 + launches_extra
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+
+    # ---- timed region 2: end to end through the public call with HOST buffers
+    h_q_pinned = torch.from_numpy(q_host).pin_memory()
+    if world == 1:
+        def step_e2e(i):
+            return model.topn(ob.DOT, q_host[i % N_QUERIES], HOW_MANY)
+        h2d, d2h = ((F + 3) // 4 * 4) * 4, 4 + HOW_MANY * 4 + HOW_MANY * 8
+    else:
+        d_qe = torch.zeros(F, dtype=torch.float32, device=dev)
+        h_res_rows = torch.zeros(HOW_MANY, dtype=torch.int64).pin_memory()
+        h_res_scores = torch.zeros(HOW_MANY, dtype=torch.float64).pin_memory()
+
+        def step_e2e(i):
+            d_qe.copy_(h_q_pinned[i % N_QUERIES], non_blocking=True)
+            model.topn_device(ob.DOT, d_qe.data_ptr(), HOW_MANY, d_rows.data_ptr(), d_scores.data_ptr(),
+                              d_n.data_ptr(), stream.cuda_stream)
+            dist.all_gather_into_tensor(g_scores, d_scores)
+            dist.all_gather_into_tensor(g_rows, d_rows)
+            dist.all_gather_into_tensor(g_n, d_n)
+            ob.merge_topn_device(g_scores.data_ptr(), g_rows.data_ptr(), g_n.data_ptr(), world, HOW_MANY,
+                                 n_items, m_rows.data_ptr(), m_scores.data_ptr(), m_n.data_ptr(),
+                                 stream.cuda_stream)
+            h_res_rows.copy_(m_rows, non_blocking=True)
+            h_res_scores.copy_(m_scores, non_blocking=True)
+            stream.synchronize()
+        h2d, d2h = F * 4, HOW_MANY * 16
+    for i in range(3):
+        step_e2e(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_e2e(i)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- numbers
+    ms_per_step = ms_total / args.steps
+    scans_per_query = world * (n_items / ITEMS_PER_GPU)   # units of "one 10M-item scan"
+    value = scans_per_query * args.steps / (ms_total / 1000.0)
+    e2e_value = scans_per_query * args.steps / e2e_s
+    peak, peak_src = measured_peaks()
+    alg_bytes = n_items * F * 4                       # Y read once per query per GPU (512 B per item-score)
+    achieved = alg_bytes / (ms_per_step / 1000.0) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "scan_traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        except (ValueError, OSError):
+            traffic = None
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = host_threads()
+        if y_host is None:
+            rows = min(n_items, 2_000_000)
+            y_sample = gen_host_matrix(rows, F, SEED_Y, threads)
+            sample_desc = f"{rows} x {F} synthetic rows (host RAM too small for the full matrix), time scaled linearly to {n_items} rows"
+        else:
+            y_sample = y_host
+            sample_desc = f"the full {n_items} x {F} matrix, same queries; median of full top-{HOW_MANY} queries over ~12 s"
+        cpu_qps, n_q, per_q = cpu_leg(y_sample, q_host, threads, 12.0, n_items)
+        cpu_baseline = {"value": cpu_qps * (n_items / ITEMS_PER_GPU),
+                        "unit": UNIT, "cores": threads, "kind": "port",
+                        "sample": f"{sample_desc}; {n_q} queries, {per_q * 1000:.1f} ms each on {threads} threads "
+                                  "(oracle/oryx_oracle.c oro_topn_mt: contiguous rows, TopNConsumer per slice)"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 scan, f64 exact re-score of the top-18",
+            "data": "synthetic",
+            "config": {"workload": f"single-query /recommend top-{HOW_MANY} (DotsFunction), {n_items} items x {F} f fp32 per GPU, "
+                                   f"LSH sample-rate 1.0 ({H} hashes, all partitions candidates), BASELINE.json configs[1]",
+                       "items_per_gpu": n_items, "features": F, "how_many": HOW_MANY, "queries_cycled": N_QUERIES,
+                       "parallelism": f"row-sharded x{world}" if world > 1 else "1 GPU",
+                       "l2_policy": f"inputs larger than L2 ({alg_bytes / 1e9:.2f} GB streamed per step vs 126 MB L2)",
+                       "item_scores_per_sec": value * ITEMS_PER_GPU, "load_seconds": round(t_load, 2),
+                       "parity_vs_oracle_full_size": parity},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg_bytes,
+                         "frac_of_nominal_8000": achieved / 8000.0},
+            "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1000.0 * e2e_s / args.steps},
+            "gpu_launches": int(gpu_launches),
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    model.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

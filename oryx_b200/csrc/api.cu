@@ -1,0 +1,567 @@
+// api.cu -- the extern "C" surface declared in include/oryx_b200.h: handle lifetime, locking,
+// host<->device staging around the kernels.  Each entry point's reference counterpart is cited in
+// the header.
+#include <algorithm>
+#include <cmath>
+
+#include "common.cuh"
+
+namespace oryx {
+
+namespace {
+thread_local char g_err[512] = {0};
+}
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+void ctx_destroy(QueryCtx* c) {
+  if (!c) return;
+  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_counter);
+  cudaFree(c->d_main_index); cudaFree(c->d_out_rows); cudaFree(c->d_out_scores); cudaFree(c->d_out_n);
+  cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_rows);
+  cudaFreeHost(c->h_out_scores); cudaFreeHost(c->h_out_n);
+}
+
+static int32_t ctx_create(Model* m, QueryCtx* c) {
+  const int fpad = m->store[ORYX_Y].fpad;
+  ORYX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  ORYX_CUDA(cudaEventCreate(&c->ev0));
+  ORYX_CUDA(cudaEventCreate(&c->ev1));
+  ORYX_CUDA(cudaMalloc(&c->d_query, (size_t)fpad * sizeof(float)));
+  c->excl_cap = 4096;
+  ORYX_CUDA(cudaMalloc(&c->d_excl, (size_t)c->excl_cap * sizeof(int32_t)));
+  ORYX_CUDA(cudaMalloc(&c->d_cand, (size_t)kMaxGrid * kMaxK * sizeof(uint2)));
+  ORYX_CUDA(cudaMalloc(&c->d_counter, sizeof(unsigned int)));
+  ORYX_CUDA(cudaMemset(c->d_counter, 0, sizeof(unsigned int)));
+  ORYX_CUDA(cudaMalloc(&c->d_main_index, sizeof(int32_t)));
+  ORYX_CUDA(cudaMemset(c->d_main_index, 0, sizeof(int32_t)));
+  ORYX_CUDA(cudaMalloc(&c->d_out_rows, (size_t)kMaxK * sizeof(int32_t)));
+  ORYX_CUDA(cudaMalloc(&c->d_out_scores, (size_t)kMaxK * sizeof(double)));
+  ORYX_CUDA(cudaMalloc(&c->d_out_n, sizeof(int32_t)));
+  ORYX_CUDA(cudaMallocHost(&c->h_query, (size_t)fpad * sizeof(float)));
+  ORYX_CUDA(cudaMallocHost(&c->h_excl, (size_t)c->excl_cap * sizeof(int32_t)));
+  ORYX_CUDA(cudaMallocHost(&c->h_out_rows, (size_t)kMaxK * sizeof(int32_t)));
+  ORYX_CUDA(cudaMallocHost(&c->h_out_scores, (size_t)kMaxK * sizeof(double)));
+  ORYX_CUDA(cudaMallocHost(&c->h_out_n, sizeof(int32_t)));
+  return ORYX_OK;
+}
+
+int32_t ctx_acquire(Model* m, QueryCtx** out) {
+  std::unique_lock<std::mutex> lk(m->pool_mu);
+  for (;;) {
+    if (!m->pool_free.empty()) {
+      *out = m->pool_free.back();
+      m->pool_free.pop_back();
+      return ORYX_OK;
+    }
+    if ((int)m->pool_all.size() < m->pool_limit) {
+      auto c = std::make_unique<QueryCtx>();
+      int32_t rc = ctx_create(m, c.get());
+      if (rc != ORYX_OK) { ctx_destroy(c.get()); return rc; }
+      *out = c.get();
+      m->pool_all.push_back(std::move(c));
+      return ORYX_OK;
+    }
+    m->pool_cv.wait(lk);
+  }
+}
+
+void ctx_release(Model* m, QueryCtx* ctx) {
+  {
+    std::lock_guard<std::mutex> lk(m->pool_mu);
+    m->pool_free.push_back(ctx);
+  }
+  m->pool_cv.notify_one();
+}
+
+static int32_t ensure_excl(QueryCtx* c, int32_t n) {
+  if (n <= c->excl_cap) return ORYX_OK;
+  int32_t cap = std::max(n, c->excl_cap * 2);
+  cudaFree(c->d_excl); cudaFreeHost(c->h_excl);
+  c->d_excl = nullptr; c->h_excl = nullptr; c->excl_cap = 0;
+  ORYX_CUDA(cudaMalloc(&c->d_excl, (size_t)cap * sizeof(int32_t)));
+  ORYX_CUDA(cudaMallocHost(&c->h_excl, (size_t)cap * sizeof(int32_t)));
+  c->excl_cap = cap;
+  return ORYX_OK;
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+    ok = cudaSetDevice(dev) == cudaSuccess;
+    if (!ok) cudaGetLastError();
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+#define ORYX_DEVICE(m)                                                   \
+  DeviceGuard guard__((m)->device);                                      \
+  if (!guard__.ok) {                                                     \
+    set_error("cannot select CUDA device %d (no CPU fallback exists)", (m)->device); \
+    return ORYX_E_CUDA;                                                  \
+  }
+
+// One query through a context: stage, launch, copy back, wait.
+static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query, int32_t how_many,
+                        const int32_t* excluded_rows, int32_t n_excluded, int32_t* out_rows,
+                        double* out_scores, int32_t* out_n) {
+  Store* s = &m->store[ORYX_Y];
+  const int fpad = s->fpad, F = s->features;
+  std::memcpy(c->h_query, query, (size_t)F * sizeof(float));
+  for (int j = F; j < fpad; j++) c->h_query[j] = 0.0f;
+  ORYX_CUDA(cudaMemcpyAsync(c->d_query, c->h_query, (size_t)fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  if (n_excluded > 0) {
+    ORYX_TRY(ensure_excl(c, n_excluded));
+    std::memcpy(c->h_excl, excluded_rows, (size_t)n_excluded * sizeof(int32_t));
+    std::sort(c->h_excl, c->h_excl + n_excluded);
+    ORYX_CUDA(cudaMemcpyAsync(c->d_excl, c->h_excl, (size_t)n_excluded * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+  }
+  TopnRequest rq{};
+  rq.kind = kind;
+  rq.d_query = c->d_query;
+  rq.how_many = how_many;
+  rq.d_excl = c->d_excl;
+  rq.n_excl = n_excluded;
+  rq.d_out_rows = c->d_out_rows;
+  rq.d_out_scores = c->d_out_scores;
+  rq.d_out_n = c->d_out_n;
+  ORYX_CUDA(cudaEventRecord(c->ev0, c->stream));
+  ORYX_TRY(scan_topn_launch(m, c, rq, c->stream));
+  ORYX_CUDA(cudaEventRecord(c->ev1, c->stream));
+  ORYX_CUDA(cudaMemcpyAsync(c->h_out_n, c->d_out_n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  ORYX_CUDA(cudaMemcpyAsync(c->h_out_rows, c->d_out_rows, (size_t)how_many * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  ORYX_CUDA(cudaMemcpyAsync(c->h_out_scores, c->d_out_scores, (size_t)how_many * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  ORYX_CUDA(cudaStreamSynchronize(c->stream));
+  int32_t n = *c->h_out_n;
+  if (n < 0 || n > how_many) {
+    set_error("device returned an impossible result count %d", n);
+    return ORYX_E_CUDA;
+  }
+  std::memcpy(out_rows, c->h_out_rows, (size_t)n * sizeof(int32_t));
+  std::memcpy(out_scores, c->h_out_scores, (size_t)n * sizeof(double));
+  *out_n = n;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);
+  else cudaGetLastError();
+  return ORYX_OK;
+}
+
+}  // namespace oryx
+
+using namespace oryx;
+
+extern "C" {
+
+int32_t oryx_last_error(char* buf, int32_t buf_len) {
+  if (!buf || buf_len <= 0) return ORYX_E_INVALID;
+  std::snprintf(buf, (size_t)buf_len, "%s", last_error());
+  return ORYX_OK;
+}
+
+int32_t oryx_lsh_plan(double sample_rate, int32_t num_cores, int32_t* num_hashes, int32_t* max_bits_differing) {
+  ORYX_ARG(num_hashes && max_bits_differing, "null output");
+  ORYX_ARG(sample_rate > 0.0 && sample_rate <= 1.0, "sampleRate must be in (0,1]");
+  ORYX_ARG(num_cores >= 1, "numCores must be >= 1");
+  int h = 0, b = 0;
+  lsh_plan(sample_rate, num_cores, &h, &b);
+  *num_hashes = h;
+  *max_bits_differing = b;
+  return ORYX_OK;
+}
+
+int32_t oryx_model_create(const oryx_config* config, oryx_model** out) {
+  ORYX_ARG(config && out, "null argument");
+  ORYX_ARG(config->features > 0, "features must be positive");
+  ORYX_ARG(config->num_hashes >= 0 && config->num_hashes <= ORYX_MAX_HASHES, "num_hashes out of range");
+  ORYX_ARG(config->max_bits_differing >= 0 && config->max_bits_differing <= config->num_hashes, "max_bits_differing out of range");
+  ORYX_ARG(config->num_hashes == 0 || config->hash_vectors != nullptr, "hash_vectors required when num_hashes > 0");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    set_error("no usable CUDA device (%s); this library has no CPU fallback",
+              e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return ORYX_E_CUDA;
+  }
+  ORYX_ARG(config->device >= 0 && config->device < count, "device ordinal out of range");
+  auto m = std::make_unique<Model>();
+  m->cfg = *config;
+  m->cfg.hash_vectors = nullptr;
+  m->device = config->device;
+  m->num_hashes = config->num_hashes;
+  m->max_bits = config->max_bits_differing;
+  ORYX_DEVICE(m.get());
+  cudaDeviceProp prop{};
+  ORYX_CUDA(cudaGetDeviceProperties(&prop, m->device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library is built for sm_100a only", m->device, prop.major, prop.minor);
+    return ORYX_E_CUDA;
+  }
+  m->num_sms = prop.multiProcessorCount;
+  ORYX_CUDA(cudaStreamCreateWithFlags(&m->update_stream, cudaStreamNonBlocking));
+  const int F = config->features, fpad = round_up(F, 4);
+  if (m->num_hashes > 0) {
+    m->h_hash_vectors.assign((size_t)m->num_hashes * fpad, 0.0f);
+    for (int h = 0; h < m->num_hashes; h++) {
+      std::memcpy(&m->h_hash_vectors[(size_t)h * fpad], config->hash_vectors + (size_t)h * F, (size_t)F * sizeof(float));
+    }
+    ORYX_CUDA(cudaMalloc(&m->d_hash_vectors, m->h_hash_vectors.size() * sizeof(float)));
+    ORYX_CUDA(cudaMemcpy(m->d_hash_vectors, m->h_hash_vectors.data(), m->h_hash_vectors.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  ORYX_TRY(store_init(m.get(), ORYX_X, 0));
+  ORYX_TRY(store_init(m.get(), ORYX_Y, config->capacity_hint));
+  *out = reinterpret_cast<oryx_model*>(m.release());
+  return ORYX_OK;
+}
+
+int32_t oryx_model_destroy(oryx_model* mh) {
+  if (!mh) return ORYX_OK;
+  Model* m = reinterpret_cast<Model*>(mh);
+  {
+    DeviceGuard g(m->device);
+    cudaDeviceSynchronize();
+    for (auto& c : m->pool_all) ctx_destroy(c.get());
+    store_free(&m->store[0]);
+    store_free(&m->store[1]);
+    cudaFree(m->d_hash_vectors);
+    if (m->update_stream) cudaStreamDestroy(m->update_stream);
+    cudaGetLastError();
+  }
+  delete m;
+  return ORYX_OK;
+}
+
+int32_t oryx_items_upsert(oryx_model* mh, int32_t which, const int32_t* rows, const float* vecs, int32_t n,
+                          int32_t* out_partitions) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(rows && vecs, "null rows/vecs");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return store_upsert(m, which, rows, vecs, n, out_partitions);
+}
+
+int32_t oryx_items_upsert_device(oryx_model* mh, int32_t which, int32_t first_row, const float* d_vecs, int64_t n) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(n >= 0 && first_row >= 0, "n and first_row must be >= 0");
+  ORYX_ARG((int64_t)first_row + n <= 0x7fffffffLL, "row ids must fit int32");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(d_vecs, "null d_vecs");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return store_upsert_device(m, which, first_row, d_vecs, n);
+}
+
+int32_t oryx_items_remove(oryx_model* mh, int32_t which, const int32_t* rows, int32_t n) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(rows, "null rows");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return store_remove(m, which, rows, n);
+}
+
+int32_t oryx_items_get(oryx_model* mh, int32_t which, int32_t row, float* out_vec, int32_t* found) {
+  ORYX_ARG(mh && out_vec && found, "null argument");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  return store_get(m, which, row, out_vec, found);
+}
+
+int32_t oryx_items_compact(oryx_model* mh, int32_t which) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return store_compact(m, which);
+}
+
+int32_t oryx_lsh_index_rows(oryx_model* mh, const float* vecs, int32_t n, int32_t* out_indices) {
+  ORYX_ARG(mh && out_indices, "null argument");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(vecs, "null vecs");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  const int F = m->cfg.features;
+  float* d_in = nullptr;
+  int32_t* d_out = nullptr;
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc = ORYX_OK;
+  do {
+    if (cudaMalloc(&d_in, (size_t)n * F * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&d_out, (size_t)n * sizeof(int32_t)) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("device allocation failed for %d vectors", n);
+      rc = ORYX_E_NOMEM;
+      break;
+    }
+    if (cudaMemcpyAsync(d_in, vecs, (size_t)n * F * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { rc = ORYX_E_CUDA; set_error("H2D copy failed"); break; }
+    rc = lsh_hash_rows_device(m, d_in, n, F, d_out, c->stream);
+    if (rc != ORYX_OK) break;
+    if (cudaMemcpyAsync(out_indices, d_out, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+      set_error("LSH hashing failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    }
+  } while (0);
+  cudaFree(d_in); cudaFree(d_out);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_lsh_index(oryx_model* mh, const float* vec, int32_t* out_index) {
+  return oryx_lsh_index_rows(mh, vec, 1, out_index);
+}
+
+int32_t oryx_lsh_candidates(oryx_model* mh, const float* vec, int32_t* out, int32_t* out_n) {
+  ORYX_ARG(mh && vec && out && out_n, "null argument");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  const int F = m->cfg.features, fpad = round_up(F, 4);
+  const int total = 1 << m->num_hashes;
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t* d_out = nullptr;
+  int32_t rc = ORYX_OK;
+  do {
+    if (cudaMalloc(&d_out, (size_t)(total + 1) * sizeof(int32_t)) != cudaSuccess) {
+      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
+    }
+    std::memcpy(c->h_query, vec, (size_t)F * sizeof(float));
+    for (int j = F; j < fpad; j++) c->h_query[j] = 0.f;
+    if (cudaMemcpyAsync(c->d_query, c->h_query, (size_t)fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { rc = ORYX_E_CUDA; set_error("H2D copy failed"); break; }
+    rc = lsh_hash_rows_device(m, c->d_query, 1, fpad, c->d_main_index, c->stream);
+    if (rc != ORYX_OK) break;
+    rc = lsh_candidates_device(m, c->d_main_index, d_out, d_out + total, c->stream);
+    if (rc != ORYX_OK) break;
+    std::vector<int32_t> host((size_t)total + 1);
+    if (cudaMemcpyAsync(host.data(), d_out, (size_t)(total + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+      set_error("candidate enumeration failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+      break;
+    }
+    int32_t n = host[(size_t)total];
+    std::memcpy(out, host.data(), (size_t)n * sizeof(int32_t));
+    *out_n = n;
+  } while (0);
+  cudaFree(d_out);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_topn(oryx_model* mh, int32_t kind, const float* query, int32_t how_many,
+                  const int32_t* excluded_rows, int32_t n_excluded,
+                  int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  ORYX_ARG(mh && query && out_rows && out_scores && out_n, "null argument");
+  ORYX_ARG(n_excluded >= 0 && (n_excluded == 0 || excluded_rows), "bad exclusion list");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc;
+  {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    rc = run_topn(m, c, kind, query, how_many, excluded_rows, n_excluded, out_rows, out_scores, out_n);
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_topn_batch(oryx_model* mh, int32_t kind, const float* queries, int32_t nq, int32_t how_many,
+                        const int32_t* excl_offsets, const int32_t* excl_rows,
+                        int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  ORYX_ARG(mh && out_rows && out_scores && out_n, "null argument");
+  ORYX_ARG(nq >= 0, "nq must be >= 0");
+  if (nq == 0) return ORYX_OK;
+  ORYX_ARG(queries, "null queries");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  const int F = m->cfg.features;
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc = ORYX_OK;
+  {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    for (int32_t i = 0; i < nq && rc == ORYX_OK; i++) {
+      const int32_t* ex = nullptr;
+      int32_t nex = 0;
+      if (excl_offsets && excl_rows) {
+        ex = excl_rows + excl_offsets[i];
+        nex = excl_offsets[i + 1] - excl_offsets[i];
+      }
+      rc = run_topn(m, c, kind, queries + (size_t)i * F, how_many, ex, nex, out_rows + (size_t)i * how_many,
+                    out_scores + (size_t)i * how_many, out_n + i);
+    }
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_scores_all(oryx_model* mh, int32_t kind, const float* query, int32_t n_rows, double* out_scores) {
+  ORYX_ARG(mh && query && out_scores, "null argument");
+  ORYX_ARG(kind == ORYX_DOT || kind == ORYX_COSINE, "kind must be ORYX_DOT or ORYX_COSINE");
+  ORYX_ARG(n_rows >= 0, "n_rows must be >= 0");
+  if (n_rows == 0) return ORYX_OK;
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  Store* s = &m->store[ORYX_Y];
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  double* d_out = nullptr;
+  int32_t rc = ORYX_OK;
+  do {
+    if (cudaMalloc(&d_out, (size_t)n_rows * sizeof(double)) != cudaSuccess) {
+      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
+    }
+    std::memcpy(c->h_query, query, (size_t)s->features * sizeof(float));
+    for (int j = s->features; j < s->fpad; j++) c->h_query[j] = 0.f;
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    if (cudaMemcpyAsync(c->d_query, c->h_query, (size_t)s->fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { rc = ORYX_E_CUDA; set_error("H2D copy failed"); break; }
+    rc = scores_all_launch(m, kind, c->d_query, n_rows, d_out, c->stream);
+    if (rc != ORYX_OK) break;
+    if (cudaMemcpyAsync(out_scores, d_out, (size_t)n_rows * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+      set_error("scores_all failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    }
+  } while (0);
+  cudaFree(d_out);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_scores_rows(oryx_model* mh, int32_t kind, const float* query, const int32_t* rows, int32_t n,
+                         double* out_scores, uint8_t* found) {
+  ORYX_ARG(mh && query && out_scores, "null argument");
+  ORYX_ARG(kind == ORYX_DOT || kind == ORYX_COSINE, "kind must be ORYX_DOT or ORYX_COSINE");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(rows, "null rows");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  Store* s = &m->store[ORYX_Y];
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t* d_slots = nullptr;
+  double* d_out = nullptr;
+  int32_t rc = ORYX_OK;
+  do {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    std::vector<int32_t> slots((size_t)n);
+    for (int32_t i = 0; i < n; i++) {
+      int32_t r = rows[i];
+      slots[i] = (r >= 0 && (size_t)r < s->row2slot.size()) ? s->row2slot[r] : -1;
+      if (found) found[i] = slots[i] >= 0;
+    }
+    if (cudaMalloc(&d_slots, (size_t)n * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc(&d_out, (size_t)n * sizeof(double)) != cudaSuccess) {
+      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
+    }
+    std::memcpy(c->h_query, query, (size_t)s->features * sizeof(float));
+    for (int j = s->features; j < s->fpad; j++) c->h_query[j] = 0.f;
+    if (cudaMemcpyAsync(c->d_query, c->h_query, (size_t)s->fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(d_slots, slots.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
+      set_error("H2D copy failed"); rc = ORYX_E_CUDA; break;
+    }
+    rc = scores_rows_launch(m, kind, c->d_query, d_slots, n, d_out, c->stream);
+    if (rc != ORYX_OK) break;
+    if (cudaMemcpyAsync(out_scores, d_out, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+      set_error("scores_rows failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    }
+  } while (0);
+  cudaFree(d_slots); cudaFree(d_out);
+  ctx_release(m, c);
+  return rc;
+}
+
+int32_t oryx_topn_device(oryx_model* mh, int32_t kind, const float* d_query, int32_t how_many,
+                         int32_t* d_out_rows, double* d_out_scores, int32_t* d_out_n, void* stream) {
+  ORYX_ARG(mh && d_query && d_out_rows && d_out_scores && d_out_n, "null argument");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  // The asynchronous form uses one dedicated context (scratch + ticket counter): the caller orders
+  // these calls on `stream`, so they never overlap each other.
+  {
+    std::unique_lock<std::mutex> lk(m->pool_mu);
+    if (m->async_ctx == nullptr) {
+      auto c = std::make_unique<QueryCtx>();
+      int32_t rc = ctx_create(m, c.get());
+      if (rc != ORYX_OK) { ctx_destroy(c.get()); return rc; }
+      m->async_ctx = c.get();
+      m->pool_all.push_back(std::move(c));
+    }
+  }
+  QueryCtx* async_ctx = m->async_ctx;
+  TopnRequest rq{};
+  rq.kind = kind;
+  rq.d_query = d_query;
+  rq.how_many = how_many;
+  rq.d_excl = nullptr;
+  rq.n_excl = 0;
+  rq.d_out_rows = d_out_rows;
+  rq.d_out_scores = d_out_scores;
+  rq.d_out_n = d_out_n;
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  return scan_topn_launch(m, async_ctx, rq, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int32_t oryx_merge_topn_device(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int32_t n_lists,
+                               int32_t how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
+                               int32_t* d_out_n, void* stream) {
+  ORYX_ARG(d_scores && d_rows && d_n && d_out_rows && d_out_scores && d_out_n, "null argument");
+  ORYX_ARG(n_lists >= 1 && n_lists <= 1024, "n_lists out of range [1, 1024]");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  return merge_topn_launch(d_scores, d_rows, d_n, n_lists, how_many, row_stride, d_out_rows, d_out_scores,
+                           d_out_n, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int32_t oryx_stats_get(oryx_model* mh, oryx_stats* out) {
+  ORYX_ARG(mh && out, "null argument");
+  Model* m = reinterpret_cast<Model*>(mh);
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  std::memset(out, 0, sizeof(*out));
+  for (int w = 0; w < 2; w++) {
+    out->rows[w] = m->store[w].live;
+    out->slots[w] = m->store[w].n_slots;
+    out->device_bytes += m->store[w].device_bytes();
+  }
+  out->queries = m->queries.load();
+  out->kernel_launches = m->launches.load();
+  out->last_query_ms = m->last_query_ms.load();
+  return ORYX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,206 @@
+// common.cuh -- shared declarations of the oryx_b200 native library (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <shared_mutex>
+#include <vector>
+
+#include "oryx_b200.h"
+
+namespace oryx {
+
+// ---- error plumbing: status codes + thread-local message, no exceptions across the ABI.
+void set_error(const char* fmt, ...);
+const char* last_error();
+
+#define ORYX_CUDA(expr)                                                                     \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess) {                                                               \
+      ::oryx::set_error("CUDA: %s -> %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                          \
+      return ORYX_E_CUDA;                                                                   \
+    }                                                                                       \
+  } while (0)
+
+#define ORYX_ARG(cond, msg)                                           \
+  do {                                                                \
+    if (!(cond)) {                                                    \
+      ::oryx::set_error("invalid argument: %s (%s)", msg, #cond);     \
+      return ORYX_E_INVALID;                                          \
+    }                                                                 \
+  } while (0)
+
+#define ORYX_TRY(expr)             \
+  do {                             \
+    int32_t s__ = (expr);          \
+    if (s__ != ORYX_OK) return s__; \
+  } while (0)
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// ---- device-side helpers
+#ifdef __CUDACC__
+// 128-bit streaming load through the read-only path, no L1 allocation (Y is read once per scan).
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// Order-preserving map float -> uint32 (larger float <=> larger key).  Key 0 is reserved as the
+// "empty" sentinel: it corresponds to a negative NaN, which is never admitted to a top-N list.
+__device__ __forceinline__ uint32_t float_key(float f) {
+  uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+  uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(b);
+}
+
+// The reference's VectorMath.dot arithmetic, exactly: binary32 product, widened, binary64 add, in
+// index order (reference VectorMath.java:38-45).  Intrinsics forbid FMA contraction.
+__device__ __forceinline__ double exact_step(double acc, float a, float b) {
+  return __dadd_rn(acc, (double)__fmul_rn(a, b));
+}
+#endif
+
+// ---- the device-resident feature-vector store (one per X / Y).
+//
+// Layout in HBM:
+//   vec       [cap_slots x fpad] fp32, row-major, fpad = features rounded up to 4 so every row is
+//             16-byte aligned and can be read with 128-bit loads; padding floats are zero.
+//   slot_row  [cap_slots] int32: caller's row id living in the slot, -1 = empty / tombstone.
+//   slot_part [cap_slots] int32: LSH partition of the row (0 when the store is not hashed), -1 = empty.
+// The host keeps row -> slot and a free list; removed slots are zero-filled and reused.
+struct Store {
+  int features = 0;
+  int fpad = 0;
+  bool hashed = false;  // Y store with num_hashes > 0
+
+  float* d_vec = nullptr;
+  int32_t* d_slot_row = nullptr;
+  int32_t* d_slot_part = nullptr;
+  int64_t cap_slots = 0;
+  int64_t n_slots = 0;  // high-water mark
+  int64_t live = 0;
+
+  std::vector<int32_t> row2slot;
+  std::vector<int32_t> free_slots;
+
+  int64_t device_bytes() const { return cap_slots * ((int64_t)fpad * 4 + 8); }
+};
+
+// ---- per-query resources: a stream, device staging, scratch for the per-CTA candidate lists and
+// pinned host staging.  A small pool of these serves concurrent callers.
+struct QueryCtx {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float* d_query = nullptr;       // [fpad]
+  int32_t* d_excl = nullptr;      // [excl_cap]
+  int32_t excl_cap = 0;
+  uint2* d_cand = nullptr;        // scratch: [max_grid x max_k] (key, slot)
+  unsigned int* d_counter = nullptr;
+  int32_t* d_main_index = nullptr;
+  int32_t* d_out_rows = nullptr;  // [max_k]
+  double* d_out_scores = nullptr; // [max_k]
+  int32_t* d_out_n = nullptr;
+  // pinned host staging
+  float* h_query = nullptr;
+  int32_t* h_excl = nullptr;
+  int32_t* h_out_rows = nullptr;
+  double* h_out_scores = nullptr;
+  int32_t* h_out_n = nullptr;
+};
+
+struct Model {
+  oryx_config cfg{};
+  int device = 0;
+  int num_sms = 0;
+  int num_hashes = 0;
+  int max_bits = 0;
+  float* d_hash_vectors = nullptr;  // [num_hashes x fpad]
+  std::vector<float> h_hash_vectors;
+  Store store[2];
+
+  std::shared_mutex mu;  // queries shared, mutations exclusive
+  cudaStream_t update_stream = nullptr;
+
+  // query context pool
+  std::mutex pool_mu;
+  std::condition_variable pool_cv;
+  std::vector<QueryCtx*> pool_free;
+  std::vector<std::unique_ptr<QueryCtx>> pool_all;
+  int pool_limit = 8;
+  QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
+
+  std::atomic<int64_t> queries{0};
+  std::atomic<int64_t> launches{0};
+  std::atomic<double> last_query_ms{0.0};
+};
+
+constexpr int kTopnMargin = 8;                      // extra candidates re-scored exactly
+constexpr int kMaxK = ORYX_MAX_HOW_MANY + kTopnMargin;  // 1024
+constexpr int kMaxGrid = 148 * 8;
+
+// store.cu
+int32_t store_init(Model* m, int which, int64_t capacity_hint);
+void store_free(Store* s);
+int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs, int32_t n,
+                     int32_t* out_partitions);
+int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float* d_vecs, int64_t n);
+int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n);
+int32_t store_get(Model* m, int which, int32_t row, float* out, int32_t* found);
+int32_t store_compact(Model* m, int which);
+
+// lsh.cu
+int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits);
+// Hash n packed rows (row stride `stride` floats) on `stream`; writes int32 partition per row.
+int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int stride, int32_t* d_out,
+                             cudaStream_t stream);
+int32_t lsh_candidates_device(Model* m, const int32_t* d_main_index, int32_t* d_out, int32_t* d_out_n,
+                              cudaStream_t stream);
+
+// scan_topn.cu
+struct TopnRequest {
+  int kind;
+  const float* d_query;  // [fpad] device
+  int how_many;
+  const int32_t* d_excl;  // sorted row ids, device
+  int n_excl;
+  int32_t* d_out_rows;
+  double* d_out_scores;
+  int32_t* d_out_n;
+};
+int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStream_t stream);
+int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_rows, double* d_out,
+                          cudaStream_t stream);
+
+int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32_t* d_slots, int n,
+                           double* d_out, cudaStream_t stream);
+
+int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists,
+                          int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
+                          int32_t* d_out_n, cudaStream_t stream);
+
+// gram.cu
+int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);
+
+// pool
+int32_t ctx_acquire(Model* m, QueryCtx** out);
+void ctx_release(Model* m, QueryCtx* ctx);
+void ctx_destroy(QueryCtx* c);
+
+}  // namespace oryx

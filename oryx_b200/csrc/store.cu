@@ -1,0 +1,407 @@
+// store.cu -- device-resident feature-vector store: the B200 counterpart of the reference's
+// FeatureVectors (app/oryx-app-common/.../als/FeatureVectors.java:36-154) and of the partitioned
+// `FeatureVectors[] Y` of ALSServingModel (.../serving/als/model/ALSServingModel.java:69,161-183).
+//
+// The reference keeps one heap-allocated float[] per ID in a hash map per LSH partition and moves an
+// item between maps when its hash changes.  Here all rows of a store live in one row-major fp32
+// matrix in HBM; partition membership is a per-slot int32 (`slot_part`) that the scan kernel tests,
+// so "moving" a row between partitions is an in-place update of that integer.  oryx_items_compact
+// re-orders slots so rows of one partition are contiguous, which only affects scan locality.
+#include <algorithm>
+#include <numeric>
+
+#include "common.cuh"
+
+namespace oryx {
+
+namespace {
+
+constexpr int64_t kChunkRows = 1 << 18;
+
+// One warp per incoming row: copy `features` floats to the destination slot, zero the padding,
+// record the row id and partition.
+__global__ void scatter_rows_kernel(const float* __restrict__ in, int64_t in_stride, int features,
+                                    int fpad, const int32_t* __restrict__ dst_slot,
+                                    const int32_t* __restrict__ rows, const int32_t* __restrict__ parts,
+                                    int64_t n, float* __restrict__ vec, int32_t* __restrict__ slot_row,
+                                    int32_t* __restrict__ slot_part) {
+  int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  int32_t slot = dst_slot[w];
+  if (slot < 0) return;  // superseded by a later occurrence of the same row in this batch
+  const float* src = in + w * in_stride;
+  float* dst = vec + (int64_t)slot * fpad;
+  for (int j = lane; j < fpad; j += 32) dst[j] = j < features ? src[j] : 0.0f;
+  if (lane == 0) {
+    slot_row[slot] = rows[w];
+    slot_part[slot] = parts ? parts[w] : 0;
+  }
+}
+
+__global__ void clear_slots_kernel(const int32_t* __restrict__ slots, int64_t n, int fpad,
+                                   float* __restrict__ vec, int32_t* __restrict__ slot_row,
+                                   int32_t* __restrict__ slot_part) {
+  int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  int32_t slot = slots[w];
+  float* dst = vec + (int64_t)slot * fpad;
+  for (int j = lane; j < fpad; j += 32) dst[j] = 0.0f;
+  if (lane == 0) {
+    slot_row[slot] = -1;
+    slot_part[slot] = -1;
+  }
+}
+
+__global__ void fill_i32_kernel(int32_t* p, int64_t n, int32_t v) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+__global__ void iota_rows_kernel(int32_t* p, int64_t n, int32_t first) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = first + (int32_t)i;
+}
+
+// Gather for compaction: new slot i takes old slot src[i].
+__global__ void gather_slots_kernel(const int32_t* __restrict__ src, int64_t n, int fpad,
+                                    const float4* __restrict__ old_vec,
+                                    const int32_t* __restrict__ old_row,
+                                    const int32_t* __restrict__ old_part, float4* __restrict__ new_vec,
+                                    int32_t* __restrict__ new_row, int32_t* __restrict__ new_part) {
+  int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  int32_t s = src[w];
+  int f4 = fpad >> 2;
+  for (int j = lane; j < f4; j += 32) new_vec[w * f4 + j] = old_vec[(int64_t)s * f4 + j];
+  if (lane == 0) {
+    new_row[w] = old_row[s];
+    new_part[w] = old_part[s];
+  }
+}
+
+int32_t grow(Model* m, Store* s, int64_t need) {
+  if (need <= s->cap_slots) return ORYX_OK;
+  int64_t cap = std::max<int64_t>(need, s->cap_slots + s->cap_slots / 2);
+  cap = std::max<int64_t>(cap, 1024);
+  float* nv = nullptr;
+  int32_t *nr = nullptr, *np = nullptr;
+  cudaError_t e = cudaMalloc(&nv, (size_t)cap * s->fpad * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&nr, (size_t)cap * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&np, (size_t)cap * sizeof(int32_t));
+  if (e != cudaSuccess) {
+    cudaFree(nv); cudaFree(nr); cudaFree(np);
+    cudaGetLastError();
+    set_error("device allocation of %lld slots x %d floats failed: %s", (long long)cap, s->fpad,
+              cudaGetErrorString(e));
+    return ORYX_E_NOMEM;
+  }
+  cudaStream_t st = m->update_stream;
+  if (s->n_slots > 0) {
+    ORYX_CUDA(cudaMemcpyAsync(nv, s->d_vec, (size_t)s->n_slots * s->fpad * sizeof(float),
+                              cudaMemcpyDeviceToDevice, st));
+    ORYX_CUDA(cudaMemcpyAsync(nr, s->d_slot_row, (size_t)s->n_slots * sizeof(int32_t),
+                              cudaMemcpyDeviceToDevice, st));
+    ORYX_CUDA(cudaMemcpyAsync(np, s->d_slot_part, (size_t)s->n_slots * sizeof(int32_t),
+                              cudaMemcpyDeviceToDevice, st));
+  }
+  int64_t tail = cap - s->n_slots;
+  if (tail > 0) {
+    int threads = 256;
+    int64_t blocks = (tail + threads - 1) / threads;
+    fill_i32_kernel<<<(unsigned)blocks, threads, 0, st>>>(nr + s->n_slots, tail, -1);
+    fill_i32_kernel<<<(unsigned)blocks, threads, 0, st>>>(np + s->n_slots, tail, -1);
+    m->launches += 2;
+    ORYX_CUDA(cudaMemsetAsync(nv + s->n_slots * s->fpad, 0, (size_t)tail * s->fpad * sizeof(float), st));
+  }
+  ORYX_CUDA(cudaStreamSynchronize(st));
+  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part);
+  s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np;
+  s->cap_slots = cap;
+  return ORYX_OK;
+}
+
+// Grow-only staging used by the (single) updater thread.
+struct Staging {
+  float* d_vec = nullptr; size_t vec_bytes = 0;
+  int32_t* d_i32 = nullptr; size_t i32_count = 0;  // [3 x chunk]: dst, rows, parts
+  int32_t* h_i32 = nullptr; size_t h_count = 0;    // pinned
+};
+thread_local Staging g_staging;  // one updater thread per store by contract
+
+int32_t staging_reserve(int64_t rows, int features, bool need_vec) {
+  Staging& g = g_staging;
+  size_t vb = need_vec ? (size_t)rows * features * sizeof(float) : 0;
+  if (vb > g.vec_bytes) {
+    cudaFree(g.d_vec);
+    g.d_vec = nullptr; g.vec_bytes = 0;
+    ORYX_CUDA(cudaMalloc(&g.d_vec, vb));
+    g.vec_bytes = vb;
+  }
+  size_t ic = (size_t)rows * 3;
+  if (ic > g.i32_count) {
+    cudaFree(g.d_i32);
+    g.d_i32 = nullptr; g.i32_count = 0;
+    ORYX_CUDA(cudaMalloc(&g.d_i32, ic * sizeof(int32_t)));
+    g.i32_count = ic;
+  }
+  if (ic > g.h_count) {
+    cudaFreeHost(g.h_i32);
+    g.h_i32 = nullptr; g.h_count = 0;
+    ORYX_CUDA(cudaMallocHost(&g.h_i32, ic * sizeof(int32_t)));
+    g.h_count = ic;
+  }
+  return ORYX_OK;
+}
+
+// Host-side slot assignment for rows[0..n): writes dst slots into h_dst (or -1 for an occurrence
+// superseded later in the same chunk).  Returns the new high-water mark through the store.
+int32_t assign_slots(Model* m, Store* s, const int32_t* rows, int64_t n, int32_t first_row,
+                     int32_t* h_dst) {
+  int32_t max_row = -1;
+  for (int64_t k = 0; k < n; k++) {
+    int32_t r = rows ? rows[k] : first_row + (int32_t)k;
+    if (r < 0) {
+      set_error("negative row id %d at position %lld", r, (long long)k);
+      return ORYX_E_INVALID;
+    }
+    max_row = std::max(max_row, r);
+  }
+  if ((int64_t)max_row >= (int64_t)s->row2slot.size()) {
+    s->row2slot.resize((size_t)max_row + 1 + (size_t)max_row / 4, -1);
+  }
+  // Count new slots needed first so the device buffers can grow before any kernel runs.
+  int64_t fresh = 0;
+  for (int64_t k = 0; k < n; k++) {
+    int32_t r = rows ? rows[k] : first_row + (int32_t)k;
+    if (s->row2slot[r] < 0) fresh++;
+  }
+  int64_t from_free = std::min<int64_t>(fresh, (int64_t)s->free_slots.size());
+  ORYX_TRY(grow(m, s, s->n_slots + (fresh - from_free)));
+  // last occurrence wins inside a chunk: remember where each slot was last written
+  std::vector<int64_t> slot_writer;  // lazily sized only when a duplicate shows up
+  for (int64_t k = 0; k < n; k++) {
+    int32_t r = rows ? rows[k] : first_row + (int32_t)k;
+    int32_t slot = s->row2slot[r];
+    if (slot < 0) {
+      if (!s->free_slots.empty()) {
+        slot = s->free_slots.back();
+        s->free_slots.pop_back();
+      } else {
+        slot = (int32_t)s->n_slots++;
+      }
+      s->row2slot[r] = slot;
+      s->live++;
+    }
+    h_dst[k] = slot;
+  }
+  if (rows) {
+    // Detect duplicates: same slot targeted twice in this chunk.
+    std::vector<int32_t> order((size_t)n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return h_dst[a] < h_dst[b]; });
+    for (int64_t i = 0; i + 1 < n; i++) {
+      if (h_dst[order[i]] == h_dst[order[i + 1]]) h_dst[order[i]] = -1;  // earlier occurrence loses
+    }
+  }
+  return ORYX_OK;
+}
+
+}  // namespace
+
+int32_t store_init(Model* m, int which, int64_t capacity_hint) {
+  Store* s = &m->store[which];
+  s->features = m->cfg.features;
+  s->fpad = round_up(m->cfg.features, 4);
+  s->hashed = (which == ORYX_Y) && m->num_hashes > 0;
+  if (capacity_hint > 0) ORYX_TRY(grow(m, s, capacity_hint));
+  return ORYX_OK;
+}
+
+void store_free(Store* s) {
+  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part);
+  s->d_vec = nullptr; s->d_slot_row = nullptr; s->d_slot_part = nullptr;
+  s->cap_slots = s->n_slots = s->live = 0;
+  s->row2slot.clear(); s->free_slots.clear();
+}
+
+int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs, int32_t n,
+                     int32_t* out_partitions) {
+  Store* s = &m->store[which];
+  cudaStream_t st = m->update_stream;
+  const int F = s->features;
+  for (int64_t off = 0; off < n; off += kChunkRows) {
+    int64_t c = std::min<int64_t>(kChunkRows, n - off);
+    ORYX_TRY(staging_reserve(c, F, true));
+    Staging& g = g_staging;
+    int32_t* h_dst = g.h_i32;
+    int32_t* h_rows = g.h_i32 + c;
+    int32_t* h_parts = g.h_i32 + 2 * c;
+    int32_t* d_dst = g.d_i32;
+    int32_t* d_rows = g.d_i32 + c;
+    int32_t* d_parts = g.d_i32 + 2 * c;
+    ORYX_TRY(assign_slots(m, s, rows + off, c, 0, h_dst));
+    std::memcpy(h_rows, rows + off, (size_t)c * sizeof(int32_t));
+    ORYX_CUDA(cudaMemcpyAsync(g.d_vec, vecs + off * F, (size_t)c * F * sizeof(float),
+                              cudaMemcpyHostToDevice, st));
+    ORYX_CUDA(cudaMemcpyAsync(d_dst, h_dst, (size_t)c * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (s->hashed) {
+      ORYX_TRY(lsh_hash_rows_device(m, g.d_vec, c, F, d_parts, st));
+      if (out_partitions) {
+        ORYX_CUDA(cudaMemcpyAsync(h_parts, d_parts, (size_t)c * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+      }
+    }
+    int threads = 256;
+    int64_t blocks = (c * 32 + threads - 1) / threads;
+    scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
+        g.d_vec, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
+        s->d_slot_row, s->d_slot_part);
+    m->launches++;
+    ORYX_CUDA(cudaGetLastError());
+    ORYX_CUDA(cudaStreamSynchronize(st));
+    if (out_partitions) {
+      if (s->hashed) std::memcpy(out_partitions + off, h_parts, (size_t)c * sizeof(int32_t));
+      else std::fill(out_partitions + off, out_partitions + off + c, 0);
+    }
+  }
+  return ORYX_OK;
+}
+
+int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float* d_vecs, int64_t n) {
+  Store* s = &m->store[which];
+  cudaStream_t st = m->update_stream;
+  const int F = s->features;
+  const int64_t chunk = 1 << 20;
+  for (int64_t off = 0; off < n; off += chunk) {
+    int64_t c = std::min<int64_t>(chunk, n - off);
+    ORYX_TRY(staging_reserve(c, F, false));
+    Staging& g = g_staging;
+    int32_t* h_dst = g.h_i32;
+    int32_t* d_dst = g.d_i32;
+    int32_t* d_rows = g.d_i32 + c;
+    int32_t* d_parts = g.d_i32 + 2 * c;
+    ORYX_TRY(assign_slots(m, s, nullptr, c, first_row + (int32_t)off, h_dst));
+    ORYX_CUDA(cudaMemcpyAsync(d_dst, h_dst, (size_t)c * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    int threads = 256;
+    iota_rows_kernel<<<(unsigned)((c + threads - 1) / threads), threads, 0, st>>>(d_rows, c, first_row + (int32_t)off);
+    m->launches++;
+    const float* src = d_vecs + off * F;
+    if (s->hashed) ORYX_TRY(lsh_hash_rows_device(m, src, c, F, d_parts, st));
+    int64_t blocks = (c * 32 + threads - 1) / threads;
+    scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
+        src, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
+        s->d_slot_row, s->d_slot_part);
+    m->launches++;
+    ORYX_CUDA(cudaGetLastError());
+    ORYX_CUDA(cudaStreamSynchronize(st));
+  }
+  return ORYX_OK;
+}
+
+int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
+  Store* s = &m->store[which];
+  cudaStream_t st = m->update_stream;
+  ORYX_TRY(staging_reserve(std::max(n, 1), s->features, false));
+  Staging& g = g_staging;
+  int32_t cnt = 0;
+  for (int32_t k = 0; k < n; k++) {
+    int32_t r = rows[k];
+    if (r < 0 || (size_t)r >= s->row2slot.size()) continue;
+    int32_t slot = s->row2slot[r];
+    if (slot < 0) continue;  // FeatureVectors.removeVector on an absent id is a no-op (FV:84-89)
+    s->row2slot[r] = -1;
+    s->free_slots.push_back(slot);
+    s->live--;
+    g.h_i32[cnt++] = slot;
+  }
+  if (cnt == 0) return ORYX_OK;
+  ORYX_CUDA(cudaMemcpyAsync(g.d_i32, g.h_i32, (size_t)cnt * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  int threads = 256;
+  int64_t blocks = ((int64_t)cnt * 32 + threads - 1) / threads;
+  clear_slots_kernel<<<(unsigned)blocks, threads, 0, st>>>(g.d_i32, cnt, s->fpad, s->d_vec,
+                                                          s->d_slot_row, s->d_slot_part);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
+  ORYX_CUDA(cudaStreamSynchronize(st));
+  return ORYX_OK;
+}
+
+int32_t store_get(Model* m, int which, int32_t row, float* out, int32_t* found) {
+  Store* s = &m->store[which];
+  *found = 0;
+  if (row < 0 || (size_t)row >= s->row2slot.size()) return ORYX_OK;
+  int32_t slot = s->row2slot[row];
+  if (slot < 0) return ORYX_OK;
+  ORYX_CUDA(cudaMemcpy(out, s->d_vec + (int64_t)slot * s->fpad, (size_t)s->features * sizeof(float),
+                       cudaMemcpyDeviceToHost));
+  *found = 1;
+  return ORYX_OK;
+}
+
+int32_t store_compact(Model* m, int which) {
+  Store* s = &m->store[which];
+  cudaStream_t st = m->update_stream;
+  int64_t n = s->n_slots;
+  if (n == 0) return ORYX_OK;
+  std::vector<int32_t> part((size_t)n), rowid((size_t)n);
+  ORYX_CUDA(cudaMemcpy(part.data(), s->d_slot_part, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  ORYX_CUDA(cudaMemcpy(rowid.data(), s->d_slot_row, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  // stable counting sort of live slots by partition
+  int n_parts = 1 << m->num_hashes;
+  if (!s->hashed) n_parts = 1;
+  std::vector<int64_t> start((size_t)n_parts + 1, 0);
+  int64_t live = 0;
+  for (int64_t i = 0; i < n; i++) {
+    if (rowid[i] >= 0 && part[i] >= 0 && part[i] < n_parts) { start[part[i] + 1]++; live++; }
+  }
+  for (int p = 0; p < n_parts; p++) start[p + 1] += start[p];
+  std::vector<int32_t> src((size_t)std::max<int64_t>(live, 1));
+  {
+    std::vector<int64_t> fill(start.begin(), start.end() - 1);
+    for (int64_t i = 0; i < n; i++) {
+      if (rowid[i] >= 0 && part[i] >= 0 && part[i] < n_parts) src[fill[part[i]]++] = (int32_t)i;
+    }
+  }
+  int64_t cap = std::max<int64_t>(s->cap_slots, 1024);
+  float* nv = nullptr; int32_t *nr = nullptr, *np = nullptr, *d_src = nullptr;
+  cudaError_t e = cudaMalloc(&nv, (size_t)cap * s->fpad * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&nr, (size_t)cap * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&np, (size_t)cap * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d_src, (size_t)std::max<int64_t>(live, 1) * sizeof(int32_t));
+  if (e != cudaSuccess) {
+    cudaFree(nv); cudaFree(nr); cudaFree(np); cudaFree(d_src);
+    cudaGetLastError();
+    set_error("compaction needs a second copy of the store: %s", cudaGetErrorString(e));
+    return ORYX_E_NOMEM;
+  }
+  int threads = 256;
+  if (live > 0) {
+    ORYX_CUDA(cudaMemcpyAsync(d_src, src.data(), (size_t)live * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    int64_t blocks = (live * 32 + threads - 1) / threads;
+    gather_slots_kernel<<<(unsigned)blocks, threads, 0, st>>>(
+        d_src, live, s->fpad, reinterpret_cast<const float4*>(s->d_vec), s->d_slot_row, s->d_slot_part,
+        reinterpret_cast<float4*>(nv), nr, np);
+    m->launches++;
+  }
+  int64_t tail = cap - live;
+  if (tail > 0) {
+    int64_t blocks = (tail + threads - 1) / threads;
+    fill_i32_kernel<<<(unsigned)blocks, threads, 0, st>>>(nr + live, tail, -1);
+    fill_i32_kernel<<<(unsigned)blocks, threads, 0, st>>>(np + live, tail, -1);
+    m->launches += 2;
+    ORYX_CUDA(cudaMemsetAsync(nv + live * s->fpad, 0, (size_t)tail * s->fpad * sizeof(float), st));
+  }
+  ORYX_CUDA(cudaGetLastError());
+  ORYX_CUDA(cudaStreamSynchronize(st));
+  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(d_src);
+  s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np;
+  s->cap_slots = cap;
+  s->n_slots = live;
+  s->free_slots.clear();
+  for (int64_t i = 0; i < live; i++) s->row2slot[rowid[src[i]]] = (int32_t)i;
+  return ORYX_OK;
+}
+
+}  // namespace oryx

@@ -1,0 +1,321 @@
+"""ctypes binding over the C ABI in include/oryx_b200.h (see that header for the reference
+counterpart of every entry point)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liboryx_b200.so")
+
+OK, E_INVALID, E_CUDA, E_SINGULAR, E_NOMEM, E_UNSUPPORTED = 0, 1, 2, 3, 4, 5
+DOT, COSINE = 0, 1
+X, Y = 0, 1
+MAX_HOW_MANY = 1016
+
+
+class OryxError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"oryx_b200 status {status}: {message}")
+        self.status = status
+
+
+class SingularMatrixSolverException(OryxError):
+    """ORYX_E_SINGULAR, mirror of com.cloudera.oryx.common.math.SingularMatrixSolverException."""
+
+    def __init__(self, apparent_rank: int, message: str):
+        super().__init__(E_SINGULAR, message)
+        self.apparent_rank = apparent_rank
+
+
+class _Config(C.Structure):
+    _fields_ = [("features", C.c_int32), ("implicit", C.c_int32), ("num_hashes", C.c_int32),
+                ("max_bits_differing", C.c_int32), ("hash_vectors", C.POINTER(C.c_float)),
+                ("device", C.c_int32), ("reserved", C.c_int32), ("capacity_hint", C.c_int64)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [("rows", C.c_int64 * 2), ("slots", C.c_int64 * 2), ("device_bytes", C.c_int64),
+                ("queries", C.c_int64), ("kernel_launches", C.c_int64), ("last_query_ms", C.c_double)]
+
+
+def build(verbose: bool = False) -> str:
+    """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j", str(os.cpu_count() or 4)]
+    if not verbose:
+        cmd.insert(1, "-s")
+    subprocess.check_call(cmd)
+    return _SO
+
+
+_lib = None
+
+# name -> (restype, argtypes); the list every test checks against include/oryx_b200.h
+_f32p, _f64p = C.POINTER(C.c_float), C.POINTER(C.c_double)
+_i32p, _i64p, _u8p = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_uint8)
+SIGNATURES = {
+    "oryx_lsh_plan": [C.c_double, C.c_int32, _i32p, _i32p],
+    "oryx_model_create": [C.POINTER(_Config), C.POINTER(C.c_void_p)],
+    "oryx_model_destroy": [C.c_void_p],
+    "oryx_items_upsert": [C.c_void_p, C.c_int32, _i32p, _f32p, C.c_int32, _i32p],
+    "oryx_items_upsert_device": [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64],
+    "oryx_items_remove": [C.c_void_p, C.c_int32, _i32p, C.c_int32],
+    "oryx_items_get": [C.c_void_p, C.c_int32, C.c_int32, _f32p, _i32p],
+    "oryx_items_compact": [C.c_void_p, C.c_int32],
+    "oryx_lsh_index": [C.c_void_p, _f32p, _i32p],
+    "oryx_lsh_index_rows": [C.c_void_p, _f32p, C.c_int32, _i32p],
+    "oryx_lsh_candidates": [C.c_void_p, _f32p, _i32p, _i32p],
+    "oryx_topn": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _i32p, C.c_int32, _i32p, _f64p, _i32p],
+    "oryx_topn_batch": [C.c_void_p, C.c_int32, _f32p, C.c_int32, C.c_int32, _i32p, _i32p, _i32p, _f64p, _i32p],
+    "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
+    "oryx_scores_rows": [C.c_void_p, C.c_int32, _f32p, _i32p, C.c_int32, _f64p, _u8p],
+    "oryx_topn_device": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_merge_topn_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
+    "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
+    "oryx_solver_destroy": [C.c_void_p],
+    "oryx_solve_f2f": [C.c_void_p, _f32p, _f32p],
+    "oryx_fold_in_batch": [C.c_void_p, C.c_int32, _f32p, _u8p, _f32p, _f64p, C.c_int64, _f32p, _u8p],
+    "oryx_last_error": [C.c_char_p, C.c_int32],
+    "oryx_stats_get": [C.c_void_p, C.POINTER(_Stats)],
+}
+
+
+def lib() -> C.CDLL:
+    """Load liboryx_b200.so.  There is no fallback: a missing library is an error."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise ImportError(
+                f"{_SO} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or `make -C oryx_b200/csrc`).  oryx_b200 has no CPU fallback.")
+        L = C.CDLL(_SO)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = C.c_int32
+            fn.argtypes = argtypes
+        _lib = L
+    return _lib
+
+
+def _last_error() -> str:
+    buf = C.create_string_buffer(512)
+    lib().oryx_last_error(buf, 512)
+    return buf.value.decode("utf-8", "replace")
+
+
+def _check(status: int):
+    if status != OK:
+        raise OryxError(status, _last_error())
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a, t):
+    return None if a is None else a.ctypes.data_as(C.POINTER(t))
+
+
+def lsh_plan(sample_rate: float, num_cores: int):
+    h, b = C.c_int32(), C.c_int32()
+    _check(lib().oryx_lsh_plan(sample_rate, num_cores, C.byref(h), C.byref(b)))
+    return h.value, b.value
+
+
+class Model:
+    """Handle over oryx_model: the device-resident X/Y stores plus the LSH geometry."""
+
+    def __init__(self, features: int, implicit: bool = True, hash_vectors=None, max_bits_differing: int = 0,
+                 device: int = 0, capacity_hint: int = 0):
+        hv = None if hash_vectors is None or len(hash_vectors) == 0 else _f32(hash_vectors)
+        cfg = _Config()
+        cfg.features = features
+        cfg.implicit = int(implicit)
+        cfg.num_hashes = 0 if hv is None else hv.shape[0]
+        cfg.max_bits_differing = max_bits_differing
+        cfg.hash_vectors = _ptr(hv, C.c_float)
+        cfg.device = device
+        cfg.capacity_hint = capacity_hint
+        self.features = features
+        self.num_hashes = cfg.num_hashes
+        self.max_bits = max_bits_differing
+        self._h = C.c_void_p()
+        _check(lib().oryx_model_create(C.byref(cfg), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().oryx_model_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- store
+    def upsert(self, which: int, rows, vecs) -> np.ndarray:
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        vecs = _f32(vecs).reshape(rows.size, self.features)
+        parts = np.zeros(rows.size, dtype=np.int32)
+        _check(lib().oryx_items_upsert(self._h, which, _ptr(rows, C.c_int32), _ptr(vecs, C.c_float),
+                                       rows.size, _ptr(parts, C.c_int32)))
+        return parts
+
+    def upsert_device(self, which: int, first_row: int, device_ptr: int, n: int):
+        _check(lib().oryx_items_upsert_device(self._h, which, first_row, C.c_void_p(device_ptr), n))
+
+    def remove(self, which: int, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        _check(lib().oryx_items_remove(self._h, which, _ptr(rows, C.c_int32), rows.size))
+
+    def get(self, which: int, row: int):
+        out = np.zeros(self.features, dtype=np.float32)
+        found = C.c_int32()
+        _check(lib().oryx_items_get(self._h, which, row, _ptr(out, C.c_float), C.byref(found)))
+        return out if found.value else None
+
+    def compact(self, which: int = Y):
+        _check(lib().oryx_items_compact(self._h, which))
+
+    # ---- LSH
+    def lsh_index(self, vec) -> int:
+        v = _f32(vec)
+        out = C.c_int32()
+        _check(lib().oryx_lsh_index(self._h, _ptr(v, C.c_float), C.byref(out)))
+        return out.value
+
+    def lsh_index_rows(self, vecs) -> np.ndarray:
+        v = _f32(vecs).reshape(-1, self.features)
+        out = np.zeros(v.shape[0], dtype=np.int32)
+        _check(lib().oryx_lsh_index_rows(self._h, _ptr(v, C.c_float), v.shape[0], _ptr(out, C.c_int32)))
+        return out
+
+    def lsh_candidates(self, vec) -> np.ndarray:
+        v = _f32(vec)
+        out = np.zeros(1 << self.num_hashes, dtype=np.int32)
+        n = C.c_int32()
+        _check(lib().oryx_lsh_candidates(self._h, _ptr(v, C.c_float), _ptr(out, C.c_int32), C.byref(n)))
+        return out[:n.value].copy()
+
+    # ---- queries
+    def topn(self, kind: int, query, how_many: int, excluded=None):
+        q = _f32(query)
+        ex = None if excluded is None or len(excluded) == 0 else np.ascontiguousarray(excluded, dtype=np.int32)
+        rows = np.zeros(max(how_many, 1), dtype=np.int32)
+        scores = np.zeros(max(how_many, 1), dtype=np.float64)
+        n = C.c_int32()
+        _check(lib().oryx_topn(self._h, kind, _ptr(q, C.c_float), how_many, _ptr(ex, C.c_int32),
+                               0 if ex is None else ex.size, _ptr(rows, C.c_int32),
+                               _ptr(scores, C.c_double), C.byref(n)))
+        return rows[:n.value].copy(), scores[:n.value].copy()
+
+    def topn_batch(self, kind: int, queries, how_many: int, excluded_lists=None):
+        q = _f32(queries).reshape(-1, self.features)
+        nq = q.shape[0]
+        offs = rows_ex = None
+        if excluded_lists is not None:
+            offs = np.zeros(nq + 1, dtype=np.int32)
+            offs[1:] = np.cumsum([len(e) for e in excluded_lists])
+            rows_ex = np.ascontiguousarray(np.concatenate([np.asarray(e, dtype=np.int32) for e in excluded_lists])
+                                           if offs[-1] else np.zeros(1, dtype=np.int32), dtype=np.int32)
+        rows = np.zeros((nq, how_many), dtype=np.int32)
+        scores = np.zeros((nq, how_many), dtype=np.float64)
+        n = np.zeros(nq, dtype=np.int32)
+        _check(lib().oryx_topn_batch(self._h, kind, _ptr(q, C.c_float), nq, how_many, _ptr(offs, C.c_int32),
+                                     _ptr(rows_ex, C.c_int32), _ptr(rows, C.c_int32), _ptr(scores, C.c_double),
+                                     _ptr(n, C.c_int32)))
+        return rows, scores, n
+
+    def scores_all(self, kind: int, query, n_rows: int) -> np.ndarray:
+        q = _f32(query)
+        out = np.zeros(n_rows, dtype=np.float64)
+        _check(lib().oryx_scores_all(self._h, kind, _ptr(q, C.c_float), n_rows, _ptr(out, C.c_double)))
+        return out
+
+    def scores_rows(self, kind: int, query, rows):
+        q = _f32(query)
+        r = np.ascontiguousarray(rows, dtype=np.int32)
+        out = np.zeros(r.size, dtype=np.float64)
+        found = np.zeros(r.size, dtype=np.uint8)
+        _check(lib().oryx_scores_rows(self._h, kind, _ptr(q, C.c_float), _ptr(r, C.c_int32), r.size,
+                                      _ptr(out, C.c_double), _ptr(found, C.c_uint8)))
+        return out, found.astype(bool)
+
+    def topn_device(self, kind: int, d_query: int, how_many: int, d_rows: int, d_scores: int, d_n: int, stream: int):
+        _check(lib().oryx_topn_device(self._h, kind, C.c_void_p(d_query), how_many, C.c_void_p(d_rows),
+                                      C.c_void_p(d_scores), C.c_void_p(d_n), C.c_void_p(stream)))
+
+    def gram(self, which: int = Y):
+        out = np.zeros((self.features, self.features), dtype=np.float64)
+        used = C.c_int64()
+        _check(lib().oryx_gram(self._h, which, _ptr(out, C.c_double), C.byref(used)))
+        return (out if used.value > 0 else None), used.value
+
+    def stats(self) -> dict:
+        s = _Stats()
+        _check(lib().oryx_stats_get(self._h, C.byref(s)))
+        return {"rows": list(s.rows), "slots": list(s.slots), "device_bytes": s.device_bytes,
+                "queries": s.queries, "kernel_launches": s.kernel_launches, "last_query_ms": s.last_query_ms}
+
+
+def merge_topn_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, how_many: int, row_stride: int,
+                      d_out_rows: int, d_out_scores: int, d_out_n: int, stream: int):
+    _check(lib().oryx_merge_topn_device(C.c_void_p(d_scores), C.c_void_p(d_rows), C.c_void_p(d_n), n_lists,
+                                        how_many, row_stride, C.c_void_p(d_out_rows), C.c_void_p(d_out_scores),
+                                        C.c_void_p(d_out_n), C.c_void_p(stream)))
+
+
+class Solver:
+    """Handle over oryx_solver (LinearSystemSolver.getSolver -> Solver)."""
+
+    def __init__(self, gram, device: int = 0):
+        g = np.ascontiguousarray(gram, dtype=np.float64)
+        assert g.ndim == 2 and g.shape[0] == g.shape[1]
+        self.n = g.shape[0]
+        self._h = C.c_void_p()
+        rank = C.c_int32()
+        st = lib().oryx_solver_create(_ptr(g, C.c_double), self.n, device, C.byref(self._h), C.byref(rank))
+        if st == E_SINGULAR:
+            raise SingularMatrixSolverException(rank.value, _last_error())
+        _check(st)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().oryx_solver_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def solve_f2f(self, b) -> np.ndarray:
+        b = _f32(b)
+        x = np.zeros(self.n, dtype=np.float32)
+        _check(lib().oryx_solve_f2f(self._h, _ptr(b, C.c_float), _ptr(x, C.c_float)))
+        return x
+
+    def fold_in_batch(self, implicit: bool, xu, has_xu, yi, values):
+        yi = _f32(yi).reshape(-1, self.n)
+        n = yi.shape[0]
+        xu_a = None if xu is None else _f32(xu).reshape(n, self.n)
+        has = None if has_xu is None else np.ascontiguousarray(has_xu, dtype=np.uint8)
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        out = np.zeros((n, self.n), dtype=np.float32)
+        valid = np.zeros(n, dtype=np.uint8)
+        _check(lib().oryx_fold_in_batch(self._h, int(implicit), _ptr(xu_a, C.c_float), _ptr(has, C.c_uint8),
+                                        _ptr(yi, C.c_float), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),
+                                        _ptr(valid, C.c_uint8)))
+        return out, valid

@@ -1,0 +1,345 @@
+"""GPU parity: the CUDA library, called through its C ABI, against the CPU oracle on the same
+seeded inputs and against the reference's golden vectors.  Integer/index results (LSH partitions,
+candidate lists, top-N row ids) must be identical; returned scores are produced by the exact
+finishing pass and must be bit-identical to the oracle's doubles."""
+import numpy as np
+import pytest
+
+import oracle
+import oryx_b200 as ob
+from als_harness import (ServingHarness, check_fixed_model_goldens, load_golden, random_hash_vectors,
+                         random_model)
+
+pytestmark = pytest.mark.gpu
+
+
+class GpuBackend:
+    """als_harness backend that routes every computation through liboryx_b200.so."""
+
+    name = "gpu"
+
+    def __init__(self, features, y, hash_vectors=None, max_bits=0, implicit=True):
+        self.features = features
+        self.n = len(y)
+        self.model = ob.Model(features, implicit=implicit, hash_vectors=hash_vectors, max_bits_differing=max_bits)
+        self.parts = self.model.upsert(ob.Y, np.arange(self.n, dtype=np.int32), y) if self.n else None
+
+    def topn(self, kind, q, how_many, excluded=None):
+        return self.model.topn(kind, q, how_many, excluded)
+
+    def scores_all(self, kind, q):
+        return self.model.scores_all(kind, q, self.n)
+
+    def gram(self):
+        return self.model.gram(ob.Y)[0]
+
+    def solver(self, g):
+        return ob.Solver(g)
+
+    def updated_xu(self, solver, value, xu, yi, implicit):
+        if yi is None:
+            return None
+        out, valid = solver.fold_in_batch(implicit, None if xu is None else xu[None, :],
+                                          None if xu is not None else np.zeros(1, np.uint8),
+                                          yi[None, :], [value])
+        return out[0] if valid[0] else None
+
+    def dot(self, x, y):
+        # point lookup through the store is exercised in test_scores_rows; here a 1-row scratch model
+        return _point(self.features, x, y, ob.DOT)
+
+    def norm(self, x):
+        import math
+        return math.sqrt(_point(self.features, x, x, ob.DOT))
+
+    def close(self):
+        self.model.close()
+
+
+def _point(features, q, y, kind):
+    with ob.Model(features) as m:
+        m.upsert(ob.Y, [0], np.asarray(y, dtype=np.float32)[None, :])
+        return float(m.scores_rows(kind, q, [0])[0][0])
+
+
+def _assert_same_topn(got, exp, scores_all=None):
+    grows, gscores = got
+    erows, escores = exp
+    assert len(grows) == len(erows)
+    # scores are exact doubles on both sides
+    assert np.array_equal(gscores, escores), (gscores, escores)
+    if not np.array_equal(grows, erows):
+        # only exact score ties may be ordered differently (the reference leaves ties unspecified)
+        for g, e, s in zip(grows, erows, escores):
+            if g != e:
+                assert scores_all is not None and scores_all[g] == s, (g, e, s)
+
+
+def test_fixed_model_endpoint_goldens():
+    g = load_golden("als_fixed_model")
+    h = ServingHarness(g["model"], lambda f, y: GpuBackend(f, y))
+    check_fixed_model_goldens(h)
+    h.backend.close()
+
+
+@pytest.mark.parametrize("n,f,how_many", [(1, 7, 3), (9, 2, 10), (1000, 50, 10), (4097, 128, 10),
+                                           (20000, 20, 5), (3000, 256, 100), (777, 300, 7), (50000, 64, 1016)])
+def test_topn_matches_oracle(n, f, how_many):
+    y = random_model(n, f, seed=n * 31 + f)
+    rng = np.random.default_rng(n + f)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        for kind in (ob.DOT, ob.COSINE):
+            for _ in range(3):
+                q = rng.standard_normal(f, dtype=np.float32)
+                exp = oracle.topn(kind, q, y, how_many)
+                got = m.topn(kind, q, how_many)
+                _assert_same_topn(got, exp, oracle.scores_all(kind, q, y))
+
+
+def test_topn_with_exclusions_and_removals():
+    n, f = 5000, 32
+    y = random_model(n, f, seed=11)
+    rng = np.random.default_rng(12)
+    q = rng.standard_normal(f, dtype=np.float32)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        full_rows, _ = oracle.topn(oracle.DOT, q, y, 20)
+        excl = np.concatenate([full_rows[:7], rng.integers(0, n, 40)]).astype(np.int32)
+        exp = oracle.topn(oracle.DOT, q, y, 10, excluded=np.unique(excl))
+        got = m.topn(ob.DOT, q, 10, excluded=excl)  # unsorted, with duplicates: the library sorts a copy
+        _assert_same_topn(got, exp)
+        # remove the current best rows: they must disappear (FeatureVectors.removeVector)
+        gone = full_rows[:5].astype(np.int32)
+        m.remove(ob.Y, gone)
+        keep = np.ones(n, dtype=bool)
+        keep[gone] = False
+        part = np.where(keep, 0, -1).astype(np.int32)
+        exp = oracle.topn(oracle.DOT, q, y, 10, part=part)
+        _assert_same_topn(m.topn(ob.DOT, q, 10), exp)
+        assert m.get(ob.Y, int(gone[0])) is None
+        # re-insert one with a new vector (setItemVector overwrite), update another in place
+        y2 = y.copy()
+        y2[gone[0]] = 10.0 * q  # becomes the clear winner
+        y2[123] = -y[123]
+        m.upsert(ob.Y, [int(gone[0]), 123], y2[[gone[0], 123]])
+        keep[gone[0]] = True
+        part = np.where(keep, 0, -1).astype(np.int32)
+        exp = oracle.topn(oracle.DOT, q, y2, 10, part=part)
+        got = m.topn(ob.DOT, q, 10)
+        _assert_same_topn(got, exp)
+        assert got[0][0] == gone[0]
+        assert np.array_equal(m.get(ob.Y, 123), y2[123])
+        st = m.stats()
+        assert st["rows"][ob.Y] == n - 4
+
+
+def test_empty_and_tiny_models():
+    with ob.Model(5) as m:
+        rows, scores = m.topn(ob.DOT, np.ones(5, np.float32), 10)
+        assert len(rows) == 0  # ALSServingModel.java:307-310 Stream.empty()
+        m.upsert(ob.Y, [3], np.ones((1, 5), np.float32))
+        rows, scores = m.topn(ob.DOT, np.ones(5, np.float32), 10)
+        assert list(rows) == [3] and list(scores) == [5.0]
+        rows, scores = m.topn(ob.DOT, np.ones(5, np.float32), 10, excluded=[3])
+        assert len(rows) == 0
+        with pytest.raises(ob.OryxError):
+            m.topn(ob.DOT, np.ones(5, np.float32), 0)
+        with pytest.raises(ob.OryxError):
+            m.topn(ob.DOT, np.ones(5, np.float32), 5000)
+
+
+def test_nan_and_ties():
+    f = 4
+    y = np.zeros((6, f), np.float32)
+    y[0] = [1, 0, 0, 0]
+    y[1] = [1, 0, 0, 0]      # exact tie with row 0
+    y[2] = [np.nan, 0, 0, 0]  # NaN score never enters (TopNConsumer.java:60)
+    y[3] = [0.5, 0, 0, 0]
+    y[4] = [0, 0, 0, 0]       # cosine: 0/0 = NaN
+    y[5] = [-1, 0, 0, 0]
+    q = np.array([1, 0, 0, 0], np.float32)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(6, dtype=np.int32), y)
+        rows, scores = m.topn(ob.DOT, q, 10)
+        assert list(scores) == [1.0, 1.0, 0.5, 0.0, -1.0]
+        assert sorted(rows[:2]) == [0, 1] and list(rows[2:]) == [3, 4, 5]
+        rows, scores = m.topn(ob.COSINE, q, 10)
+        assert list(scores) == [1.0, 1.0, 1.0, -1.0] and sorted(rows[:3]) == [0, 1, 3] and rows[3] == 5
+
+
+@pytest.mark.parametrize("rate,cores,f", [(0.5, 32, 20), (0.3, 32, 50), (0.1, 8, 128), (1.0, 8, 10), (0.5, 1, 16)])
+def test_lsh_bit_exact_and_filtered_topn(rate, cores, f):
+    h, bits = ob.lsh_plan(rate, cores)
+    assert (h, bits) == oracle.lsh_plan(rate, cores)
+    hv = random_hash_vectors(h, f, seed=h * 7 + f)
+    n = 20000
+    y = random_model(n, f, seed=3 * f)
+    rng = np.random.default_rng(f)
+    with ob.Model(f, hash_vectors=hv, max_bits_differing=bits) as m:
+        parts = m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        exp_parts = oracle.lsh_index_rows(hv, y)
+        assert np.array_equal(parts, exp_parts)  # bit-exact partition index per item
+        assert np.array_equal(m.lsh_index_rows(y[:1000]), exp_parts[:1000])
+        for _ in range(4):
+            q = rng.standard_normal(f, dtype=np.float32)
+            main = oracle.lsh_index(hv, q)
+            assert m.lsh_index(q) == main
+            cand = oracle.lsh_candidates(h, bits, main)
+            assert np.array_equal(m.lsh_candidates(q), cand)  # same list, same order
+            for kind in (ob.DOT, ob.COSINE):
+                exp = oracle.topn(kind, q, y, 10, part=exp_parts, cand=cand)
+                _assert_same_topn(m.topn(kind, q, 10), exp)
+        # compaction changes layout only
+        q = rng.standard_normal(f, dtype=np.float32)
+        before = m.topn(ob.DOT, q, 10)
+        m.compact(ob.Y)
+        after = m.topn(ob.DOT, q, 10)
+        assert np.array_equal(before[0], after[0]) and np.array_equal(before[1], after[1])
+        assert np.array_equal(m.get(ob.Y, 77), y[77])
+        # an update that changes a row's partition is honoured (ALSServingModel.java:165-176)
+        newv = -y[5]
+        p = m.upsert(ob.Y, [5], newv[None, :])
+        assert p[0] == oracle.lsh_index(hv, newv)
+
+
+def test_lsh_edge_vectors():
+    # zero vector -> index 0; candidates lists of LocalitySensitiveHashTest.java:85-139
+    L = load_golden("lsh")
+    for key in ("candidates_no_sample", "candidates_one_bit", "candidates_bands"):
+        c = L[key]
+        h, bits = ob.lsh_plan(c["sample_rate"], c["cores"])
+        hv = random_hash_vectors(h, c["features"], seed=5)
+        with ob.Model(c["features"], hash_vectors=hv, max_bits_differing=bits) as m:
+            zero = np.zeros(c["features"], np.float32)
+            one = np.ones(c["features"], np.float32)
+            assert m.lsh_index(zero) == 0
+            for v in (zero, one):
+                exp = oracle.lsh_candidates(h, bits, oracle.lsh_index(hv, v))
+                assert np.array_equal(m.lsh_candidates(v), exp)
+            if key == "candidates_bands":
+                cand = m.lsh_candidates(one)
+                assert len(cand) == c["count"]
+                for lo, hi, b in c["bands"]:
+                    assert all(bin(int(cand[0]) ^ int(cand[i])).count("1") == b for i in range(lo, hi))
+
+
+def test_scores_all_and_rows_exact():
+    n, f = 3000, 77
+    y = random_model(n, f, seed=21)
+    q = np.random.default_rng(22).standard_normal(f, dtype=np.float32)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        m.remove(ob.Y, [10])
+        for kind in (ob.DOT, ob.COSINE):
+            got = m.scores_all(kind, q, n + 5)
+            exp = oracle.scores_all(kind, q, y)
+            assert np.isnan(got[10]) and np.all(np.isnan(got[n:]))
+            mask = np.ones(n, bool)
+            mask[10] = False
+            assert np.array_equal(got[:n][mask], exp[mask])
+        rows = [0, 5, 10, 2999, 5000]
+        got, found = m.scores_rows(ob.DOT, q, rows)
+        assert list(found) == [True, True, False, True, False]
+        assert got[0] == oracle.dot(q, y[0]) and got[3] == oracle.dot(q, y[2999]) and got[2] == 0.0
+        got, _ = m.scores_rows(ob.COSINE, q, [7])
+        assert got[0] == oracle.dot(q, y[7]) / (oracle.norm(q) * oracle.norm(y[7]))
+
+
+@pytest.mark.parametrize("n,f", [(3, 3), (2, 3), (1000, 50), (5000, 128), (700, 256), (100, 70)])
+def test_gram_matches_oracle(n, f):
+    y = random_model(n, f, seed=n + f)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        g, used = m.gram(ob.Y)
+        exp = oracle.transpose_times_self(y)
+        assert used == n
+        # same products, same binary64 adds, different row order only
+        assert np.max(np.abs(g - exp)) <= 1e-12 * max(1.0, np.max(np.abs(exp)))
+        m.upsert(ob.X, np.arange(5, dtype=np.int32), y[:5])
+        gx, used = m.gram(ob.X)
+        assert used == 5 and np.max(np.abs(gx - oracle.transpose_times_self(y[:5]))) <= 1e-12 * np.max(np.abs(exp))
+    with ob.Model(f) as m:
+        g, used = m.gram(ob.Y)
+        assert g is None and used == 0  # VectorMath.java:65-67 null for empty
+
+
+def test_gram_goldens():
+    for c in load_golden("math")["transpose_times_self"]:
+        rows = np.asarray(c["rows"], dtype=np.float32)
+        with ob.Model(rows.shape[1]) as m:
+            m.upsert(ob.Y, np.arange(len(rows), dtype=np.int32), rows)
+            g, _ = m.gram(ob.Y)
+            assert np.max(np.abs(g - np.asarray(c["value"]))) <= max(c["tol"], 1e-15), c["_cite"]
+
+
+def test_solver_goldens_and_random():
+    M = load_golden("math")["solver"]
+    s = M["solve_f2f"]
+    x = ob.Solver(s["a"]).solve_f2f(s["b"])
+    assert np.array_equal(x, np.asarray(s["x"], dtype=np.float32)), x
+    for c in M["non_singular"]:
+        try:
+            ob.Solver(c["a"])
+            ok = True
+        except ob.SingularMatrixSolverException:
+            ok = False
+        assert ok == c["value"], c["_cite"]
+    for c in M["apparent_rank"]:
+        with pytest.raises(ob.SingularMatrixSolverException) as ei:
+            ob.Solver(c["a"])
+        assert ei.value.apparent_rank == c["rank"], c["_cite"]
+    rng = np.random.default_rng(4)
+    for f in (2, 17, 64, 128, 256):
+        y = rng.standard_normal((4 * f + 10, f), dtype=np.float32)
+        g = oracle.transpose_times_self(y)
+        so, sg = oracle.Solver(g), ob.Solver(g)
+        for _ in range(3):
+            b = rng.standard_normal(f, dtype=np.float32)
+            xo, xg = so.solve_f2f(b), sg.solve_f2f(b)
+            # binary64 inside, narrowed to float: at most a last-place difference
+            assert np.max(np.abs(xo - xg)) <= 2e-7 * np.max(np.abs(xo))
+
+
+def test_fold_in_goldens_and_random():
+    u = load_golden("math")["updated_xu"]
+    g = oracle.transpose_times_self(np.asarray(u["rows"], dtype=np.float32))
+    sg = ob.Solver(g)
+    for c in u["cases"]:
+        if c["yi"] is None:
+            continue
+        xu = None if c["xu"] is None else np.asarray(c["xu"], np.float32)[None, :]
+        has = None if xu is not None else np.zeros(1, np.uint8)
+        out, valid = sg.fold_in_batch(c["implicit"], xu, has, np.asarray(c["yi"], np.float32)[None, :], [c["value"]])
+        assert valid[0] == 1 and np.array_equal(out[0], np.asarray(c["out"], np.float32)), (out, c)
+    # speed-layer goldens (ALSSpeedIT.java:80-113)
+    s = load_golden("speed")
+    X = {k: np.asarray(v, np.float32) for k, v in s["X"].items()}
+    Y = {k: np.asarray(v, np.float32) for k, v in s["Y"].items()}
+    yty = ob.Solver(oracle.transpose_times_self(np.stack(list(Y.values()))))
+    xtx = ob.Solver(oracle.transpose_times_self(np.stack(list(X.values()))))
+    for user, item, value in s["interactions"]:
+        if user in s["expected_X"]:
+            out, valid = yty.fold_in_batch(True, None, np.zeros(1, np.uint8), Y[item][None, :], [value])
+            assert valid[0] and np.max(np.abs(out[0] - np.asarray(s["expected_X"][user], np.float32))) <= s["tol"]
+        else:
+            out, valid = xtx.fold_in_batch(True, None, np.zeros(1, np.uint8), X[user][None, :], [value])
+            assert valid[0] and np.max(np.abs(out[0] - np.asarray(s["expected_Y"][item], np.float32))) <= s["tol"]
+    # random batch, implicit and explicit, mixed null Xu, values that yield "no change"
+    rng = np.random.default_rng(9)
+    for f in (8, 50, 128):
+        n = 1000
+        ymat = rng.standard_normal((3000, f), dtype=np.float32) * 0.3
+        gram = oracle.transpose_times_self(ymat)
+        so, sgpu = oracle.Solver(gram), ob.Solver(gram)
+        xu = rng.standard_normal((n, f), dtype=np.float32) * 0.3
+        yi = ymat[rng.integers(0, 3000, n)]
+        has = (rng.random(n) < 0.7).astype(np.uint8)
+        vals = rng.choice([1.0, 2.5, -1.0, 0.0, 0.5, -0.3], n)
+        for implicit in (True, False):
+            eo, ev = oracle.fold_in_batch(so, implicit, xu, has, yi, vals)
+            go, gv = sgpu.fold_in_batch(implicit, xu, has, yi, vals)
+            assert np.array_equal(ev, gv)
+            ok = ev.astype(bool)
+            scale = np.maximum(np.abs(eo[ok]).max(axis=1, keepdims=True), 1e-6)
+            assert np.max(np.abs(eo[ok] - go[ok]) / scale) <= 5e-7
