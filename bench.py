@@ -195,7 +195,7 @@ def run_reference(args):
     for i in range(args.steps):
         oracle.topn_mt(oracle.DOT, q[i % N_QUERIES], y, HOW_MANY, threads)
     dt = (time.perf_counter() - t0) * scale
-    qps = args.steps / dt
+    qps = args.steps / dt * (n_items / ITEMS_PER_GPU)   # in 10M-item scans per second
     sample = (f"every step = one full top-{HOW_MANY} query over {sample_rows} x {args.features} rows"
               + ("" if sample_rows == n_items else f", time scaled x{scale:.2f} to {n_items} rows (linear in items)"))
     line = {
