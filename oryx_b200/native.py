@@ -15,6 +15,7 @@ OK, E_INVALID, E_CUDA, E_SINGULAR, E_NOMEM, E_UNSUPPORTED = 0, 1, 2, 3, 4, 5
 DOT, COSINE = 0, 1
 X, Y = 0, 1
 MAX_HOW_MANY = 1016
+STATIC_MAX_HOW_MANY = 56
 
 
 class OryxError(RuntimeError):
@@ -73,6 +74,7 @@ SIGNATURES = {
     "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
     "oryx_scores_rows": [C.c_void_p, C.c_int32, _f32p, _i32p, C.c_int32, _f64p, _u8p],
     "oryx_topn_device": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_topn_device_static": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
@@ -255,6 +257,13 @@ class Model:
     def topn_device(self, kind: int, d_query: int, how_many: int, d_rows: int, d_scores: int, d_n: int, stream: int):
         _check(lib().oryx_topn_device(self._h, kind, C.c_void_p(d_query), how_many, C.c_void_p(d_rows),
                                       C.c_void_p(d_scores), C.c_void_p(d_n), C.c_void_p(stream)))
+
+    def topn_device_static(self, kind: int, d_query: int, how_many: int, d_rows: int, d_scores: int, d_n: int,
+                           stream: int):
+        """oryx_topn_device_static: same query as topn_device, scratch in the module's fixed array, no
+        allocation.  how_many <= STATIC_MAX_HOW_MANY; calls that overlap on one GPU race."""
+        _check(lib().oryx_topn_device_static(self._h, kind, C.c_void_p(d_query), how_many, C.c_void_p(d_rows),
+                                             C.c_void_p(d_scores), C.c_void_p(d_n), C.c_void_p(stream)))
 
     def gram(self, which: int = Y):
         out = np.zeros((self.features, self.features), dtype=np.float64)
