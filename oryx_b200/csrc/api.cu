@@ -25,7 +25,7 @@ void ctx_destroy(QueryCtx* c) {
   if (c->stream) cudaStreamDestroy(c->stream);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
-  cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_counter);
+  cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter);
   cudaFree(c->d_main_index); cudaFree(c->d_out_rows); cudaFree(c->d_out_scores); cudaFree(c->d_out_n);
   cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_rows);
   cudaFreeHost(c->h_out_scores); cudaFreeHost(c->h_out_n);
@@ -39,9 +39,11 @@ static int32_t ctx_create(Model* m, QueryCtx* c) {
   ORYX_CUDA(cudaMalloc(&c->d_query, (size_t)fpad * sizeof(float)));
   c->excl_cap = 4096;
   ORYX_CUDA(cudaMalloc(&c->d_excl, (size_t)c->excl_cap * sizeof(int32_t)));
-  ORYX_CUDA(cudaMalloc(&c->d_cand, (size_t)kMaxGrid * kMaxK * sizeof(uint2)));
-  ORYX_CUDA(cudaMalloc(&c->d_counter, sizeof(unsigned int)));
-  ORYX_CUDA(cudaMemset(c->d_counter, 0, sizeof(unsigned int)));
+  c->scratch_sets = 2;
+  ORYX_CUDA(cudaMalloc(&c->d_cand, (size_t)2 * kMaxGrid * kMaxK * sizeof(uint2)));
+  ORYX_CUDA(cudaMalloc(&c->d_list_max, (size_t)2 * kMaxGrid * sizeof(uint32_t)));
+  ORYX_CUDA(cudaMalloc(&c->d_counter, 32 * sizeof(unsigned int)));
+  ORYX_CUDA(cudaMemset(c->d_counter, 0, 32 * sizeof(unsigned int)));
   ORYX_CUDA(cudaMalloc(&c->d_main_index, sizeof(int32_t)));
   ORYX_CUDA(cudaMemset(c->d_main_index, 0, sizeof(int32_t)));
   ORYX_CUDA(cudaMalloc(&c->d_out_rows, (size_t)kMaxK * sizeof(int32_t)));
@@ -121,18 +123,26 @@ static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query,
   std::memcpy(c->h_query, query, (size_t)F * sizeof(float));
   for (int j = F; j < fpad; j++) c->h_query[j] = 0.0f;
   ORYX_CUDA(cudaMemcpyAsync(c->d_query, c->h_query, (size_t)fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  int32_t n_excl_slots = 0;
   if (n_excluded > 0) {
+    // The allowed-predicate arrives as row ids; the kernel filters by slot, so translate here (the
+    // caller holds the model's shared lock, row2slot is stable) and sort for the binary search.
     ORYX_TRY(ensure_excl(c, n_excluded));
-    std::memcpy(c->h_excl, excluded_rows, (size_t)n_excluded * sizeof(int32_t));
-    std::sort(c->h_excl, c->h_excl + n_excluded);
-    ORYX_CUDA(cudaMemcpyAsync(c->d_excl, c->h_excl, (size_t)n_excluded * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    for (int32_t i = 0; i < n_excluded; i++) {
+      int32_t r = excluded_rows[i];
+      if (r >= 0 && (size_t)r < s->row2slot.size() && s->row2slot[r] >= 0) c->h_excl[n_excl_slots++] = s->row2slot[r];
+    }
+    std::sort(c->h_excl, c->h_excl + n_excl_slots);
+    if (n_excl_slots > 0) {
+      ORYX_CUDA(cudaMemcpyAsync(c->d_excl, c->h_excl, (size_t)n_excl_slots * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    }
   }
   TopnRequest rq{};
   rq.kind = kind;
   rq.d_query = c->d_query;
   rq.how_many = how_many;
   rq.d_excl = c->d_excl;
-  rq.n_excl = n_excluded;
+  rq.n_excl = n_excl_slots;
   rq.d_out_rows = c->d_out_rows;
   rq.d_out_scores = c->d_out_scores;
   rq.d_out_n = c->d_out_n;
@@ -546,6 +556,26 @@ int32_t oryx_merge_topn_device(const double* d_scores, const int32_t* d_rows, co
   ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
   return merge_topn_launch(d_scores, d_rows, d_n, n_lists, how_many, row_stride, d_out_rows, d_out_scores,
                            d_out_n, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// Development aid (not part of the public header): arm == 1 allocates/re-arms the timestamp buffer the
+// scan kernel fills; arm == 0 synchronises and copies out 8 globaltimer values (ns):
+// [0] earliest CTA start, [1]/[2] earliest/latest end of a CTA's scan, [3] merge start,
+// [4] selection done, [5] exact re-score done, [6] merge end.
+int32_t oryx_debug_scan_timestamps(oryx_model* mh, int32_t arm, unsigned long long* out) {
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  if (arm) {
+    if (!m->d_debug_ts) ORYX_CUDA(cudaMalloc(&m->d_debug_ts, 8 * sizeof(unsigned long long)));
+    unsigned long long init[8] = {~0ull, ~0ull, 0, 0, 0, 0, 0, 0};
+    ORYX_CUDA(cudaDeviceSynchronize());
+    ORYX_CUDA(cudaMemcpy(m->d_debug_ts, init, sizeof(init), cudaMemcpyHostToDevice));
+    return ORYX_OK;
+  }
+  ORYX_ARG(out && m->d_debug_ts, "not armed");
+  ORYX_CUDA(cudaDeviceSynchronize());
+  ORYX_CUDA(cudaMemcpy(out, m->d_debug_ts, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return ORYX_OK;
 }
 
 int32_t oryx_stats_get(oryx_model* mh, oryx_stats* out) {

@@ -84,7 +84,7 @@ __device__ __forceinline__ double exact_step(double acc, float a, float b) {
 //             16-byte aligned and can be read with 128-bit loads; padding floats are zero.
 //   slot_row  [cap_slots] int32: caller's row id living in the slot, -1 = empty / tombstone.
 //   slot_part [cap_slots] int32: LSH partition of the row (0 when the store is not hashed), -1 = empty.
-// The host keeps row -> slot and a free list; removed slots are zero-filled and reused.
+// The host keeps row -> slot and a free list; removed slots (tombstones) are NaN-filled and reused.
 struct Store {
   int features = 0;
   int fpad = 0;
@@ -111,8 +111,13 @@ struct QueryCtx {
   float* d_query = nullptr;       // [fpad]
   int32_t* d_excl = nullptr;      // [excl_cap]
   int32_t excl_cap = 0;
-  uint2* d_cand = nullptr;        // scratch: [max_grid x max_k] (key, slot)
-  unsigned int* d_counter = nullptr;
+  // Scan scratch.  When `scratch_sets` == 2 the launcher alternates between two sets so the finishing
+  // kernel of one query can overlap the scan of the next (programmatic dependent launch).
+  uint2* d_cand = nullptr;        // [scratch_sets x max_grid x max_k] (key, slot)
+  uint32_t* d_list_max = nullptr; // [scratch_sets x max_grid] best key of each CTA's list
+  unsigned int* d_counter = nullptr;  // [scratch_sets x 16] dynamic tile counters (64 B apart)
+  int scratch_sets = 1;
+  int flip = 0;
   int32_t* d_main_index = nullptr;
   int32_t* d_out_rows = nullptr;  // [max_k]
   double* d_out_scores = nullptr; // [max_k]
@@ -144,6 +149,7 @@ struct Model {
   std::vector<QueryCtx*> pool_free;
   std::vector<std::unique_ptr<QueryCtx>> pool_all;
   int pool_limit = 8;
+  unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
 
   std::atomic<int64_t> queries{0};
@@ -178,7 +184,7 @@ struct TopnRequest {
   int kind;
   const float* d_query;  // [fpad] device
   int how_many;
-  const int32_t* d_excl;  // sorted row ids, device
+  const int32_t* d_excl;  // sorted SLOT ids, device
   int n_excl;
   int32_t* d_out_rows;
   double* d_out_scores;

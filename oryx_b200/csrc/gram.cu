@@ -8,7 +8,7 @@
 // a binary64 entry, for every row v.  gram_exact_kernel performs exactly those operations
 // (__fmul_rn, widen, __dadd_rn); only the order in which rows are summed differs (the reference's
 // own order is hash-map iteration order, i.e. unspecified), so entries agree to ~1e-16 relative.
-// Tombstoned slots are zero-filled by the store and contribute exact zeros.
+// Tombstoned slots (NaN-filled by the store) are skipped via slot_row.
 #include <algorithm>
 
 #include "common.cuh"
@@ -21,7 +21,8 @@ constexpr int kTile = 64;   // output block is kTile x kTile
 constexpr int kKC = 32;     // rows staged per step
 
 // grid.x = upper-triangular block index, grid.y = row chunk.
-__global__ void __launch_bounds__(256) gram_exact_kernel(const float* __restrict__ vec, int64_t n_slots,
+__global__ void __launch_bounds__(256) gram_exact_kernel(const float* __restrict__ vec,
+                                                        const int32_t* __restrict__ slot_row, int64_t n_slots,
                                                         int fpad, int features, int nb,
                                                         int64_t rows_per_chunk, double* __restrict__ out) {
   __shared__ __align__(16) float As[kKC][kTile];
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(256) gram_exact_kernel(const float* __restrict
       int k = e / kTile, c = e - k * kTile;
       int64_t row = r0 + k;
       int ca = bi * kTile + c, cb = bj * kTile + c;
-      bool ok = row < row_end;
+      bool ok = row < row_end && slot_row[row] >= 0;  // tombstones are NaN-filled: skip them
       As[k][c] = (ok && ca < features) ? vec[row * fpad + ca] : 0.0f;
       Bs[k][c] = (ok && cb < features) ? vec[row * fpad + cb] : 0.0f;
     }
@@ -94,7 +95,7 @@ int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream) {
   rows_per_chunk = (rows_per_chunk + kKC - 1) / kKC * kKC;
   chunks = (s->n_slots + rows_per_chunk - 1) / rows_per_chunk;
   dim3 grid((unsigned)n_blocks, (unsigned)chunks);
-  gram_exact_kernel<<<grid, 256, 0, stream>>>(s->d_vec, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
+  gram_exact_kernel<<<grid, 256, 0, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;

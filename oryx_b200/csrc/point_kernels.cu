@@ -1,0 +1,150 @@
+// point_kernels.cu -- the small exact-arithmetic kernels around the scan: scores of every row (the
+// arbitrary-Rescorer path, TopNConsumer.java:56-58), scores of a handful of rows (Estimate /
+// SimilarityToItem / Because / MostSurprising point lookups, kernel K10) and the cross-shard merge of
+// per-GPU top-N lists (ALSServingModel.java:334 when Y is row-sharded over several GPUs).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace oryx {
+
+namespace {
+
+// One thread per slot, exact arithmetic, result scattered to out[row].
+__global__ void scores_all_kernel(const float* __restrict__ y, const int32_t* __restrict__ slot_row,
+                                  int64_t n_slots, int fpad, int features, const float* __restrict__ q,
+                                  int kind, int32_t n_rows, double* __restrict__ out) {
+  extern __shared__ float s_tile[];  // [blockDim.x x (features+1)]
+  const int ld = features + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < n_slots; base += (int64_t)gridDim.x * blockDim.x) {
+    __syncthreads();
+    for (int r = warp; r < (int)blockDim.x; r += nwarps) {
+      int64_t slot = base + r;
+      if (slot < n_slots) {
+        const float* src = y + slot * fpad;
+        for (int j = lane; j < features; j += 32) s_tile[r * ld + j] = src[j];
+      }
+    }
+    __syncthreads();
+    int64_t slot = base + threadIdx.x;
+    if (slot < n_slots) {
+      int32_t row = slot_row[slot];
+      if (row >= 0 && row < n_rows) {
+        const float* v = s_tile + threadIdx.x * ld;
+        double dot = 0.0, tot = 0.0;
+        for (int j = 0; j < features; j++) {
+          float yv = v[j];
+          dot = exact_step(dot, __ldg(q + j), yv);
+          if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+        }
+        out[row] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
+      }
+    }
+  }
+}
+
+// Point lookups (kernel K10): one thread per requested slot, exact arithmetic.
+__global__ void scores_rows_kernel(const float* __restrict__ y, int fpad, int features,
+                                   const float* __restrict__ q, int kind, const int32_t* __restrict__ slots,
+                                   int n, double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int32_t slot = slots[i];
+  if (slot < 0) { out[i] = 0.0; return; }
+  const float* v = y + (int64_t)slot * fpad;
+  double dot = 0.0, tot = 0.0, qq = 0.0;
+  for (int j = 0; j < features; j++) {
+    float yv = v[j], qv = q[j];
+    dot = exact_step(dot, qv, yv);
+    if (kind == ORYX_COSINE) { tot = exact_step(tot, yv, yv); qq = exact_step(qq, qv, qv); }
+  }
+  // SimilarityToItem.java:62-63: dot / (toItemNorm * norm(item))
+  out[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dmul_rn(__dsqrt_rn(qq), __dsqrt_rn(tot))) : dot;
+}
+
+// Cross-shard merge (kernel K7, multi-GPU leg): rank-sort of n_lists*how_many exact (score,row) pairs
+// by (score desc, global row asc) in one CTA.
+__global__ void merge_topn_kernel(const double* __restrict__ scores, const int32_t* __restrict__ rows,
+                                  const int32_t* __restrict__ counts, int n_lists, int how_many,
+                                  int64_t row_stride, int64_t* __restrict__ out_rows,
+                                  double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
+  const int total = n_lists * how_many;
+  int valid_total = 0;
+  for (int l = 0; l < n_lists; l++) valid_total += min(max(counts[l], 0), how_many);
+  const int n_out = min(valid_total, how_many);
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int li = i / how_many, pi = i - li * how_many;
+    if (pi >= counts[li]) continue;
+    const double si = scores[i];
+    const int64_t ri = (int64_t)li * row_stride + rows[i];
+    int rank = 0;
+    for (int j = 0; j < total; j++) {
+      const int lj = j / how_many, pj = j - lj * how_many;
+      if (pj >= counts[lj]) continue;
+      const double sj = scores[j];
+      const int64_t rj = (int64_t)lj * row_stride + rows[j];
+      rank += ((sj > si) || (sj == si && rj < ri)) ? 1 : 0;
+    }
+    if (rank < n_out) { out_rows[rank] = ri; out_scores[rank] = si; }
+  }
+  if (threadIdx.x == 0) *out_n = n_out;
+}
+
+__global__ void fill_nan_kernel(double* p, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = __longlong_as_double(0x7ff8000000000000LL);
+}
+
+}  // namespace
+
+int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_rows, double* d_out,
+                          cudaStream_t stream) {
+  Store* s = &m->store[ORYX_Y];
+  int threads = 256;
+  if (n_rows > 0) {
+    fill_nan_kernel<<<(n_rows + threads - 1) / threads, threads, 0, stream>>>(d_out, n_rows);
+    m->launches++;
+  }
+  if (s->n_slots == 0 || n_rows <= 0) return ORYX_OK;
+  int tile = 128;
+  while (tile > 32 && (size_t)tile * (s->features + 1) * sizeof(float) > 200 * 1024) tile -= 32;
+  size_t smem = (size_t)tile * (s->features + 1) * sizeof(float);
+  if (smem > 200 * 1024) {
+    set_error("features=%d too large for the exact scoring kernel", s->features);
+    return ORYX_E_UNSUPPORTED;
+  }
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    ORYX_CUDA(cudaFuncSetAttribute(scores_all_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  int64_t tiles = (s->n_slots + tile - 1) / tile;
+  int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
+  scores_all_kernel<<<grid, tile, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, s->features,
+                                                  d_query, kind, n_rows, d_out);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32_t* d_slots, int n,
+                           double* d_out, cudaStream_t stream) {
+  Store* s = &m->store[ORYX_Y];
+  scores_rows_kernel<<<(n + 127) / 128, 128, 0, stream>>>(s->d_vec, s->fpad, s->features, d_query, kind,
+                                                         d_slots, n, d_out);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists,
+                          int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
+                          int32_t* d_out_n, cudaStream_t stream) {
+  merge_topn_kernel<<<1, 256, 0, stream>>>(d_scores, d_rows, d_n, n_lists, how_many, row_stride, d_out_rows,
+                                           d_out_scores, d_out_n);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+}  // namespace oryx

@@ -1,5 +1,6 @@
-// scan_topn.cu -- single-query scoring scan with a fused per-CTA top-N heap (kernels K1/K2/K7 of
-// SURVEY.md section 2.3).
+// scan_topn.cu -- single-query scoring scan with a fused per-CTA top-N candidate list, and the
+// finishing kernel that merges the lists and re-scores exactly (kernels K1/K2/K6/K7 of SURVEY.md
+// section 2.3).
 //
 // Replaces the hot loop of ALSServingModel.topN (reference: app/oryx-app-serving/src/main/java/com/
 // cloudera/oryx/app/serving/als/model/ALSServingModel.java:289-335): per candidate partition a
@@ -7,24 +8,31 @@
 // CosineAverageFunction (VectorMath.dot, VectorMath.java:38-45) and keeps the howMany best; the
 // per-partition lists are concatenated, sorted descending and cut (ALSServingModel.java:329-334).
 //
-// Device algorithm (one launch per query):
-//   1. scan     -- HBM-bound.  A group of G lanes owns one row and reads it with coalesced 128-bit
-//                  streaming loads; fp32 FMA partial sums are combined with xor-shuffles.  Rows of
-//                  non-candidate LSH partitions are skipped before their loads are issued
-//                  (candidate(p) <=> popcount(p ^ mainIndex) <= maxBitsDiffering, which is exactly
-//                  the set LocalitySensitiveHash.getCandidateIndices enumerates).
-//   2. per-CTA heap -- scores above the CTA's current k-th best (k = howMany + 8) take a rare slow
-//                  path: the allowed-predicate (row is live, not in the exclusion list) is tested and
-//                  the row is pushed into a shared-memory binary min-heap under a CTA-local lock.
-//                  Strict '>' admission, NaN never enters (TopNConsumer.java:60-64).
-//   3. merge    -- every CTA publishes its heap to global scratch; the last CTA to finish (atomic
-//                  ticket) radix-selects the k best of all lists,
-//   4. finish   -- re-scores those k rows with the reference's exact arithmetic (binary32 product,
-//                  binary64 accumulate, index order; cosine adds the exact norm and a binary64
-//                  sqrt/divide), sorts by (exact score desc, row asc) and writes howMany results.
+// Device algorithm (two launches per query):
+//   scan_topn_kernel -- HBM-bound.
+//     * A group of G lanes owns one row and reads it with coalesced 128-bit streaming loads; fp32
+//       FMA partial sums are combined with a transposed xor-shuffle reduction.  Rows of non-candidate
+//       LSH partitions are skipped before their loads are issued (candidate(p) <=>
+//       popcount(p ^ mainIndex) <= maxBitsDiffering, exactly the set
+//       LocalitySensitiveHash.getCandidateIndices enumerates).
+//     * Work distribution: SMs do not stream at the same speed (distance to the memory partitions),
+//       and a static split left the fastest CTAs idle for the last ~20 % of the launch.  Three
+//       quarters of the tiles are therefore assigned statically (interleaved by warp), the rest is
+//       handed out in small chunks from a global counter that each warp fetches one chunk ahead.
+//     * Scores above the CTA's current k-th best (k = howMany + 8) take a rare slow path: the
+//       allowed-predicate (slot not in the exclusion list) and a lock-free replace-the-minimum in a
+//       shared-memory candidate array.  Strict '>' admission, NaN never enters
+//       (TopNConsumer.java:60-64); tombstoned slots are NaN-filled so they never qualify.
+//     * Each CTA publishes its k candidates (order-preserving key, slot) to global scratch.
+//   topn_finish_kernel -- one 1024-thread CTA.
+//     * Selects the k best of all lists (for k <= 32: the k-th largest list maximum prunes all but
+//       ~k lists, the survivors are rank-sorted in shared memory; otherwise a radix select), re-scores those k rows with the reference's exact arithmetic (binary32 product,
+//       binary64 accumulate, index order; cosine adds the exact norm and a binary64 sqrt/divide),
+//       ranks by (exact score desc, row asc) and writes howMany results.
 // Returned scores are therefore bit-identical to the Java path's; the fp32 scan only decides
 // which k rows get re-scored.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -32,122 +40,415 @@ namespace oryx {
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kScanThreads = 256;
+constexpr int kFinishThreads = 1024;
+constexpr int kDynChunkMax = 16;       // largest guided chunk, in tiles
+constexpr int kExclSmemMax = 4096;     // exclusion entries staged in shared memory (16 KB)
+constexpr int kRowStageFloats = 16384; // floats of row staging in the finishing CTA (64 KB)
 
 struct ScanParams {
   const float4* y;
   const int32_t* slot_row;
   const int32_t* slot_part;
   const float* q;  // [fpad]
-  const int32_t* excl;
+  const int32_t* excl;  // sorted SLOT ids the allowed-predicate rejects
   int n_excl;
+  int excl_in_smem;     // the list was small enough to stage in shared memory
   int64_t n_slots;
   int features;
   int f4;  // fpad / 4
-  int k;   // heap size = how_many + margin
+  int k;   // candidates per list = how_many + margin
   int how_many;
   int max_bits;
   const int32_t* main_index;
-  uint2* cand;  // scratch [gridDim.x x k]
-  unsigned int* counter;
+  uint2* cand;            // scratch [n_lists x k]
+  uint32_t* list_max;     // scratch [n_lists]: largest key of each published list (0 = empty list)
+  unsigned int* counter;  // dynamic tile counter; zero at launch, reset by the finishing kernel
   int32_t* out_rows;
   double* out_scores;
   int32_t* out_n;
+  unsigned long long* debug_ts;  // optional [8] timestamps (ns): see oryx_debug_scan_timestamps
 };
 
-struct HeapView {
-  float* score;
-  int32_t* slot;
-};
+// Programmatic dependent launch: let the next kernel in the stream start / wait for the previous one.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait_primary() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
-__device__ __forceinline__ void heap_sift_up(HeapView h, int i) {
-  float s = h.score[i];
-  int v = h.slot[i];
-  while (i > 0) {
-    int p = (i - 1) >> 1;
-    if (!(s < h.score[p])) break;
-    h.score[i] = h.score[p];
-    h.slot[i] = h.slot[p];
-    i = p;
-  }
-  h.score[i] = s;
-  h.slot[i] = v;
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
 }
 
-__device__ __forceinline__ void heap_replace_root(HeapView h, int n, float s, int v) {
-  int i = 0;
-  int half = n >> 1;
-  while (i < half) {
-    int c = 2 * i + 1;
-    if (c + 1 < n && h.score[c + 1] < h.score[c]) c++;
-    if (!(h.score[c] < s)) break;
-    h.score[i] = h.score[c];
-    h.slot[i] = h.slot[c];
-    i = c;
-  }
-  h.score[i] = s;
-  h.slot[i] = v;
-}
-
-__device__ __forceinline__ bool excluded(const int32_t* excl, int n, int32_t row) {
+__device__ __forceinline__ bool excluded(const int32_t* excl, int n, int32_t slot) {
   int lo = 0, hi = n - 1;
   while (lo <= hi) {
     int mid = (lo + hi) >> 1;
-    int32_t v = __ldg(excl + mid);
-    if (v == row) return true;
-    if (v < row) lo = mid + 1; else hi = mid - 1;
+    int32_t v = excl[mid];
+    if (v == slot) return true;
+    if (v < slot) lo = mid + 1; else hi = mid - 1;
   }
   return false;
 }
 
-// Slow path, executed by one lane of a warp for one qualifying row.
-__device__ __noinline__ void heap_offer(const ScanParams& p, HeapView h, int* s_cnt, int* s_lock,
-                                        volatile float* s_thr, float score, int32_t slot) {
-  // TopNConsumer.java:57 allowedPredicate: the slot must hold a live row that is not excluded.
-  int32_t row = __ldg(p.slot_row + slot);
-  if (row < 0) return;
-  if (p.n_excl > 0 && excluded(p.excl, p.n_excl, row)) return;
-  while (atomicCAS(s_lock, 0, 1) != 0) {
+// ------------------------------------------------------------------------------------------------
+// The CTA's candidate list: k packed words (score key << 32 | slot) in shared memory, unordered,
+// all starting as the empty sentinel 0.  An offer replaces the current minimum if the new score is
+// strictly greater (TopNConsumer.java:60-64: strict '>', so equal scores never displace), using a
+// 64-bit compare-and-swap -- no lock, so the warps of a CTA never queue behind one another, and the
+// whole warp takes part in the search for the minimum.  The published threshold only ever rises
+// (atomicMax on the key); a stale, lower value merely causes a redundant offer.
+//
+// This slow path runs for ~k*ln(rows per CTA / k) rows per CTA and touches shared memory only: the
+// memory system is saturated by the scan, so one dependent global load here would stall the warp
+// for microseconds.
+__device__ __forceinline__ void warp_min_entry(const unsigned long long* arr, int k, int lane,
+                                               unsigned long long& best, int& best_idx) {
+  best = ~0ull;
+  best_idx = 0;
+  for (int i = lane; i < k; i += 32) {
+    unsigned long long v = *(const volatile unsigned long long*)(arr + i);
+    if (v < best) { best = v; best_idx = i; }
   }
-  __threadfence_block();
-  int n = *(volatile int*)s_cnt;
-  if (n < p.k) {
-    h.score[n] = score;
-    h.slot[n] = slot;
-    heap_sift_up(h, n);
-    n++;
-    *(volatile int*)s_cnt = n;
-    if (n == p.k) *s_thr = h.score[0];
-  } else if (score > h.score[0]) {  // re-check against the live minimum (TopNConsumer.java:63)
-    heap_replace_root(h, n, score, slot);
-    *s_thr = h.score[0];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
+    int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+    if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
   }
-  __threadfence_block();
-  atomicExch(s_lock, 0);
 }
 
-// ---- the last CTA's work: select, exact re-score, order, write.
-__device__ void final_merge(const ScanParams& p, int kind, unsigned char* smem_raw, int n_lists) {
+__device__ __noinline__ void warp_offer(const ScanParams& p, unsigned long long* arr, const int32_t* s_excl,
+                                        unsigned int* s_thr_key, uint32_t key, int32_t slot, int lane) {
+  // TopNConsumer.java:57 allowedPredicate: the row must not be in the exclusion list.  Excluded rows
+  // are translated to slots by the host, so the test needs no slot -> row lookup.
+  if (p.n_excl > 0 && excluded(s_excl, p.n_excl, slot)) return;
+  const unsigned long long x = ((unsigned long long)key << 32) | (unsigned long long)(uint32_t)slot;
+  unsigned long long best;
+  int best_idx;
+  for (;;) {
+    warp_min_entry(arr, p.k, lane, best, best_idx);
+    if (key <= (uint32_t)(best >> 32)) {  // not strictly above the current minimum: rejected
+      if (lane == 0) atomicMax(s_thr_key, (uint32_t)(best >> 32));
+      return;
+    }
+    unsigned long long old = 0ull;
+    if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
+    old = __shfl_sync(0xffffffffu, old, 0);
+    if (old == best) break;  // replaced the minimum; otherwise another warp got there first: retry
+  }
+  warp_min_entry(arr, p.k, lane, best, best_idx);
+  if (lane == 0) atomicMax(s_thr_key, (uint32_t)(best >> 32));
+}
+
+// Scores of one warp tile.  G lanes share a row, each lane holds NV float4 of U rows (rows
+// row0 + u*RPI).  `vals` are per-lane partial sums; the reduction is "transposed": log2(U) exchange
+// steps hand each lane one row to own while halving the lanes per row, then log2(G/U) plain xor
+// steps finish -- log2(G) shuffles for U rows instead of U*log2(G).  On return lane gl < U holds
+// the total of row u = owned_row<U>(gl) in vals[0].
+template <int G, int U>
+__device__ __forceinline__ void reduce_rows(float (&vals)[U], int gl) {
+  static_assert(U <= G, "rows per group must not exceed lanes per group");
+  int bit = 1;
+#pragma unroll
+  for (int half = U / 2; half >= 1; half /= 2) {
+    const bool upper = (gl & bit) != 0;
+#pragma unroll
+    for (int j = 0; j < half; j++) {
+      const float keep = upper ? vals[j + half] : vals[j];
+      const float send = upper ? vals[j] : vals[j + half];
+      vals[j] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+    bit <<= 1;
+  }
+#pragma unroll
+  for (int o = U; o < G; o <<= 1) vals[0] += __shfl_xor_sync(0xffffffffu, vals[0], o);
+}
+
+// Which of the U rows of its group lane `gl` (< U) owns after reduce_rows.
+template <int U>
+__device__ __forceinline__ int owned_row(int gl) {
+  int u = 0, bit = 1;
+#pragma unroll
+  for (int half = U / 2; half >= 1; half /= 2) {
+    if (gl & bit) u += half;
+    bit <<= 1;
+  }
+  return u;
+}
+
+// G lanes per row, NV float4 per lane, U rows per group in flight.
+template <int G, int NV, int U, int KIND, bool LSH>
+__global__ void __launch_bounds__(kScanThreads, (NV * U <= 8) ? 4 : 2)
+scan_topn_kernel(const __grid_constant__ ScanParams p) {
+  constexpr int T = kScanThreads;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ unsigned int s_thr_key;
+
+  unsigned long long* cand_arr = reinterpret_cast<unsigned long long*>(smem_raw);  // [k]
+  int32_t* s_excl_buf = reinterpret_cast<int32_t*>(smem_raw + (size_t)p.k * 8);    // [n_excl] if staged
+
   const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int gl = lane % G;   // lane within the row group
+  const int grp = lane / G;  // which row of the warp's row set
+  constexpr int RPI = 32 / G;       // rows covered by one load instruction of a warp
+  constexpr int RPT = RPI * U;      // rows per warp tile
+
+  const int32_t* excl = p.excl_in_smem ? s_excl_buf : p.excl;
+  if (p.excl_in_smem) {
+    for (int i = tid; i < p.n_excl; i += T) s_excl_buf[i] = __ldg(p.excl + i);
+  }
+  if (p.debug_ts && tid == 0) atomicMin(p.debug_ts + 0, global_ns());  // earliest CTA start
+  for (int i = tid; i < p.k; i += T) cand_arr[i] = 0ull;  // empty sentinels
+  if (tid == 0) s_thr_key = 0u;
+  __syncthreads();
+
+  const int f4 = p.f4;
+  float4 qv[NV];
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    int idx = gl + v * G;
+    qv[v] = idx < f4 ? __ldg(reinterpret_cast<const float4*>(p.q) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const int main_idx = LSH ? __ldg(p.main_index) : 0;
+  const bool full_width = (f4 == G * NV);  // every lane's every float4 is inside the row
+
+  const int warps_total = (int)gridDim.x * (T / 32);
+  const int gw = (int)blockIdx.x * (T / 32) + (tid >> 5);
+  const int n_slots = (int)p.n_slots;  // slots are int32 row handles
+  const int n_tiles = (n_slots + RPT - 1) / RPT;
+  const int n_full_tiles = n_slots / RPT;
+  const int my_u = owned_row<U>(gl);
+
+  // Offer the rows whose reduced score beats the CTA threshold (slow path, rare).  The whole warp
+  // takes part in each offer.
+  auto offer = [&](float score, bool hit, int tile) {
+    unsigned ball = __ballot_sync(0xffffffffu, hit);
+    if (ball == 0u) return;
+    const int my_slot = tile * RPT + grp + my_u * RPI;
+    const uint32_t my_key = float_key(score);
+    while (ball != 0u) {
+      const int src = __ffs(ball) - 1;
+      ball &= ball - 1;
+      const uint32_t key = __shfl_sync(0xffffffffu, my_key, src);
+      const int slot = __shfl_sync(0xffffffffu, my_slot, src);
+      warp_offer(p, cand_arr, excl, &s_thr_key, key, slot, lane);
+    }
+  };
+
+  auto score_tile = [&](const float4 (&d)[U][NV], float (&acc)[U], float (&nrm)[U]) {
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      float a = 0.f, n = 0.f;
+#pragma unroll
+      for (int v = 0; v < NV; v++) {
+        a = fmaf(d[u][v].x, qv[v].x, a);
+        a = fmaf(d[u][v].y, qv[v].y, a);
+        a = fmaf(d[u][v].z, qv[v].z, a);
+        a = fmaf(d[u][v].w, qv[v].w, a);
+        if (KIND == ORYX_COSINE) {
+          n = fmaf(d[u][v].x, d[u][v].x, n);
+          n = fmaf(d[u][v].y, d[u][v].y, n);
+          n = fmaf(d[u][v].z, d[u][v].z, n);
+          n = fmaf(d[u][v].w, d[u][v].w, n);
+        }
+      }
+      acc[u] = a;
+      nrm[u] = n;
+    }
+    reduce_rows<G, U>(acc, gl);
+    if (KIND == ORYX_COSINE) reduce_rows<G, U>(nrm, gl);
+  };
+
+  // A full tile of an unfiltered scan: every load unconditional.
+  auto fast_tile = [&](int tile) {
+    const float4* ptr = p.y + ((int64_t)tile * RPT + grp) * f4 + gl;
+    const int row_step = RPI * f4;
+    float4 d[U][NV];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+#pragma unroll
+      for (int v = 0; v < NV; v++) d[u][v] = ldg_stream(ptr + u * row_step + v * G);
+    const uint32_t thr_key = *(volatile unsigned int*)&s_thr_key;
+    float acc[U], nrm[U];
+    score_tile(d, acc, nrm);
+    const float score = (KIND == ORYX_COSINE) ? acc[0] * rsqrtf(nrm[0]) : acc[0];
+    offer(score, gl < U && score == score && float_key(score) > thr_key, tile);
+  };
+
+  // Any tile: LSH-filtered scans, ragged widths, the final partial tile.
+  auto general_tile = [&](int tile) {
+    const int row0 = tile * RPT + grp;
+    float4 d[U][NV];
+    bool act[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int row = row0 + u * RPI;
+      act[u] = row < n_slots;
+      if (LSH) {
+        int part = act[u] ? __ldg(p.slot_part + row) : -1;
+        act[u] = part >= 0 && __popc(part ^ main_idx) <= p.max_bits;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const float4* src = p.y + (int64_t)(row0 + u * RPI) * f4;
+#pragma unroll
+      for (int v = 0; v < NV; v++) {
+        int idx = gl + v * G;
+        d[u][v] = (act[u] && idx < f4) ? ldg_stream(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    const uint32_t thr_key = *(volatile unsigned int*)&s_thr_key;
+    float acc[U], nrm[U];
+    score_tile(d, acc, nrm);
+    const float score = (KIND == ORYX_COSINE) ? acc[0] * rsqrtf(nrm[0]) : acc[0];
+    // the owning lane decides; its row's activity flag sits at index my_u
+    bool mine = false;
+#pragma unroll
+    for (int u = 0; u < U; u++) mine = mine || (u == my_u && act[u]);
+    offer(score, gl < U && mine && score == score && float_key(score) > thr_key, tile);
+  };
+
+  // Hybrid schedule over tiles [0, total): 3/4 statically interleaved by warp, the rest handed out
+  // from the global counter in guided chunks (large while much work remains, single tiles at the
+  // end).  Every fetch is issued one chunk ahead -- the first one before the static phase -- so the
+  // atomic's latency (and the burst of all warps hitting one address) hides behind useful work.
+  auto for_each_tile = [&](int total, auto&& body) {
+    const int iters_static = (total / warps_total) * 3 / 4;
+    const int static_tiles = iters_static * warps_total;
+    const int dyn_total = total - static_tiles;
+    auto guided = [&](int remaining) { return max(1, min(kDynChunkMax, remaining / (2 * warps_total))); };
+    int size = guided(dyn_total);
+    int nxt = 0;
+    if (lane == 0) nxt = (int)atomicAdd(p.counter, (unsigned)size);
+    for (int i = 0; i < iters_static; i++) body(gw + i * warps_total);
+    for (;;) {
+      const int cur = __shfl_sync(0xffffffffu, nxt, 0);
+      if (cur >= dyn_total) break;
+      const int end = min(cur + size, dyn_total);
+      size = guided(dyn_total - end);
+      if (lane == 0) nxt = (int)atomicAdd(p.counter, (unsigned)size);
+      for (int t = cur; t < end; t++) body(static_tiles + t);
+    }
+  };
+
+  if (!LSH && full_width) {
+    for_each_tile(n_full_tiles, fast_tile);
+    if (n_tiles > n_full_tiles && gw == n_full_tiles % warps_total) general_tile(n_full_tiles);
+  } else {
+    for_each_tile(n_tiles, general_tile);
+  }
+
+  // publish this CTA's candidates (key, slot); unused entries still carry the empty sentinel key 0.
+  __syncthreads();
+  if (p.debug_ts && tid == 0) {
+    unsigned long long t = global_ns();
+    atomicMin(p.debug_ts + 1, t);
+    atomicMax(p.debug_ts + 2, t);
+  }
+  uint2* mine_out = p.cand + (size_t)blockIdx.x * p.k;
+  for (int i = tid; i < p.k; i += T) {
+    const unsigned long long v = cand_arr[i];
+    uint2 e;
+    e.x = (uint32_t)(v >> 32);
+    e.y = (uint32_t)v;
+    mine_out[i] = e;
+  }
+  if (tid < 32) {  // the list's best key lets the finishing kernel discard whole lists unread
+    uint32_t mx = 0u;
+    for (int i = lane; i < p.k; i += 32) mx = max(mx, (uint32_t)(cand_arr[i] >> 32));
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 0) p.list_max[blockIdx.x] = mx;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Finishing kernel: one CTA of 1024 threads.
+
+// ---- selection for small k (k <= 32) -----------------------------------------------------------
+// The k-th largest of the lists' maxima, M, is a lower bound of the global k-th best score (k
+// different lists each hold an entry >= M).  So only lists whose maximum reaches M can contribute,
+// and only with entries >= M: at most ~k lists x k entries instead of n_lists x k.  Those few
+// entries are gathered into shared memory and rank-sorted, one thread per entry.
+constexpr int kSmallKMax = 32;
+constexpr int kGatherCap = 1024;  // = kFinishThreads: one thread per gathered entry
+
+// k-th largest of n 32-bit keys in shared memory, by one warp (bisection, hardware warp reduce).
+// Returns the largest t with count(key >= t) >= k, or 1 if fewer than k keys are non-zero.
+__device__ __forceinline__ uint32_t warp_kth_largest_key(const uint32_t* keys, int n, int k, int lane) {
+  uint32_t lo = 1u, hi = 0xffffffffu;
+  while (hi - lo > 1u) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    int c = 0;
+    for (int i = lane; i < n; i += 32) c += keys[i] >= mid ? 1 : 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (c >= k) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// Returns the number selected (written to out[0..) in descending order), or -1 if the gather buffer
+// overflowed (pathological ties) and the caller must use the general path.
+__device__ int select_small_k(const ScanParams& p, int n_lists, uint32_t* s_max /*[n_lists]*/,
+                              unsigned long long* s_ent /*[kGatherCap]*/, unsigned long long* out) {
+  constexpr int T = kFinishThreads;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int k = p.k;
+  __shared__ uint32_t s_m;
+  __shared__ unsigned int s_count;
+  for (int i = tid; i < n_lists; i += T) s_max[i] = __ldcg(p.list_max + i);
+  if (tid == 0) s_count = 0u;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t m = n_lists >= k ? warp_kth_largest_key(s_max, n_lists, k, lane) : 1u;
+    if (lane == 0) s_m = m;
+  }
+  __syncthreads();
+  const uint32_t m = s_m;
   const int64_t total = (int64_t)n_lists * k;
-  // shared layout: sel_key[k] u32 | sel_row[k] i32 | sel_exact[k] f64 | hist[256] | misc
-  uint32_t* sel_key = reinterpret_cast<uint32_t*>(smem_raw);
-  int32_t* sel_slot = reinterpret_cast<int32_t*>(smem_raw + (size_t)k * 4);
-  double* sel_exact = reinterpret_cast<double*>(smem_raw + (size_t)k * 8);
-  unsigned int* hist = reinterpret_cast<unsigned int*>(smem_raw + (size_t)k * 16);
+  for (int64_t i = tid; i < total; i += T) {
+    const int list = (int)(i / k);
+    if (s_max[list] < m) continue;  // nothing in this list can make the cut: never read it
+    const uint2 e = __ldcg(&p.cand[i]);
+    if (e.x != 0u && e.x >= m) {
+      const unsigned pos = atomicAdd(&s_count, 1u);
+      if (pos < (unsigned)kGatherCap) s_ent[pos] = ((unsigned long long)e.x << 32) | (unsigned long long)e.y;
+    }
+  }
+  __syncthreads();
+  const int n = (int)s_count;
+  if (n > kGatherCap) return -1;
+  // rank-sort: words are unique, rank = number of larger words
+  if (tid < n) {
+    const unsigned long long mine = s_ent[tid];
+    int rank = 0;
+    for (int j = 0; j < n; j++) rank += s_ent[j] > mine ? 1 : 0;
+    if (rank < k) out[rank] = mine;
+  }
+  __syncthreads();
+  return min(n, k);
+}
+
+// Radix select (4 passes x 8 bits, most significant first) of the k largest keys among `total`
+// entries read through `key_at` / `entry_at`.  Used when k is large.  Writes packed words to out
+// (unordered) and returns how many.
+template <typename KeyAt, typename EntryAt>
+__device__ int select_radix(int64_t total, int k, unsigned int* hist, unsigned long long* out, KeyAt key_at,
+                            EntryAt entry_at) {
+  constexpr int T = kFinishThreads;
+  const int tid = threadIdx.x;
   __shared__ unsigned int s_prefix, s_mask, s_remaining, s_nsel, s_neq;
   if (tid == 0) { s_prefix = 0; s_mask = 0; s_remaining = (unsigned)k; s_nsel = 0; s_neq = 0; }
   __syncthreads();
-
-  // Radix select (4 passes x 8 bits, most significant first) of the k-th largest key.
   for (int pass = 0; pass < 4; pass++) {
     const int shift = 24 - 8 * pass;
-    for (int b = tid; b < 256; b += kThreads) hist[b] = 0;
+    for (int b = tid; b < 256; b += T) hist[b] = 0;
     __syncthreads();
     const unsigned prefix = s_prefix, mask = s_mask;
-    for (int64_t i = tid; i < total; i += kThreads) {
-      unsigned key = __ldcg(&p.cand[i].x);
+    for (int64_t i = tid; i < total; i += T) {
+      unsigned key = key_at(i);
       if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
     }
     __syncthreads();
@@ -165,10 +466,9 @@ __device__ void final_merge(const ScanParams& p, int kind, unsigned char* smem_r
       }
       unsigned excl_sum = incl - sum;
       unsigned remaining = s_remaining;
-      bool mine = (excl_sum < remaining) && (incl >= remaining);
       // Exactly one lane owns the crossing: the matching keys always number >= remaining >= 1
-      // (pass 0 sees all gridDim.x * k entries, sentinels included).
-      if (mine) {
+      // (pass 0 sees all entries, sentinels included).
+      if ((excl_sum < remaining) && (incl >= remaining)) {
         unsigned cum = excl_sum;
         int digit = 0;
 #pragma unroll
@@ -186,46 +486,122 @@ __device__ void final_merge(const ScanParams& p, int kind, unsigned char* smem_r
   const unsigned thr_key = s_prefix;
   const unsigned need_eq = s_remaining;
   __syncthreads();
-  for (int64_t i = tid; i < total; i += kThreads) {
-    uint2 e = __ldcg(&p.cand[i]);
-    if (e.x == 0u) continue;  // empty sentinel
-    bool take = e.x > thr_key;
-    if (!take && e.x == thr_key && thr_key != 0u) take = atomicAdd(&s_neq, 1u) < need_eq;
+  for (int64_t i = tid; i < total; i += T) {
+    unsigned long long e = entry_at(i);
+    unsigned key = (unsigned)(e >> 32);
+    if (key == 0u) continue;  // empty sentinel
+    bool take = key > thr_key;
+    if (!take && key == thr_key && thr_key != 0u) take = atomicAdd(&s_neq, 1u) < need_eq;
     if (take) {
       unsigned pos = atomicAdd(&s_nsel, 1u);
-      if (pos < (unsigned)k) { sel_key[pos] = e.x; sel_slot[pos] = (int32_t)e.y; }
+      if (pos < (unsigned)k) out[pos] = e;
     }
   }
   __syncthreads();
-  const int nsel = min((int)s_nsel, k);
+  return min((int)s_nsel, k);
+}
 
-  // Exact re-score: VectorMath.dot / CosineAverageFunction.applyAsDouble arithmetic, one thread per row.
-  for (int i = tid; i < nsel; i += kThreads) {
-    const int32_t slot = sel_slot[i];
-    const float* y = reinterpret_cast<const float*>(p.y) + (int64_t)slot * p.f4 * 4;
-    double dot = 0.0, tot = 0.0;
-    for (int j = 0; j < p.features; j++) {
-      float yv = y[j];
-      dot = exact_step(dot, __ldg(p.q + j), yv);
-      if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+// Byte offsets of the finishing CTA's shared-memory regions (host and device agree through this).
+struct FinishLayout {
+  size_t sel, exact, rows, hist, q, rowbuf, lmax, gather, total;
+};
+__host__ __device__ inline FinishLayout finish_layout(int k, int fpad, int rescore_warps, int n_lists) {
+  FinishLayout L;
+  size_t o = 0;
+  L.sel = o;    o += (size_t)k * 8;
+  L.exact = o;  o += (size_t)k * 8;
+  L.rows = o;   o += (size_t)k * 4;
+  o = (o + 15) & ~(size_t)15;
+  L.hist = o;   o += 256 * 4;
+  L.q = o;      o += (size_t)fpad * 4;
+  L.rowbuf = o; o += (size_t)rescore_warps * fpad * 4;
+  o = (o + 15) & ~(size_t)15;
+  L.gather = o; o += (k <= 32) ? (size_t)1024 * 8 : 0;
+  L.lmax = o;   o += (k <= 32) ? (size_t)n_lists * 4 : 0;
+  L.total = (o + 15) & ~(size_t)15;
+  return L;
+}
+
+__global__ void __launch_bounds__(kFinishThreads, 1)
+topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, int rescore_warps) {
+  constexpr int T = kFinishThreads;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int k = p.k;
+  const int64_t total = (int64_t)n_lists * k;
+  const int fpad = p.f4 * 4;
+  const FinishLayout L = finish_layout(k, fpad, rescore_warps, n_lists);
+  unsigned long long* sel = reinterpret_cast<unsigned long long*>(smem_raw + L.sel);
+  double* sel_exact = reinterpret_cast<double*>(smem_raw + L.exact);
+  int32_t* sel_row = reinterpret_cast<int32_t*>(smem_raw + L.rows);
+  unsigned int* hist = reinterpret_cast<unsigned int*>(smem_raw + L.hist);
+  float* s_q = reinterpret_cast<float*>(smem_raw + L.q);
+  float* rowbuf = reinterpret_cast<float*>(smem_raw + L.rowbuf);  // [rescore_warps x fpad]
+  unsigned long long* s_ent = reinterpret_cast<unsigned long long*>(smem_raw + L.gather);
+  uint32_t* s_max = reinterpret_cast<uint32_t*>(smem_raw + L.lmax);
+
+  // The next query's scan does not depend on this kernel (it uses the other scratch set): let it
+  // start now.  This kernel itself was launched ahead of time and must wait for its own scan.
+  pdl_launch_dependents();
+  for (int j = tid; j < fpad; j += T) s_q[j] = __ldg(p.q + j);
+  pdl_wait_primary();
+  if (p.debug_ts && tid == 0) p.debug_ts[3] = global_ns();
+
+  int nsel = -1;
+  if (k <= kSmallKMax) nsel = select_small_k(p, n_lists, s_max, s_ent, sel);
+  if (nsel < 0) {
+    __syncthreads();
+    nsel = select_radix(total, k, hist, sel,
+                        [&](int64_t i) { return __ldcg(&p.cand[i].x); },
+                        [&](int64_t i) {
+                          uint2 e = __ldcg(&p.cand[i]);
+                          return ((unsigned long long)e.x << 32) | (unsigned long long)e.y;
+                        });
+  }
+  if (p.debug_ts && tid == 0) p.debug_ts[4] = global_ns();
+
+  // Exact re-score: VectorMath.dot / CosineAverageFunction.applyAsDouble arithmetic.  One warp per
+  // selected row: the lanes stage the row in shared memory with coalesced loads (one round trip),
+  // lane 0 then walks it in index order.
+  if (warp < rescore_warps) {
+    for (int i = warp; i < nsel; i += rescore_warps) {
+      const int32_t slot = (int32_t)(uint32_t)sel[i];
+      const float4* y4 = p.y + (int64_t)slot * p.f4;
+      float4* rb4 = reinterpret_cast<float4*>(rowbuf + (size_t)warp * fpad);
+      for (int j = lane; j < p.f4; j += 32) rb4[j] = y4[j];
+      __syncwarp();
+      if (lane == 0) {
+        const int32_t row_id = __ldg(p.slot_row + slot);  // issued before the chain, used after it
+        const float* y = rowbuf + (size_t)warp * fpad;
+        double dot = 0.0, tot = 0.0;
+#pragma unroll 8
+        for (int j = 0; j < p.features; j++) {
+          const float yv = y[j];
+          dot = exact_step(dot, s_q[j], yv);
+          if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+        }
+        sel_exact[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
+        sel_row[i] = row_id;
+      }
+      __syncwarp();
     }
-    sel_exact[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
-    sel_slot[i] = __ldg(p.slot_row + slot);  // from here on: row ids
   }
   __syncthreads();
+  if (p.debug_ts && tid == 0) p.debug_ts[5] = global_ns();
+
   // Rank by (exact score desc, row asc) -- Pairs.orderBySecond(DESCENDING) (Pairs.java:48-54), ties
   // made deterministic.  A NaN exact score (possible only if fp32 and fp64 disagree about a zero
   // norm) ranks last.
   const int n_out = min(nsel, p.how_many);
-  for (int i = tid; i < nsel; i += kThreads) {
+  for (int i = tid; i < nsel; i += T) {
     const double si = sel_exact[i];
-    const int32_t ri = sel_slot[i];
+    const int32_t ri = sel_row[i];
     const bool nan_i = si != si;
     int rank = 0;
     for (int j = 0; j < nsel; j++) {
       const double sj = sel_exact[j];
       const bool nan_j = sj != sj;
-      const int32_t rj = sel_slot[j];
+      const int32_t rj = sel_row[j];
       bool better;  // does j rank before i?
       if (nan_j) better = nan_i && rj < ri;
       else if (nan_i) better = true;
@@ -237,156 +613,62 @@ __device__ void final_merge(const ScanParams& p, int kind, unsigned char* smem_r
       p.out_scores[rank] = si;
     }
   }
-  if (tid == 0) *p.out_n = n_out;
-}
-
-// G lanes per row, NV float4 per lane, U rows per group in flight.
-template <int G, int NV, int U, int KIND, bool LSH>
-__global__ void __launch_bounds__(kThreads) scan_topn_kernel(const __grid_constant__ ScanParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ float s_thr;
-  __shared__ int s_cnt, s_lock, s_last;
-
-  HeapView heap;
-  heap.score = reinterpret_cast<float*>(smem_raw);
-  heap.slot = reinterpret_cast<int32_t*>(smem_raw + (size_t)p.k * 4);
-
-  const int tid = threadIdx.x;
-  const int lane = tid & 31;
-  const int gl = lane % G;   // lane within the row group
-  const int grp = lane / G;  // which row of the warp's row set
-  constexpr int RPI = 32 / G;       // rows covered by one load instruction of a warp
-  constexpr int RPT = RPI * U;      // rows per warp tile
-
-  if (tid == 0) { s_thr = -INFINITY; s_cnt = 0; s_lock = 0; }
-  __syncthreads();
-
-  float4 qv[NV];
-#pragma unroll
-  for (int v = 0; v < NV; v++) {
-    int idx = gl + v * G;
-    qv[v] = idx < p.f4 ? __ldg(reinterpret_cast<const float4*>(p.q) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  const int main_idx = LSH ? __ldg(p.main_index) : 0;
-
-  const int64_t warps_total = (int64_t)gridDim.x * (kThreads / 32);
-  const int64_t gw = (int64_t)blockIdx.x * (kThreads / 32) + (tid >> 5);
-  const int64_t n_tiles = (p.n_slots + RPT - 1) / RPT;
-
-  for (int64_t tile = gw; tile < n_tiles; tile += warps_total) {
-    const int64_t row0 = tile * RPT + grp;
-    float4 d[U][NV];
-    bool act[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int64_t row = row0 + u * RPI;
-      act[u] = row < p.n_slots;
-      if (LSH) {
-        int part = act[u] ? __ldg(p.slot_part + row) : -1;
-        act[u] = part >= 0 && __popc(part ^ main_idx) <= p.max_bits;
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int64_t row = row0 + u * RPI;
-      const float4* src = p.y + row * p.f4;
-#pragma unroll
-      for (int v = 0; v < NV; v++) {
-        int idx = gl + v * G;
-        d[u][v] = (act[u] && idx < p.f4) ? ldg_stream(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-    }
-    float thr = *(volatile float*)&s_thr;
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      float acc = 0.f, nrm = 0.f;
-#pragma unroll
-      for (int v = 0; v < NV; v++) {
-        acc = fmaf(d[u][v].x, qv[v].x, acc);
-        acc = fmaf(d[u][v].y, qv[v].y, acc);
-        acc = fmaf(d[u][v].z, qv[v].z, acc);
-        acc = fmaf(d[u][v].w, qv[v].w, acc);
-        if (KIND == ORYX_COSINE) {
-          nrm = fmaf(d[u][v].x, d[u][v].x, nrm);
-          nrm = fmaf(d[u][v].y, d[u][v].y, nrm);
-          nrm = fmaf(d[u][v].z, d[u][v].z, nrm);
-          nrm = fmaf(d[u][v].w, d[u][v].w, nrm);
-        }
-      }
-#pragma unroll
-      for (int o = G / 2; o > 0; o >>= 1) {
-        acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (KIND == ORYX_COSINE) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
-      }
-      float score = (KIND == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc;
-      bool hit = act[u] && gl == 0 && score > thr;
-      unsigned ball = __ballot_sync(0xffffffffu, hit);
-      if (ball != 0u) {
-        while (ball != 0u) {
-          int src = __ffs(ball) - 1;
-          ball &= ball - 1;
-          float s = __shfl_sync(0xffffffffu, score, src);
-          int64_t r = row0 + u * RPI;
-          int32_t slot = __shfl_sync(0xffffffffu, (int32_t)r, src);
-          if (lane == 0) heap_offer(p, heap, &s_cnt, &s_lock, &s_thr, s, slot);
-        }
-        __syncwarp();
-        thr = *(volatile float*)&s_thr;
-      }
-    }
-  }
-
-  // publish this CTA's heap (key, slot); unused entries carry the empty sentinel key 0.
-  __syncthreads();
-  const int cnt = s_cnt;
-  uint2* mine = p.cand + (size_t)blockIdx.x * p.k;
-  for (int i = tid; i < p.k; i += kThreads) {
-    uint2 e;
-    if (i < cnt) { e.x = float_key(heap.score[i]); e.y = (unsigned)heap.slot[i]; }
-    else { e.x = 0u; e.y = 0u; }
-    __stcg(mine + i, e);
-  }
-  __threadfence();
-  __syncthreads();
   if (tid == 0) {
-    unsigned ticket = atomicAdd(p.counter, 1u);
-    s_last = (ticket == gridDim.x - 1);
+    *p.out_n = n_out;
+    *p.counter = 0u;  // the dynamic tile counter starts at zero for the next query on this context
+    if (p.debug_ts) p.debug_ts[6] = global_ns();
   }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  final_merge(p, KIND, smem_raw, (int)gridDim.x);
-  if (tid == 0) *p.counter = 0u;  // self-cleaning for the next query on this context
 }
+
+// ------------------------------------------------------------------------------------------------
 
 // cudaOccupancyMaxActiveBlocksPerMultiprocessor costs microseconds; remember it per (kernel, smem).
-int occupancy_cached(const void* kern, size_t smem) {
+int occupancy_cached(const void* kern, int threads, size_t smem, size_t max_dynamic_smem) {
   static std::mutex mu;
   static std::vector<std::pair<std::pair<const void*, size_t>, int>> cache;
   std::lock_guard<std::mutex> lk(mu);
   for (auto& e : cache) if (e.first.first == kern && e.first.second == smem) return e.second;
   int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem) != cudaSuccess) {
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_dynamic_smem) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem) != cudaSuccess) {
     cudaGetLastError();
     per_sm = 1;
   }
+  if (per_sm < 1) per_sm = 1;
   cache.push_back({{kern, smem}, per_sm});
   return per_sm;
 }
 
+// Dynamic shared memory of a scan CTA: the candidate array (8 B per entry) plus the staged exclusion list.
+size_t scan_smem_bytes(int k, int n_excl_staged) {
+  return (size_t)k * 8 + (size_t)n_excl_staged * sizeof(int32_t);
+}
+
 template <int G, int NV, int U>
-int32_t launch_variant(Model* m, const ScanParams& p, int kind, bool lsh, size_t smem, cudaStream_t stream,
+int32_t launch_variant(Model* m, const ScanParams& p, int kind, bool lsh, bool overlap, cudaStream_t stream,
                        int* grid_out) {
+  // 256-thread CTAs; the register allocation is bounded for 4 CTAs per SM (<= 64 registers) when a
+  // thread keeps at most 8 float4 in flight.
+  constexpr int T = kScanThreads;
   auto pick = [&](auto kern) -> int32_t {
-    int per_sm = occupancy_cached(reinterpret_cast<const void*>(kern), smem);
-    if (per_sm < 1) per_sm = 1;
     constexpr int RPT = (32 / G) * U;
     int64_t n_tiles = (p.n_slots + RPT - 1) / RPT;
-    int64_t want = (n_tiles + (kThreads / 32) - 1) / (kThreads / 32);
+    int64_t want = (n_tiles + (T / 32) - 1) / (T / 32);
+    const size_t smem = scan_smem_bytes(p.k, p.excl_in_smem ? p.n_excl : 0);
+    int per_sm = occupancy_cached(reinterpret_cast<const void*>(kern), T, smem, scan_smem_bytes(kMaxK, kExclSmemMax));
     int grid = (int)std::min<int64_t>(std::min<int64_t>((int64_t)m->num_sms * per_sm, kMaxGrid), std::max<int64_t>(want, 1));
     *grid_out = grid;
-    kern<<<grid, kThreads, smem, stream>>>(p);
-    ORYX_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(T);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = overlap ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ORYX_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
     return ORYX_OK;
   };
   if (kind == ORYX_COSINE) {
@@ -397,90 +679,33 @@ int32_t launch_variant(Model* m, const ScanParams& p, int kind, bool lsh, size_t
              : pick(scan_topn_kernel<G, NV, U, ORYX_DOT, false>);
 }
 
-// One thread per slot, exact arithmetic, result scattered to out[row].
-__global__ void scores_all_kernel(const float* __restrict__ y, const int32_t* __restrict__ slot_row,
-                                  int64_t n_slots, int fpad, int features, const float* __restrict__ q,
-                                  int kind, int32_t n_rows, double* __restrict__ out) {
-  extern __shared__ float s_tile[];  // [blockDim.x x (features+1)]
-  const int ld = features + 1;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < n_slots; base += (int64_t)gridDim.x * blockDim.x) {
-    __syncthreads();
-    for (int r = warp; r < (int)blockDim.x; r += nwarps) {
-      int64_t slot = base + r;
-      if (slot < n_slots) {
-        const float* src = y + slot * fpad;
-        for (int j = lane; j < features; j += 32) s_tile[r * ld + j] = src[j];
-      }
-    }
-    __syncthreads();
-    int64_t slot = base + threadIdx.x;
-    if (slot < n_slots) {
-      int32_t row = slot_row[slot];
-      if (row >= 0 && row < n_rows) {
-        const float* v = s_tile + threadIdx.x * ld;
-        double dot = 0.0, tot = 0.0;
-        for (int j = 0; j < features; j++) {
-          float yv = v[j];
-          dot = exact_step(dot, __ldg(q + j), yv);
-          if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
-        }
-        out[row] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
-      }
-    }
+int32_t launch_finish(const ScanParams& p, int n_lists, int kind, cudaStream_t stream) {
+  const int fpad = p.f4 * 4;
+  const int rescore_warps = std::max(1, std::min(kFinishThreads / 32, kRowStageFloats / fpad));
+  const FinishLayout L = finish_layout(p.k, fpad, rescore_warps, n_lists);
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(topn_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+  });
+  ORYX_CUDA(attr_err);
+  if (L.total > 224 * 1024) {
+    set_error("finishing kernel needs %zu bytes of shared memory (features=%d, how_many=%d)", L.total, p.features,
+              p.how_many);
+    return ORYX_E_UNSUPPORTED;
   }
-}
-
-// Point lookups (kernel K10): one thread per requested slot, exact arithmetic.
-__global__ void scores_rows_kernel(const float* __restrict__ y, int fpad, int features,
-                                   const float* __restrict__ q, int kind, const int32_t* __restrict__ slots,
-                                   int n, double* __restrict__ out) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int32_t slot = slots[i];
-  if (slot < 0) { out[i] = 0.0; return; }
-  const float* v = y + (int64_t)slot * fpad;
-  double dot = 0.0, tot = 0.0, qq = 0.0;
-  for (int j = 0; j < features; j++) {
-    float yv = v[j], qv = q[j];
-    dot = exact_step(dot, qv, yv);
-    if (kind == ORYX_COSINE) { tot = exact_step(tot, yv, yv); qq = exact_step(qq, qv, qv); }
-  }
-  // SimilarityToItem.java:62-63: dot / (toItemNorm * norm(item))
-  out[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dmul_rn(__dsqrt_rn(qq), __dsqrt_rn(tot))) : dot;
-}
-
-// Cross-shard merge (kernel K7, multi-GPU leg): rank-sort of n_lists*how_many exact (score,row) pairs
-// by (score desc, global row asc) in one CTA.
-__global__ void merge_topn_kernel(const double* __restrict__ scores, const int32_t* __restrict__ rows,
-                                  const int32_t* __restrict__ counts, int n_lists, int how_many,
-                                  int64_t row_stride, int64_t* __restrict__ out_rows,
-                                  double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
-  const int total = n_lists * how_many;
-  int valid_total = 0;
-  for (int l = 0; l < n_lists; l++) valid_total += min(max(counts[l], 0), how_many);
-  const int n_out = min(valid_total, how_many);
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int li = i / how_many, pi = i - li * how_many;
-    if (pi >= counts[li]) continue;
-    const double si = scores[i];
-    const int64_t ri = (int64_t)li * row_stride + rows[i];
-    int rank = 0;
-    for (int j = 0; j < total; j++) {
-      const int lj = j / how_many, pj = j - lj * how_many;
-      if (pj >= counts[lj]) continue;
-      const double sj = scores[j];
-      const int64_t rj = (int64_t)lj * row_stride + rows[j];
-      rank += ((sj > si) || (sj == si && rj < ri)) ? 1 : 0;
-    }
-    if (rank < n_out) { out_rows[rank] = ri; out_scores[rank] = si; }
-  }
-  if (threadIdx.x == 0) *out_n = n_out;
-}
-
-__global__ void fill_nan_kernel(double* p, int64_t n) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = __longlong_as_double(0x7ff8000000000000LL);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(kFinishThreads);
+  cfg.dynamicSmemBytes = L.total;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;  // pre-launched; waits for its scan on the device
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  ORYX_CUDA(cudaLaunchKernelEx(&cfg, topn_finish_kernel, p, n_lists, kind, rescore_warps));
+  return ORYX_OK;
 }
 
 }  // namespace
@@ -504,6 +729,7 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   p.q = rq.d_query;
   p.excl = rq.d_excl;
   p.n_excl = rq.n_excl;
+  p.excl_in_smem = rq.n_excl > 0 && rq.n_excl <= kExclSmemMax;
   p.n_slots = s->n_slots;
   p.features = s->features;
   p.f4 = s->fpad / 4;
@@ -511,80 +737,38 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   p.how_many = rq.how_many;
   p.max_bits = m->max_bits;
   p.main_index = ctx->d_main_index;
-  p.cand = ctx->d_cand;
-  p.counter = ctx->d_counter;
+  // Two scratch sets alternate so that this query's scan may start while the previous query's
+  // finishing kernel (which reads the other set) is still running.  An LSH-filtered query runs a
+  // hashing kernel first, which serialises behind the previous query anyway.
+  const bool overlap = ctx->scratch_sets == 2 && !lsh;
+  const int set = ctx->scratch_sets == 2 ? (ctx->flip ^= 1) : 0;
+  p.cand = ctx->d_cand + (size_t)set * kMaxGrid * kMaxK;
+  p.list_max = ctx->d_list_max + (size_t)set * kMaxGrid;
+  p.counter = ctx->d_counter + set * 16;
   p.out_rows = rq.d_out_rows;
   p.out_scores = rq.d_out_scores;
   p.out_n = rq.d_out_n;
-  size_t smem = (size_t)p.k * 16 + 256 * sizeof(unsigned int);
+  p.debug_ts = m->d_debug_ts;
   int grid = 0;
   int32_t rc;
   const int f4 = p.f4;
-  if (f4 <= 8) rc = launch_variant<8, 1, 8>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 16) rc = launch_variant<8, 2, 4>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 24) rc = launch_variant<8, 3, 2>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 32) rc = launch_variant<8, 4, 2>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 48) rc = launch_variant<8, 6, 1>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 64) rc = launch_variant<8, 8, 1>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 128) rc = launch_variant<32, 4, 2>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 256) rc = launch_variant<32, 8, 1>(m, p, rq.kind, lsh, smem, stream, &grid);
-  else if (f4 <= 512) rc = launch_variant<32, 16, 1>(m, p, rq.kind, lsh, smem, stream, &grid);
+  if (f4 <= 8) rc = launch_variant<8, 1, 8>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 16) rc = launch_variant<8, 2, 4>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 24) rc = launch_variant<8, 3, 2>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 32) rc = launch_variant<8, 4, 2>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 48) rc = launch_variant<8, 6, 1>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 64) rc = launch_variant<8, 8, 1>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 128) rc = launch_variant<32, 4, 2>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 256) rc = launch_variant<32, 8, 1>(m, p, rq.kind, lsh, overlap, stream, &grid);
+  else if (f4 <= 512) rc = launch_variant<32, 16, 1>(m, p, rq.kind, lsh, overlap, stream, &grid);
   else {
     set_error("features=%d beyond the scan kernel's envelope (2048)", s->features);
     return ORYX_E_UNSUPPORTED;
   }
   ORYX_TRY(rc);
-  m->launches++;
+  ORYX_TRY(launch_finish(p, grid, rq.kind, stream));
+  m->launches += 2;
   m->queries++;
-  return ORYX_OK;
-}
-
-int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_rows, double* d_out,
-                          cudaStream_t stream) {
-  Store* s = &m->store[ORYX_Y];
-  int threads = 256;
-  if (n_rows > 0) {
-    fill_nan_kernel<<<(n_rows + threads - 1) / threads, threads, 0, stream>>>(d_out, n_rows);
-    m->launches++;
-  }
-  if (s->n_slots == 0 || n_rows <= 0) return ORYX_OK;
-  int tile = 128;
-  while (tile > 32 && (size_t)tile * (s->features + 1) * sizeof(float) > 200 * 1024) tile -= 32;
-  size_t smem = (size_t)tile * (s->features + 1) * sizeof(float);
-  if (smem > 200 * 1024) {
-    set_error("features=%d too large for the exact scoring kernel", s->features);
-    return ORYX_E_UNSUPPORTED;
-  }
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(scores_all_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  int64_t tiles = (s->n_slots + tile - 1) / tile;
-  int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
-  scores_all_kernel<<<grid, tile, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, s->features,
-                                                  d_query, kind, n_rows, d_out);
-  m->launches++;
-  ORYX_CUDA(cudaGetLastError());
-  return ORYX_OK;
-}
-
-int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32_t* d_slots, int n,
-                           double* d_out, cudaStream_t stream) {
-  Store* s = &m->store[ORYX_Y];
-  scores_rows_kernel<<<(n + 127) / 128, 128, 0, stream>>>(s->d_vec, s->fpad, s->features, d_query, kind,
-                                                         d_slots, n, d_out);
-  m->launches++;
-  ORYX_CUDA(cudaGetLastError());
-  return ORYX_OK;
-}
-
-int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists,
-                          int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
-                          int32_t* d_out_n, cudaStream_t stream) {
-  merge_topn_kernel<<<1, 256, 0, stream>>>(d_scores, d_rows, d_n, n_lists, how_many, row_stride, d_out_rows,
-                                           d_out_scores, d_out_n);
-  ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }
 

@@ -46,8 +46,11 @@ __global__ void clear_slots_kernel(const int32_t* __restrict__ slots, int64_t n,
   int lane = threadIdx.x & 31;
   if (w >= n) return;
   int32_t slot = slots[w];
+  // A tombstone is all-NaN: whatever the query, its score is NaN and "score > threshold" is false, so
+  // the scan never has to look at slot_row on its hot path (TopNConsumer never admits NaN either).
   float* dst = vec + (int64_t)slot * fpad;
-  for (int j = lane; j < fpad; j += 32) dst[j] = 0.0f;
+  const float qnan = __int_as_float(0x7fc00000);
+  for (int j = lane; j < fpad; j += 32) dst[j] = qnan;
   if (lane == 0) {
     slot_row[slot] = -1;
     slot_part[slot] = -1;

@@ -2,7 +2,7 @@
 // allocate.
 //
 // Who needs this.  oryx_topn / oryx_topn_device take their scratch (the per-CTA candidate lists, the
-// "last CTA" ticket and the query's LSH index) from a query context that the library creates with
+// scan work counter and the query's LSH index) from a query context that the library creates with
 // cudaMalloc / cudaMallocHost the first time a context is needed.  Some hosts cannot afford that:
 //   * a serving thread on a latency budget -- cudaMalloc may synchronise the whole device and stall
 //     every other query in flight;
@@ -13,10 +13,10 @@
 // For them this entry point runs the same kernel with its scratch in a fixed array that is part of
 // the loaded module, so the call performs no device, pinned or pooled allocation at all.
 //
-// Cost and limits.  The array (about 593 KB) is resident on every GPU that loads the library, from
+// Cost and limits.  The array (about 598 KB) is resident on every GPU that loads the library, from
 // load until the process exits.  It bounds the request: how_many <= ORYX_STATIC_MAX_HOW_MANY (56).
 // There is ONE array per device, shared by all callers: it still holds whatever the previous call left
-// in it (this call resets the ticket before launching; candidate slots are fully rewritten by every
+// in it (this call resets the work counter before launching; candidate slots are fully rewritten by every
 // launch), and two calls whose kernels overlap on the same GPU -- different streams, different
 // threads, different models -- race on it and return garbage.  Serialise them (one stream, or
 // events).  The first call on each device looks up the array's device address
@@ -28,11 +28,12 @@ namespace oryx {
 namespace {
 
 constexpr int kStaticMaxHowMany = ORYX_STATIC_MAX_HOW_MANY;  // 56
-constexpr int kStaticK = kStaticMaxHowMany + kTopnMargin;    // 64 heap entries per CTA
+constexpr int kStaticK = kStaticMaxHowMany + kTopnMargin;    // 64 candidate entries per CTA
 constexpr size_t kCandBytes = (size_t)kMaxGrid * kStaticK * sizeof(uint2);
-constexpr size_t kCounterOffset = kCandBytes;          // unsigned int ticket
+constexpr size_t kCounterOffset = kCandBytes;          // unsigned int work counter
 constexpr size_t kMainIndexOffset = kCandBytes + 64;   // int32 LSH index of the query
-constexpr size_t kScratchBytes = kCandBytes + 256;
+constexpr size_t kListMaxOffset = kCandBytes + 256;    // uint32 best key per CTA list
+constexpr size_t kScratchBytes = kListMaxOffset + (size_t)kMaxGrid * sizeof(uint32_t);
 
 // In host code this name is only a handle for the runtime's symbol table, never a device address.
 static __device__ __align__(256) unsigned char g_topn_static_scratch[kScratchBytes];
@@ -97,9 +98,10 @@ extern "C" int32_t oryx_topn_device_static(oryx_model* mh, int32_t kind, const f
   QueryCtx ctx;
   ctx.d_cand = reinterpret_cast<uint2*>(base);
   ctx.d_counter = reinterpret_cast<unsigned int*>(base + kCounterOffset);
+  ctx.d_list_max = reinterpret_cast<uint32_t*>(base + kListMaxOffset);
   ctx.d_main_index = reinterpret_cast<int32_t*>(base + kMainIndexOffset);
-  // The ticket must start at zero; the array keeps the last call's contents (a call that failed
-  // midway could have left it non-zero).
+  // The work counter must start at zero; the array keeps the last call's contents (a call that
+  // failed midway could have left it non-zero).
   ORYX_CUDA(cudaMemsetAsync(base + kCounterOffset, 0, 128, st));
 
   TopnRequest rq{};

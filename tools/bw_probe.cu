@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdint>
+#include <cstdlib>
 #include <vector>
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e), __LINE__); return 1; } } while (0)
@@ -86,11 +87,73 @@ __global__ void bulk_kernel(const char* __restrict__ p, size_t bytes, int ch, fl
   if (acc == 123.456f) *sink = acc;
 }
 
-int main() {
+
+// ---- scan-pattern probes: the product kernel's access pattern with features added one by one.
+// MODE 0: loads + fp32 dot only;  1: + xor-shuffle reduce;  2: + ballot on score > thr (thr in smem)
+template <int MODE, int U>
+__global__ void __launch_bounds__(256) scanpat_kernel(const float4* __restrict__ y, long n_rows, const float4* __restrict__ q, float* sink) {
+  __shared__ float s_thr;
+  if (threadIdx.x == 0) s_thr = 1e30f;
+  __syncthreads();
+  constexpr int G = 8, NV = 4, RPI = 4, RPT = RPI * U, F4 = 32;
+  const int lane = threadIdx.x & 31, gl = lane % G, grp = lane / G;
+  float4 qv[NV];
+#pragma unroll
+  for (int v = 0; v < NV; v++) qv[v] = q[gl + v * G];
+  const long warps_total = (long)gridDim.x * 8, gw = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const long n_tiles = n_rows / RPT;
+  float keep = 0.f;
+  for (long tile = gw; tile < n_tiles; tile += warps_total) {
+    const long row0 = tile * RPT + grp;
+    float4 d[U][NV];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+#pragma unroll
+      for (int v = 0; v < NV; v++) d[u][v] = ldg_stream(y + (row0 + u * RPI) * F4 + gl + v * G);
+    float thr = MODE >= 2 ? *(volatile float*)&s_thr : 0.f;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      float acc = 0.f;
+#pragma unroll
+      for (int v = 0; v < NV; v++) {
+        acc = fmaf(d[u][v].x, qv[v].x, acc); acc = fmaf(d[u][v].y, qv[v].y, acc);
+        acc = fmaf(d[u][v].z, qv[v].z, acc); acc = fmaf(d[u][v].w, qv[v].w, acc);
+      }
+      if (MODE >= 1) {
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      }
+      if (MODE >= 2) {
+        unsigned ball = __ballot_sync(0xffffffffu, gl == 0 && acc > thr);
+        if (ball) keep += 1.f;
+      } else keep += acc;
+    }
+  }
+  if (keep == 123.456f) *sink = keep;
+}
+
+__global__ void fill_random(uint32_t* p, size_t n, int mode) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint32_t x = (uint32_t)(i * 2654435761u) ^ (uint32_t)(i >> 32);
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    if (mode == 1) {  // random float in [-2, 2): random mantissa + sign, narrow exponent range
+      uint32_t sign = x & 0x80000000u, man = x & 0x007fffffu, e = 126 + ((x >> 23) & 1);
+      x = sign | (e << 23) | man;
+    }
+    p[i] = x;
+  }
+}
+
+int main(int argc, char** argv) {
+  int fill_mode = argc > 1 ? atoi(argv[1]) : -1;
   size_t bytes = 5120000000ull;
   char* d; float* sink;
   CK(cudaMalloc(&d, bytes)); CK(cudaMalloc(&sink, 4));
   CK(cudaMemset(d, 1, bytes));
+  if (fill_mode >= 0) { fill_random<<<148 * 8, 256>>>((uint32_t*)d, bytes / 4, fill_mode); CK(cudaDeviceSynchronize()); }
+  printf("fill mode %d (-1 = constant bytes, 0 = random bits, 1 = random floats)\n", fill_mode);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   int sms = 148;
   auto time_it = [&](auto launch, const char* name) {
@@ -104,12 +167,25 @@ int main() {
   };
   size_t n4 = bytes / 16;
   char name[128];
-  for (int bps : {2, 3, 4, 6, 8}) {
+  float4* dq; cudaMalloc(&dq, 512); cudaMemset(dq, 0, 512);
+  long n_rows = bytes / 512;
+  for (int bps : {4}) {
+    snprintf(name, 128, "scanpat mode0 U=2 x %d/SM", bps); time_it([&] { scanpat_kernel<0, 2><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+    snprintf(name, 128, "scanpat mode1 U=2 x %d/SM", bps); time_it([&] { scanpat_kernel<1, 2><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+    snprintf(name, 128, "scanpat mode2 U=2 x %d/SM", bps); time_it([&] { scanpat_kernel<2, 2><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+    snprintf(name, 128, "scanpat mode2 U=1 x %d/SM", bps); time_it([&] { scanpat_kernel<2, 1><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+    snprintf(name, 128, "scanpat mode2 U=4 x %d/SM", bps); time_it([&] { scanpat_kernel<2, 4><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+  }
+  for (int bps : {8}) {
+    snprintf(name, 128, "scanpat mode2 U=1 x %d/SM", bps); time_it([&] { scanpat_kernel<2, 1><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+    snprintf(name, 128, "scanpat mode2 U=2 x %d/SM", bps); time_it([&] { scanpat_kernel<2, 2><<<sms * bps, 256>>>((const float4*)d, n_rows, dq, sink); }, name);
+  }
+  for (int bps : {3, 4}) {
     snprintf(name, 128, "ldg U=4  256thr x %d/SM", bps); time_it([&] { ldg_kernel<4><<<sms * bps, 256>>>((const float4*)d, n4, sink); }, name);
     snprintf(name, 128, "ldg U=8  256thr x %d/SM", bps); time_it([&] { ldg_kernel<8><<<sms * bps, 256>>>((const float4*)d, n4, sink); }, name);
     snprintf(name, 128, "ldg U=16 256thr x %d/SM", bps); time_it([&] { ldg_kernel<16><<<sms * bps, 256>>>((const float4*)d, n4, sink); }, name);
   }
-  for (int ch : {8192, 16384, 32768}) {
+  for (int ch : {32768}) {
     for (int thr : {128, 256}) {
       {
         constexpr int S = 4; size_t sm = (size_t)S * ch;
