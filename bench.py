@@ -257,16 +257,25 @@ def run_ours(args):
 
     q_host = np.random.default_rng(SEED_Q).standard_normal((N_QUERIES, F), dtype=np.float32)
     d_q = torch.from_numpy(q_host).to(dev)
-    d_rows = torch.zeros(HOW_MANY, dtype=torch.int32, device=dev)
-    d_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
-    d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+    # this rank's result lives in one packed record (scores | rows | count) so the exchange is ONE all-gather
+    rec_bytes = ob.packed_record_bytes(HOW_MANY)
+    d_rec = torch.zeros(rec_bytes, dtype=torch.uint8, device=dev)
+    d_scores = d_rec[: HOW_MANY * 8].view(torch.float64)
+    d_rows = d_rec[HOW_MANY * 8: HOW_MANY * 12].view(torch.int32)
+    d_n = d_rec[HOW_MANY * 12: HOW_MANY * 12 + 4].view(torch.int32)
     if world > 1:
-        g_rows = torch.zeros((world, HOW_MANY), dtype=torch.int32, device=dev)
-        g_scores = torch.zeros((world, HOW_MANY), dtype=torch.float64, device=dev)
-        g_n = torch.zeros(world, dtype=torch.int32, device=dev)
+        from oryx_b200.sharded import ShardPlan, exchange_packed
+        plan = ShardPlan(world, n_items)   # rank r owns global rows [r*n_items, (r+1)*n_items)
+        g_rec = torch.zeros(world * rec_bytes, dtype=torch.uint8, device=dev)
         m_rows = torch.zeros(HOW_MANY, dtype=torch.int64, device=dev)
         m_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
         m_n = torch.zeros(1, dtype=torch.int32, device=dev)
+
+        def exchange_merge():
+            exchange_packed(dist, torch, plan, d_rec, g_rec)
+            ob.merge_topn_packed(g_rec.data_ptr(), world, rec_bytes, HOW_MANY, plan.rows_per_rank,
+                                 m_rows.data_ptr(), m_scores.data_ptr(), m_n.data_ptr(),
+                                 torch.cuda.current_stream(dev).cuda_stream)
     stream = torch.cuda.current_stream(dev)
     launches_extra = 0
 
@@ -277,12 +286,7 @@ def run_ours(args):
                           d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
         if world > 1:
             # the one exchange step: N x (10 scores, 10 rows, count) over NCCL / NVLink, then merge
-            dist.all_gather_into_tensor(g_scores, d_scores)
-            dist.all_gather_into_tensor(g_rows, d_rows)
-            dist.all_gather_into_tensor(g_n, d_n)
-            ob.merge_topn_device(g_scores.data_ptr(), g_rows.data_ptr(), g_n.data_ptr(), world, HOW_MANY,
-                                 n_items, m_rows.data_ptr(), m_scores.data_ptr(), m_n.data_ptr(),
-                                 stream.cuda_stream)
+            exchange_merge()
             launches_extra += 1
 
     def barrier():
@@ -342,12 +346,7 @@ def run_ours(args):
             d_qe.copy_(h_q_pinned[i % N_QUERIES], non_blocking=True)
             model.topn_device(ob.DOT, d_qe.data_ptr(), HOW_MANY, d_rows.data_ptr(), d_scores.data_ptr(),
                               d_n.data_ptr(), stream.cuda_stream)
-            dist.all_gather_into_tensor(g_scores, d_scores)
-            dist.all_gather_into_tensor(g_rows, d_rows)
-            dist.all_gather_into_tensor(g_n, d_n)
-            ob.merge_topn_device(g_scores.data_ptr(), g_rows.data_ptr(), g_n.data_ptr(), world, HOW_MANY,
-                                 n_items, m_rows.data_ptr(), m_scores.data_ptr(), m_n.data_ptr(),
-                                 stream.cuda_stream)
+            exchange_merge()
             h_res_rows.copy_(m_rows, non_blocking=True)
             h_res_scores.copy_(m_scores, non_blocking=True)
             stream.synchronize()

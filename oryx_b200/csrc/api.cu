@@ -558,6 +558,17 @@ int32_t oryx_merge_topn_device(const double* d_scores, const int32_t* d_rows, co
                            d_out_n, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int32_t oryx_merge_topn_packed(const void* d_records, int32_t n_lists, int32_t record_bytes, int32_t how_many,
+                               int64_t row_stride, int64_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
+                               void* stream) {
+  ORYX_ARG(d_records && d_out_rows && d_out_scores && d_out_n, "null argument");
+  ORYX_ARG(n_lists >= 1 && n_lists <= 1024, "n_lists out of range [1, 1024]");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  ORYX_ARG(record_bytes >= how_many * 12 + 4 && record_bytes % 8 == 0, "record_bytes too small or not a multiple of 8");
+  return merge_topn_packed_launch(d_records, n_lists, record_bytes, how_many, row_stride, d_out_rows, d_out_scores,
+                                  d_out_n, reinterpret_cast<cudaStream_t>(stream));
+}
+
 // Development aid (not part of the public header): arm == 1 allocates/re-arms the timestamp buffer the
 // scan kernel fills; arm == 0 synchronises and copies out 8 globaltimer values (ns):
 // [0] earliest CTA start, [1]/[2] earliest/latest end of a CTA's scan, [3] merge start,

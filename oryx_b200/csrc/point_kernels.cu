@@ -65,25 +65,30 @@ __global__ void scores_rows_kernel(const float* __restrict__ y, int fpad, int fe
 
 // Cross-shard merge (kernel K7, multi-GPU leg): rank-sort of n_lists*how_many exact (score,row) pairs
 // by (score desc, global row asc) in one CTA.
-__global__ void merge_topn_kernel(const double* __restrict__ scores, const int32_t* __restrict__ rows,
-                                  const int32_t* __restrict__ counts, int n_lists, int how_many,
+__global__ void merge_topn_kernel(const unsigned char* __restrict__ scores_b, const unsigned char* __restrict__ rows_b,
+                                  const unsigned char* __restrict__ counts_b, int64_t scores_stride,
+                                  int64_t rows_stride, int64_t counts_stride, int n_lists, int how_many,
                                   int64_t row_stride, int64_t* __restrict__ out_rows,
                                   double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
+  // list l: scores at scores_b + l*scores_stride, rows at rows_b + l*rows_stride, count at counts_b + l*counts_stride
+  auto score_at = [&](int l, int j) { return reinterpret_cast<const double*>(scores_b + l * scores_stride)[j]; };
+  auto row_at = [&](int l, int j) { return reinterpret_cast<const int32_t*>(rows_b + l * rows_stride)[j]; };
+  auto count_at = [&](int l) { return *reinterpret_cast<const int32_t*>(counts_b + l * counts_stride); };
   const int total = n_lists * how_many;
   int valid_total = 0;
-  for (int l = 0; l < n_lists; l++) valid_total += min(max(counts[l], 0), how_many);
+  for (int l = 0; l < n_lists; l++) valid_total += min(max(count_at(l), 0), how_many);
   const int n_out = min(valid_total, how_many);
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int li = i / how_many, pi = i - li * how_many;
-    if (pi >= counts[li]) continue;
-    const double si = scores[i];
-    const int64_t ri = (int64_t)li * row_stride + rows[i];
+    if (pi >= count_at(li)) continue;
+    const double si = score_at(li, pi);
+    const int64_t ri = (int64_t)li * row_stride + row_at(li, pi);
     int rank = 0;
     for (int j = 0; j < total; j++) {
       const int lj = j / how_many, pj = j - lj * how_many;
-      if (pj >= counts[lj]) continue;
-      const double sj = scores[j];
-      const int64_t rj = (int64_t)lj * row_stride + rows[j];
+      if (pj >= count_at(lj)) continue;
+      const double sj = score_at(lj, pj);
+      const int64_t rj = (int64_t)lj * row_stride + row_at(lj, pj);
       rank += ((sj > si) || (sj == si && rj < ri)) ? 1 : 0;
     }
     if (rank < n_out) { out_rows[rank] = ri; out_scores[rank] = si; }
@@ -141,8 +146,22 @@ int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32
 int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists,
                           int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
                           int32_t* d_out_n, cudaStream_t stream) {
-  merge_topn_kernel<<<1, 256, 0, stream>>>(d_scores, d_rows, d_n, n_lists, how_many, row_stride, d_out_rows,
+  merge_topn_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const unsigned char*>(d_scores),
+                                           reinterpret_cast<const unsigned char*>(d_rows),
+                                           reinterpret_cast<const unsigned char*>(d_n), (int64_t)how_many * 8,
+                                           (int64_t)how_many * 4, 4, n_lists, how_many, row_stride, d_out_rows,
                                            d_out_scores, d_out_n);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_bytes, int how_many,
+                                 int64_t row_stride, int64_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
+                                 cudaStream_t stream) {
+  const unsigned char* base = reinterpret_cast<const unsigned char*>(d_records);
+  merge_topn_kernel<<<1, 256, 0, stream>>>(base, base + (size_t)how_many * 8, base + (size_t)how_many * 12,
+                                           record_bytes, record_bytes, record_bytes, n_lists, how_many,
+                                           row_stride, d_out_rows, d_out_scores, d_out_n);
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }

@@ -76,6 +76,7 @@ SIGNATURES = {
     "oryx_topn_device": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_topn_device_static": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_merge_topn_packed": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
@@ -283,6 +284,18 @@ def merge_topn_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, how_ma
     _check(lib().oryx_merge_topn_device(C.c_void_p(d_scores), C.c_void_p(d_rows), C.c_void_p(d_n), n_lists,
                                         how_many, row_stride, C.c_void_p(d_out_rows), C.c_void_p(d_out_scores),
                                         C.c_void_p(d_out_n), C.c_void_p(stream)))
+
+
+def packed_record_bytes(how_many: int) -> int:
+    """Size of one packed per-shard result record (scores f64 | rows i32 | count i32), 8-byte aligned."""
+    return (how_many * 12 + 4 + 7) // 8 * 8
+
+
+def merge_topn_packed(d_records: int, n_lists: int, record_bytes: int, how_many: int, row_stride: int,
+                      d_out_rows: int, d_out_scores: int, d_out_n: int, stream: int):
+    _check(lib().oryx_merge_topn_packed(C.c_void_p(d_records), n_lists, record_bytes, how_many, row_stride,
+                                        C.c_void_p(d_out_rows), C.c_void_p(d_out_scores), C.c_void_p(d_out_n),
+                                        C.c_void_p(stream)))
 
 
 class Solver:

@@ -344,3 +344,51 @@ def test_fold_in_goldens_and_random():
             ok = ev.astype(bool)
             scale = np.maximum(np.abs(eo[ok]).max(axis=1, keepdims=True), 1e-6)
             assert np.max(np.abs(eo[ok] - go[ok]) / scale) <= 5e-7
+
+
+def test_cross_shard_merge_kernels():
+    """oryx_merge_topn_device / oryx_merge_topn_packed: per-shard exact lists -> the global list."""
+    import torch
+    n, f, how_many, shards = 9000, 24, 10, 3
+    y = random_model(n, f, seed=61)
+    q = np.random.default_rng(62).standard_normal(f, dtype=np.float32)
+    per = n // shards
+    dev = torch.device("cuda")
+    rec = ob.packed_record_bytes(how_many)
+    g_rec = torch.zeros(shards * rec, dtype=torch.uint8, device=dev)
+    g_scores = torch.zeros((shards, how_many), dtype=torch.float64, device=dev)
+    g_rows = torch.zeros((shards, how_many), dtype=torch.int32, device=dev)
+    g_n = torch.zeros(shards, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    with ob.Model(f) as m:
+        for sidx in range(shards):
+            # shard 2 holds only 4 rows: a short list must merge correctly
+            lo, hi = sidx * per, (sidx * per + 4 if sidx == 2 else (sidx + 1) * per)
+            if sidx > 0:
+                m.remove(ob.Y, np.arange(0, per, dtype=np.int32))
+            m.upsert(ob.Y, np.arange(hi - lo, dtype=np.int32), y[lo:hi])
+            r = g_rec[sidx * rec:(sidx + 1) * rec]
+            d_q = torch.from_numpy(q).to(dev)
+            m.topn_device(ob.DOT, d_q.data_ptr(), how_many, r[how_many * 8:].data_ptr(), r.data_ptr(),
+                          r[how_many * 12:].data_ptr(), stream.cuda_stream)
+            stream.synchronize()
+            g_scores[sidx] = r[: how_many * 8].view(torch.float64)
+            g_rows[sidx] = r[how_many * 8: how_many * 12].view(torch.int32)
+            g_n[sidx] = r[how_many * 12: how_many * 12 + 4].view(torch.int32)[0]
+    keep = np.ones(n, bool)
+    keep[2 * per + 4:] = False
+    part = np.where(keep, 0, -1).astype(np.int32)
+    e_rows, e_scores = oracle.topn(oracle.DOT, q, y, how_many, part=part)
+    for packed in (False, True):
+        o_rows = torch.zeros(how_many, dtype=torch.int64, device=dev)
+        o_scores = torch.zeros(how_many, dtype=torch.float64, device=dev)
+        o_n = torch.zeros(1, dtype=torch.int32, device=dev)
+        if packed:
+            ob.merge_topn_packed(g_rec.data_ptr(), shards, rec, how_many, per, o_rows.data_ptr(),
+                                 o_scores.data_ptr(), o_n.data_ptr(), stream.cuda_stream)
+        else:
+            ob.merge_topn_device(g_scores.data_ptr(), g_rows.data_ptr(), g_n.data_ptr(), shards, how_many, per,
+                                 o_rows.data_ptr(), o_scores.data_ptr(), o_n.data_ptr(), stream.cuda_stream)
+        stream.synchronize()
+        assert int(o_n.item()) == how_many
+        assert np.array_equal(o_rows.cpu().numpy(), e_rows) and np.array_equal(o_scores.cpu().numpy(), e_scores)
