@@ -421,7 +421,30 @@ int32_t oryx_topn_batch(oryx_model* mh, int32_t kind, const float* queries, int3
   int32_t rc = ORYX_OK;
   {
     std::shared_lock<std::shared_mutex> lk(m->mu);
+    Store* s = &m->store[ORYX_Y];
+    bool batched = false;
+    if (batch_topn_supported(m, nq)) {
+      // exclusion rows -> sorted slots, CSR per query
+      std::vector<int32_t> eo, es;
+      if (excl_offsets && excl_rows) {
+        eo.resize((size_t)nq + 1, 0);
+        for (int32_t i = 0; i < nq; i++) {
+          size_t begin = es.size();
+          for (int32_t j = excl_offsets[i]; j < excl_offsets[i + 1]; j++) {
+            int32_t r = excl_rows[j];
+            if (r >= 0 && (size_t)r < s->row2slot.size() && s->row2slot[r] >= 0) es.push_back(s->row2slot[r]);
+          }
+          std::sort(es.begin() + begin, es.end());
+          eo[i + 1] = (int32_t)es.size();
+        }
+      }
+      rc = batch_topn_run(m, kind, queries, nq, how_many, eo.empty() ? nullptr : eo.data(),
+                          es.empty() ? nullptr : es.data(), out_rows, out_scores, out_n, c->stream, &m->last_batch);
+      batched = rc == ORYX_OK;
+      if (rc == ORYX_E_NOMEM) rc = ORYX_OK;  // not enough scratch for the tensor-core path: answer one by one
+    }
     for (int32_t i = 0; i < nq && rc == ORYX_OK; i++) {
+      if (batched && out_n[i] >= 0) continue;  // -1 marks a query the batched path handed back
       const int32_t* ex = nullptr;
       int32_t nex = 0;
       if (excl_offsets && excl_rows) {
@@ -435,6 +458,17 @@ int32_t oryx_topn_batch(oryx_model* mh, int32_t kind, const float* queries, int3
   if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
   ctx_release(m, c);
   return rc;
+}
+
+// Development aid (not in the public header): phase timings (ms) and flops of the last tensor-core batch.
+int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {
+  Model* m = reinterpret_cast<Model*>(mh);
+  out5[0] = m->last_batch.convert_ms;
+  out5[1] = m->last_batch.score_ms;
+  out5[2] = m->last_batch.threshold_ms;
+  out5[3] = m->last_batch.refine_ms;
+  out5[4] = m->last_batch.flops;
+  return ORYX_OK;
 }
 
 int32_t oryx_scores_all(oryx_model* mh, int32_t kind, const float* query, int32_t n_rows, double* out_scores) {

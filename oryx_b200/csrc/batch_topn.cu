@@ -1,0 +1,746 @@
+// batch_topn.cu -- batched top-N over the whole item store on the 5th-generation tensor cores
+// (kernel K3 of SURVEY.md section 2.3).
+//
+// The reference has no batched call: concurrent /recommend requests, /recommendToMany-style fan-outs
+// and the PopularRepresentativeItems loop each run ALSServingModel.topN once per query
+// (ALSServingModel.java:289-335, PopularRepresentativeItems.java:52-57).  oryx_topn_batch answers nq
+// such calls at once; per query the result is the same list the single-query path returns.
+//
+// Y is read once per batch instead of once per query, so the work is a dense contraction S = Q Y^T
+// (2*nq*N*F flops) and belongs on tcgen05.  The 4096 x 10M score matrix is never materialised:
+//
+//   1. convert   Y (fp32 store) and Q -> bf16 scratch, K padded to 64; per-row norms give a rigorous
+//                bound on what bf16 rounding can do to a score:
+//                |s_bf16 - s| <= delta_q = 2^-7 (1 + 2^-9) ||q|| max_j ||y_j||  (unit roundoff of bf16 is
+//                2^-8 per operand; Cauchy-Schwarz over the products; fp32 accumulation adds < 1 %).
+//   2. score     batch_score_kernel: persistent, warp-specialised.  One warp drives TMA
+//                (cp.async.bulk.tensor, 128-byte swizzle), one thread issues tcgen05.mma
+//                (cta_group::1, kind::f16, M=128 queries x N=256 items x K=16, accumulators in TMEM,
+//                two accumulator stages), four warps run the epilogue: tcgen05.ld the accumulator
+//                and keep only the MAXIMUM of every 32-item sub-block per query -> bmax[nq][N/32]
+//                (1/32 of the scores, written with full-sector stores).  The Y tile stays resident in
+//                shared memory while all query tiles stream past it.
+//   3. threshold per query: T' = k-th largest sub-block maximum (k sub-blocks each hold an item with
+//                bf16 score >= T', so the true k-th best exact score is >= T' - delta).  Every item of
+//                the true top k therefore lives in a sub-block whose maximum is >= T' - 2 delta: those
+//                sub-blocks are the candidates (typically ~1.2 k of them).
+//   4. refine    one CTA per query re-scores the candidate sub-blocks in fp32 straight from the fp32
+//                store, keeps the k best, re-scores those with the reference's exact arithmetic and
+//                ranks them -- the same finishing pass as the single-query path, so both paths return
+//                identical rows and bit-identical scores.
+//
+// Candidate pruning is exact (the bound is rigorous), so unlike a plain reduced-precision scorer
+// this path needs no recall caveat: recall@N against the fp32 path is 1.0 by construction, and the
+// tests check it.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace oryx {
+
+namespace {
+
+constexpr int BM = 128;        // queries per Q tile (UMMA M)
+constexpr int BN = 256;        // items per Y tile (UMMA N)
+constexpr int BK = 64;         // bf16 elements per K chunk = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int QSTAGES = 4;     // Q chunk ring
+constexpr int SUB = 32;        // items per sub-block whose maximum is kept
+constexpr int SUBS_PER_TILE = BN / SUB;  // 8
+constexpr int kScoreThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
+constexpr uint32_t Y_CHUNK_BYTES = BN * BK * 2;  // 32 KB
+constexpr uint32_t Q_CHUNK_BYTES = BM * BK * 2;  // 16 KB
+
+// ---------------------------------------------------------------- PTX wrappers (sm_100a)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate, issued by one thread.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major operand tile, 128-byte swizzle, 8-row atoms packed 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);   // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                       // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset between 8-row atoms
+  d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=256.
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---------------------------------------------------------------- step 1: conversions
+// Y fp32 [n x fpad] -> bf16 [n x kpad] (zero padded), and the largest row norm.  One warp per row.
+// For the cosine score (dot(q, y) / ||y||, CosineAverageFunction.java:54-56) rows are divided by their
+// norm first, so the tensor-core pass scores q . (y/||y||) and every "row norm" is 1.
+__global__ void convert_y_kernel(const float* __restrict__ y, int64_t n, int fpad, int features, int kpad,
+                                 int normalize, __nv_bfloat16* __restrict__ out,
+                                 unsigned int* __restrict__ max_norm_bits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  float local_max = 0.f;
+  for (int64_t row = w0; row < n; row += stride) {
+    const float* src = y + row * fpad;
+    __nv_bfloat16* dst = out + row * kpad;
+    float ss = 0.f;
+    for (int j = lane; j < features; j += 32) { float v = src[j]; ss = fmaf(v, v, ss); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float scale = normalize ? rsqrtf(ss) : 1.0f;  // zero row: inf -> NaN entries, never selected
+    for (int j = lane; j < kpad; j += 32) {
+      float v = j < features ? src[j] * scale : 0.f;
+      if (normalize && j >= features) v = 0.f;
+      dst[j] = __float2bfloat16_rn(v);
+    }
+    if (ss == ss) local_max = fmaxf(local_max, normalize ? 1.0002f : ss);  // tombstones are NaN rows: ignore
+  }
+  // sqrt is monotone: keep the max of squared norms (non-negative floats order like their bit patterns)
+  if (lane == 0) atomicMax(max_norm_bits, __float_as_uint(local_max));
+}
+
+// Q fp32 [nq x features] -> bf16 [nq_pad x kpad] (zero padded rows and columns), and ||q|| per row.
+__global__ void convert_q_kernel(const float* __restrict__ q, int nq, int nq_pad, int features, int kpad,
+                                 __nv_bfloat16* __restrict__ out, float* __restrict__ qnorm) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= nq_pad) return;
+  float ss = 0.f;
+  for (int j = lane; j < kpad; j += 32) {
+    float v = (row < nq && j < features) ? q[(size_t)row * features + j] : 0.f;
+    ss = fmaf(v, v, ss);
+    out[(size_t)row * kpad + j] = __float2bfloat16_rn(v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  if (lane == 0) qnorm[row] = sqrtf(ss);
+}
+
+// ---------------------------------------------------------------- step 2: tensor-core scoring
+struct ScoreSmem {
+  // dynamic shared memory, 1024-byte aligned: [YB][NCH] Y chunks, [QSTAGES] Q chunks, then barriers
+  static __host__ __device__ size_t bytes(int nch, int yb) {
+    return (size_t)yb * nch * Y_CHUNK_BYTES + (size_t)QSTAGES * Q_CHUNK_BYTES + 256 + 1024;
+  }
+};
+
+template <int NCH>
+__global__ void __launch_bounds__(kScoreThreads, 1)
+batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_y,
+                   int n_qtiles, int n_ytiles, int64_t n_slots, float* __restrict__ bmax, int64_t bmax_stride) {
+  constexpr int YB = (NCH <= 2) ? 2 : 1;  // double-buffer the resident Y tile when it fits
+  extern __shared__ unsigned char smem_dyn[];
+  unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+  unsigned char* ybuf = base;                                            // [YB][NCH][32 KB]
+  unsigned char* qbuf = base + (size_t)YB * NCH * Y_CHUNK_BYTES;         // [QSTAGES][16 KB]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(qbuf + (size_t)QSTAGES * Q_CHUNK_BYTES);
+  uint64_t* y_full = bars;                 // [2]
+  uint64_t* y_empty = bars + 2;            // [2]
+  uint64_t* q_full = bars + 4;             // [QSTAGES]
+  uint64_t* q_empty = bars + 4 + QSTAGES;  // [QSTAGES]
+  uint64_t* t_full = bars + 4 + 2 * QSTAGES;   // [2]
+  uint64_t* t_empty = bars + 6 + 2 * QSTAGES;  // [2]
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 8 + 2 * QSTAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_q) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_y) : "memory");
+    for (int i = 0; i < 2; i++) { mbar_init(&y_full[i], 1); mbar_init(&y_empty[i], 1); }
+    for (int i = 0; i < QSTAGES; i++) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
+    for (int i = 0; i < 2; i++) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM: all 512 columns = two 128 x 256 fp32 accumulators
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_holder)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t qs = 0, qphase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < n_ytiles; t += gridDim.x, it++) {
+        const int yb = it % YB;
+        const uint32_t yph = (uint32_t)(it / YB) & 1u;
+        mbar_wait(&y_empty[yb], yph ^ 1u);
+        mbar_expect_tx(&y_full[yb], NCH * Y_CHUNK_BYTES);
+#pragma unroll
+        for (int c = 0; c < NCH; c++)
+          tma_load_2d(ybuf + ((size_t)yb * NCH + c) * Y_CHUNK_BYTES, &tm_y, c * BK, t * BN, &y_full[yb]);
+        for (int qt = 0; qt < n_qtiles; qt++) {
+#pragma unroll
+          for (int c = 0; c < NCH; c++) {
+            mbar_wait(&q_empty[qs], qphase ^ 1u);
+            mbar_expect_tx(&q_full[qs], Q_CHUNK_BYTES);
+            tma_load_2d(qbuf + (size_t)qs * Q_CHUNK_BYTES, &tm_q, c * BK, qt * BM, &q_full[qs]);
+            if (++qs == QSTAGES) { qs = 0; qphase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      uint32_t qs = 0, qphase = 0;
+      int it = 0, acc_it = 0;
+      for (int t = blockIdx.x; t < n_ytiles; t += gridDim.x, it++) {
+        const int yb = it % YB;
+        const uint32_t yph = (uint32_t)(it / YB) & 1u;
+        mbar_wait(&y_full[yb], yph);
+        for (int qt = 0; qt < n_qtiles; qt++, acc_it++) {
+          const int acc = acc_it & 1;
+          const uint32_t aph = (uint32_t)(acc_it >> 1) & 1u;
+          mbar_wait(&t_empty[acc], aph ^ 1u);
+          tcgen05_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
+#pragma unroll
+          for (int c = 0; c < NCH; c++) {
+            mbar_wait(&q_full[qs], qphase);
+            tcgen05_fence_after();
+            const uint32_t a_addr = smem_u32(qbuf + (size_t)qs * Q_CHUNK_BYTES);
+            const uint32_t b_addr = smem_u32(ybuf + ((size_t)yb * NCH + c) * Y_CHUNK_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; k++) {
+              const uint64_t a_desc = umma_desc_k_sw128(a_addr + k * UMMA_K * 2);
+              const uint64_t b_desc = umma_desc_k_sw128(b_addr + k * UMMA_K * 2);
+              umma_bf16(d_tmem, a_desc, b_desc, kIdesc, (uint32_t)((c | k) != 0));
+            }
+            tcgen05_commit(&q_empty[qs]);  // the Q stage is free once these MMAs have read it
+            if (++qs == QSTAGES) { qs = 0; qphase ^= 1u; }
+          }
+          tcgen05_commit(&t_full[acc]);    // accumulator ready for the epilogue
+        }
+        tcgen05_commit(&y_empty[yb]);      // every MMA that reads this Y tile has been issued before this commit
+      }
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> sub-block maxima =====
+    const int w4 = warp & 3;  // TMEM lane quarter this warp may read
+    int acc_it = 0;
+    for (int t = blockIdx.x; t < n_ytiles; t += gridDim.x) {
+      const int64_t col0 = (int64_t)t * BN;
+      const bool ragged = col0 + BN > n_slots;
+      for (int qt = 0; qt < n_qtiles; qt++, acc_it++) {
+        const int acc = acc_it & 1;
+        const uint32_t aph = (uint32_t)(acc_it >> 1) & 1u;
+        mbar_wait(&t_full[acc], aph);
+        tcgen05_fence_after();
+        float mx[SUBS_PER_TILE];
+#pragma unroll
+        for (int j = 0; j < SUBS_PER_TILE; j++) {
+          uint32_t r[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(w4 * 32) << 16) + (uint32_t)(acc * BN + j * SUB);
+          tmem_ld_32x32b_x32(taddr, r);
+          tmem_ld_wait();
+          float m = -INFINITY;
+          if (!ragged) {
+#pragma unroll
+            for (int i = 0; i < 32; i++) m = fmaxf(m, __uint_as_float(r[i]));  // fmaxf drops NaN (tombstones)
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+              const float v = __uint_as_float(r[i]);
+              if (col0 + j * SUB + i < n_slots) m = fmaxf(m, v);
+            }
+          }
+          mx[j] = m;
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[acc]);  // accumulator drained (4 warps arrive)
+        const int64_t q = (int64_t)qt * BM + w4 * 32 + lane;
+        float4* dst = reinterpret_cast<float4*>(bmax + q * bmax_stride + (int64_t)t * SUBS_PER_TILE);
+        dst[0] = make_float4(mx[0], mx[1], mx[2], mx[3]);
+        dst[1] = make_float4(mx[4], mx[5], mx[6], mx[7]);
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------- step 3: thresholds and candidates
+constexpr int kThrThreads = 256;
+constexpr int kTopPerThread = 4;     // 256 x 4 = 1024 >= largest k
+constexpr int kCollectCap = 4096;    // sub-blocks above the first cut, staged in shared memory
+
+// One CTA per query.  cand[q][0..cand_cap) receives candidate sub-block ids, cand_n[q] their number
+// (or -1 when more than cand_cap sub-blocks qualified: the host re-runs that query unbatched).
+__global__ void __launch_bounds__(kThrThreads)
+batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, int n_sub, int k,
+                       const float* __restrict__ qnorm, const unsigned int* __restrict__ max_norm_sq_bits,
+                       int32_t* __restrict__ cand, int cand_cap, int32_t* __restrict__ cand_n) {
+  __shared__ float s_top[kThrThreads * kTopPerThread];
+  __shared__ float s_val[kCollectCap];
+  __shared__ int32_t s_id[kCollectCap];
+  __shared__ unsigned int s_count, s_out;
+  __shared__ float s_lb, s_t;
+  const int q = blockIdx.x, tid = threadIdx.x;
+  const float* row = bmax + (int64_t)q * bmax_stride;
+  // rigorous bound on |bf16 score - exact score| for this query (see file header)
+  const float delta = 0.0078125f * 1.01f * qnorm[q] * sqrtf(__uint_as_float(*max_norm_sq_bits));
+
+  // pass A: every thread keeps the 4 largest values of its strided share
+  float top[kTopPerThread];
+#pragma unroll
+  for (int j = 0; j < kTopPerThread; j++) top[j] = -INFINITY;
+  for (int i = tid; i < n_sub; i += kThrThreads) {
+    float v = row[i];
+    if (v > top[kTopPerThread - 1]) {
+      top[kTopPerThread - 1] = v;
+#pragma unroll
+      for (int j = kTopPerThread - 1; j > 0; j--) {
+        if (top[j] > top[j - 1]) { float t = top[j]; top[j] = top[j - 1]; top[j - 1] = t; }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kTopPerThread; j++) s_top[tid * kTopPerThread + j] = top[j];
+  if (tid == 0) { s_count = 0u; s_out = 0u; }
+  __syncthreads();
+  // lower bound of the k-th largest value: the k-th largest of these 1024 (rank count; ties by index)
+  {
+    const int m = kThrThreads * kTopPerThread;
+    const int kk = min(k, m);
+    for (int e = tid; e < m; e += kThrThreads) {
+      const float v = s_top[e];
+      int rank = 0;
+      for (int j = 0; j < m; j++) {
+        const float u = s_top[j];
+        rank += (u > v || (u == v && j < e)) ? 1 : 0;
+      }
+      if (rank == kk - 1) s_lb = v;
+    }
+  }
+  __syncthreads();
+  const float lb = s_lb;  // -inf when fewer than k finite values exist: then everything is collected
+  const float cut1 = lb - 2.0f * delta;
+
+  // pass B: collect every sub-block at or above the first cut
+  for (int i = tid; i < n_sub; i += kThrThreads) {
+    float v = row[i];
+    if (v >= cut1 && v > -INFINITY) {
+      unsigned pos = atomicAdd(&s_count, 1u);
+      if (pos < (unsigned)kCollectCap) { s_val[pos] = v; s_id[pos] = i; }
+    }
+  }
+  __syncthreads();
+  const int n = (int)s_count;
+  if (n > kCollectCap) {
+    if (tid == 0) cand_n[q] = -1;
+    return;
+  }
+  // exact k-th largest sub-block maximum T' among the collected ones (they include everything >= lb)
+  {
+    const int kk = min(k, n);
+    if (tid == 0) s_t = -INFINITY;
+    __syncthreads();
+    for (int e = tid; e < n; e += kThrThreads) {
+      const float v = s_val[e];
+      int rank = 0;
+      for (int j = 0; j < n; j++) {
+        const float u = s_val[j];
+        rank += (u > v || (u == v && j < e)) ? 1 : 0;
+      }
+      if (rank == kk - 1) s_t = v;
+    }
+    __syncthreads();
+  }
+  const float cut2 = (n >= k) ? s_t - 2.0f * delta : -INFINITY;
+  int32_t* out = cand + (int64_t)q * cand_cap;
+  for (int e = tid; e < n; e += kThrThreads) {
+    if (s_val[e] >= cut2) {
+      unsigned pos = atomicAdd(&s_out, 1u);
+      if (pos < (unsigned)cand_cap) out[pos] = s_id[e];
+    }
+  }
+  __syncthreads();
+  if (tid == 0) cand_n[q] = (int)s_out > cand_cap ? -1 : (int)s_out;
+}
+
+// ---------------------------------------------------------------- step 4: refine
+constexpr int kRefineThreads = 256;
+
+__device__ __forceinline__ bool excluded_slot(const int32_t* excl, int n, int32_t slot) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) {
+    int mid = (lo + hi) >> 1;
+    int32_t v = __ldg(excl + mid);
+    if (v == slot) return true;
+    if (v < slot) lo = mid + 1; else hi = mid - 1;
+  }
+  return false;
+}
+
+// One CTA per query: fp32 scores of every row of the candidate sub-blocks (one warp per sub-block,
+// one lane per row -- sub-blocks are few, this phase is small), the k best kept in a shared
+// candidate array, then the exact finishing pass.  Same selection rule and the same exact arithmetic
+// as scan_topn.cu, so results are identical to the single-query path.
+__global__ void __launch_bounds__(kRefineThreads)
+batch_refine_kernel(const float* __restrict__ y, const int32_t* __restrict__ slot_row, int64_t n_slots, int fpad,
+                    int features, const float* __restrict__ queries, int kind, int k, int how_many,
+                    const int32_t* __restrict__ cand, int cand_cap, const int32_t* __restrict__ cand_n,
+                    const int32_t* __restrict__ excl_offsets, const int32_t* __restrict__ excl_slots,
+                    int32_t* __restrict__ out_rows, double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // layout: q[fpad] f32 | arr[k] u64 | exact[k] f64 | rows[k] i32
+  float* s_q = reinterpret_cast<float*>(smem_raw);
+  unsigned long long* arr = reinterpret_cast<unsigned long long*>(smem_raw + (((size_t)fpad * 4 + 15) & ~(size_t)15));
+  double* s_exact = reinterpret_cast<double*>(arr + k);
+  int32_t* s_rows = reinterpret_cast<int32_t*>(s_exact + k);
+  __shared__ unsigned int s_thr_key;
+  const int qi = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nc = cand_n[qi];
+  if (nc < 0) {  // overflow in the threshold step: the host answers this query unbatched
+    if (tid == 0) out_n[qi] = -1;
+    return;
+  }
+  for (int j = tid; j < fpad; j += kRefineThreads) s_q[j] = j < features ? queries[(size_t)qi * features + j] : 0.f;
+  for (int i = tid; i < k; i += kRefineThreads) arr[i] = 0ull;
+  if (tid == 0) s_thr_key = 0u;
+  __syncthreads();
+  const int32_t* excl = excl_offsets ? excl_slots + excl_offsets[qi] : nullptr;
+  const int n_excl = excl_offsets ? excl_offsets[qi + 1] - excl_offsets[qi] : 0;
+  const int32_t* my_cand = cand + (int64_t)qi * cand_cap;
+
+  for (int c = warp; c < nc; c += kRefineThreads / 32) {
+    const int64_t slot = (int64_t)my_cand[c] * SUB + lane;
+    float acc = 0.f, nrm = 0.f;
+    const bool in = slot < n_slots;
+    if (in) {
+      const float4* r4 = reinterpret_cast<const float4*>(y + slot * fpad);
+      const float4* q4 = reinterpret_cast<const float4*>(s_q);
+      for (int j = 0; j < (fpad >> 2); j++) {
+        const float4 a = __ldg(r4 + j);
+        const float4 b = q4[j];
+        acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
+        if (kind == ORYX_COSINE) {
+          nrm = fmaf(a.x, a.x, nrm); nrm = fmaf(a.y, a.y, nrm); nrm = fmaf(a.z, a.z, nrm); nrm = fmaf(a.w, a.w, nrm);
+        }
+      }
+    }
+    const float score = (kind == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc;
+    const uint32_t key = float_key(score);
+    bool hit = in && score == score && key > *(volatile unsigned int*)&s_thr_key;
+    if (hit && n_excl > 0 && excluded_slot(excl, n_excl, (int32_t)slot)) hit = false;
+    unsigned ball = __ballot_sync(0xffffffffu, hit);
+    while (ball != 0u) {
+      const int src = __ffs(ball) - 1;
+      ball &= ball - 1;
+      const uint32_t ky = __shfl_sync(0xffffffffu, key, src);
+      const int32_t sl = __shfl_sync(0xffffffffu, (int32_t)slot, src);
+      // replace-the-minimum with a 64-bit CAS, whole warp searches (as in scan_topn.cu)
+      const unsigned long long x = ((unsigned long long)ky << 32) | (unsigned long long)(uint32_t)sl;
+      for (;;) {
+        unsigned long long best = ~0ull;
+        int best_idx = 0;
+        for (int i = lane; i < k; i += 32) {
+          unsigned long long v = *(const volatile unsigned long long*)(arr + i);
+          if (v < best) { best = v; best_idx = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
+          int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+          if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
+        }
+        if (ky <= (uint32_t)(best >> 32)) {
+          if (lane == 0) atomicMax(&s_thr_key, (uint32_t)(best >> 32));
+          break;
+        }
+        unsigned long long old = 0ull;
+        if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == best) break;
+      }
+    }
+  }
+  __syncthreads();
+
+  // exact re-score (one thread per kept row here: k rows, short chains run side by side)
+  __shared__ int s_nsel;
+  if (tid == 0) s_nsel = 0;
+  __syncthreads();
+  for (int i = tid; i < k; i += kRefineThreads) {
+    const unsigned long long v = arr[i];
+    if ((v >> 32) == 0ull) continue;
+    const int32_t slot = (int32_t)(uint32_t)v;
+    const float* r = y + (int64_t)slot * fpad;
+    double dot = 0.0, tot = 0.0;
+    for (int j = 0; j < features; j++) {
+      const float yv = r[j];
+      dot = exact_step(dot, s_q[j], yv);
+      if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+    }
+    const int pos = atomicAdd(&s_nsel, 1);
+    s_exact[pos] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
+    s_rows[pos] = __ldg(slot_row + slot);
+  }
+  __syncthreads();
+  const int nsel = s_nsel;
+  const int n_out = min(nsel, how_many);
+  for (int i = tid; i < nsel; i += kRefineThreads) {
+    const double si = s_exact[i];
+    const int32_t ri = s_rows[i];
+    const bool nan_i = si != si;
+    int rank = 0;
+    for (int j = 0; j < nsel; j++) {
+      const double sj = s_exact[j];
+      const bool nan_j = sj != sj;
+      const int32_t rj = s_rows[j];
+      bool better;
+      if (nan_j) better = nan_i && rj < ri;
+      else if (nan_i) better = true;
+      else better = (sj > si) || (sj == si && rj < ri);
+      rank += better ? 1 : 0;
+    }
+    if (rank < n_out) {
+      out_rows[(size_t)qi * how_many + rank] = ri;
+      out_scores[(size_t)qi * how_many + rank] = si;
+    }
+  }
+  if (tid == 0) out_n[qi] = n_out;
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// bf16 row-major [rows x kpad] matrix, box = {64 elements (128 B), box_rows}, 128-byte swizzle.
+int32_t make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t kpad, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return ORYX_E_CUDA;
+  }
+  cuuint64_t dims[2] = {kpad, rows};
+  cuuint64_t strides[1] = {kpad * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return ORYX_E_CUDA;
+  }
+  return ORYX_OK;
+}
+
+template <int NCH>
+int32_t launch_score(const CUtensorMap& tq, const CUtensorMap& ty, int n_qtiles, int n_ytiles, int64_t n_slots,
+                     float* bmax, int64_t bmax_stride, int num_sms, cudaStream_t st) {
+  constexpr int YB = (NCH <= 2) ? 2 : 1;
+  const size_t smem = ScoreSmem::bytes(NCH, YB);
+  static bool configured = false;
+  if (!configured) {
+    ORYX_CUDA(cudaFuncSetAttribute(batch_score_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const int grid = std::min(num_sms, n_ytiles);
+  batch_score_kernel<NCH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { cudaFree(p); }
+  int32_t alloc(size_t bytes) {
+    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+      set_error("device allocation of %zu bytes failed (batched top-N scratch)", bytes);
+      return ORYX_E_NOMEM;
+    }
+    return ORYX_OK;
+  }
+};
+
+}  // namespace
+
+bool batch_topn_supported(Model* m, int nq) {
+  Store* s = &m->store[ORYX_Y];
+  const bool lsh = s->hashed && m->num_hashes != m->max_bits;
+  const int kpad = round_up(s->features, BK);
+  return !lsh && kpad <= 256 && nq >= 32 && s->n_slots >= 4096 && encode_tiled_fn() != nullptr;
+}
+
+// queries: HOST [nq x features].  Outputs: HOST arrays.  out_n[i] == -1 marks a query the caller must
+// answer unbatched (candidate overflow; pathological score distributions only).
+int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
+                       const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
+                       cudaStream_t st, BatchTimings* timings) {
+  Store* s = &m->store[ORYX_Y];
+  const int F = s->features, fpad = s->fpad;
+  const int kpad = round_up(F, BK), nch = kpad / BK;
+  const int k = how_many + kTopnMargin;
+  const int nq_pad = round_up(nq, BM);
+  const int n_qtiles = nq_pad / BM;
+  const int64_t n = s->n_slots;
+  const int n_ytiles = (int)((n + BN - 1) / BN);
+  const int n_sub = n_ytiles * SUBS_PER_TILE;
+  const int64_t bmax_stride = n_sub;
+  const int cand_cap = 4096;
+
+  DevBuf d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
+  ORYX_TRY(d_ybf.alloc((size_t)n * kpad * 2));
+  ORYX_TRY(d_qbf.alloc((size_t)nq_pad * kpad * 2));
+  ORYX_TRY(d_q.alloc((size_t)nq * F * 4));
+  ORYX_TRY(d_qnorm.alloc((size_t)nq_pad * 4));
+  ORYX_TRY(d_maxn.alloc(4));
+  ORYX_TRY(d_bmax.alloc((size_t)nq_pad * bmax_stride * 4));
+  ORYX_TRY(d_cand.alloc((size_t)nq * cand_cap * 4));
+  ORYX_TRY(d_candn.alloc((size_t)nq * 4));
+  ORYX_TRY(d_orows.alloc((size_t)nq * how_many * 4));
+  ORYX_TRY(d_oscores.alloc((size_t)nq * how_many * 8));
+  ORYX_TRY(d_on.alloc((size_t)nq * 4));
+  const int n_excl_total = excl_offsets ? excl_offsets[nq] : 0;
+  if (excl_offsets) {
+    ORYX_TRY(d_eo.alloc((size_t)(nq + 1) * 4));
+    ORYX_TRY(d_es.alloc((size_t)std::max(n_excl_total, 1) * 4));
+    ORYX_CUDA(cudaMemcpyAsync(d_eo.p, excl_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (n_excl_total > 0)
+      ORYX_CUDA(cudaMemcpyAsync(d_es.p, excl_slots, (size_t)n_excl_total * 4, cudaMemcpyHostToDevice, st));
+  }
+  cudaEvent_t ev[5];
+  for (auto& e : ev) ORYX_CUDA(cudaEventCreate(&e));
+  struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 5; i++) cudaEventDestroy(e[i]); } } evg{ev};
+
+  ORYX_CUDA(cudaMemcpyAsync(d_q.p, queries, (size_t)nq * F * 4, cudaMemcpyHostToDevice, st));
+  ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 4, st));
+  ORYX_CUDA(cudaEventRecord(ev[0], st));
+  convert_y_kernel<<<m->num_sms * 8, 256, 0, st>>>(s->d_vec, n, fpad, F, kpad, kind == ORYX_COSINE ? 1 : 0,
+                                                  (__nv_bfloat16*)d_ybf.p, (unsigned int*)d_maxn.p);
+  convert_q_kernel<<<(nq_pad + 7) / 8, 256, 0, st>>>((const float*)d_q.p, nq, nq_pad, F, kpad,
+                                                    (__nv_bfloat16*)d_qbf.p, (float*)d_qnorm.p);
+  ORYX_CUDA(cudaGetLastError());
+  ORYX_CUDA(cudaEventRecord(ev[1], st));
+
+  CUtensorMap tq, ty;
+  ORYX_TRY(make_map(&tq, d_qbf.p, (uint64_t)nq_pad, (uint64_t)kpad, BM));
+  ORYX_TRY(make_map(&ty, d_ybf.p, (uint64_t)n, (uint64_t)kpad, BN));
+  int32_t rc;
+  switch (nch) {
+    case 1: rc = launch_score<1>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
+    case 2: rc = launch_score<2>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
+    case 3: rc = launch_score<3>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
+    default: rc = launch_score<4>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
+  }
+  ORYX_TRY(rc);
+  ORYX_CUDA(cudaEventRecord(ev[2], st));
+
+  batch_threshold_kernel<<<nq, kThrThreads, 0, st>>>((const float*)d_bmax.p, bmax_stride, n_sub, k,
+                                                    (const float*)d_qnorm.p, (const unsigned int*)d_maxn.p,
+                                                    (int32_t*)d_cand.p, cand_cap, (int32_t*)d_candn.p);
+  ORYX_CUDA(cudaGetLastError());
+  ORYX_CUDA(cudaEventRecord(ev[3], st));
+
+  const size_t rsmem = (((size_t)fpad * 4 + 15) & ~(size_t)15) + (size_t)k * 20 + 16;
+  static bool refine_configured = false;
+  if (!refine_configured) {
+    ORYX_CUDA(cudaFuncSetAttribute(batch_refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    refine_configured = true;
+  }
+  batch_refine_kernel<<<nq, kRefineThreads, rsmem, st>>>(
+      s->d_vec, s->d_slot_row, n, fpad, F, (const float*)d_q.p, kind, k, how_many, (const int32_t*)d_cand.p,
+      cand_cap, (const int32_t*)d_candn.p, excl_offsets ? (const int32_t*)d_eo.p : nullptr,
+      excl_offsets ? (const int32_t*)d_es.p : nullptr, (int32_t*)d_orows.p, (double*)d_oscores.p, (int32_t*)d_on.p);
+  ORYX_CUDA(cudaGetLastError());
+  ORYX_CUDA(cudaEventRecord(ev[4], st));
+  ORYX_CUDA(cudaMemcpyAsync(out_rows, d_orows.p, (size_t)nq * how_many * 4, cudaMemcpyDeviceToHost, st));
+  ORYX_CUDA(cudaMemcpyAsync(out_scores, d_oscores.p, (size_t)nq * how_many * 8, cudaMemcpyDeviceToHost, st));
+  ORYX_CUDA(cudaMemcpyAsync(out_n, d_on.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, st));
+  ORYX_CUDA(cudaStreamSynchronize(st));
+  m->launches += 5;
+  if (timings) {
+    float ms;
+    cudaEventElapsedTime(&ms, ev[0], ev[1]); timings->convert_ms = ms;
+    cudaEventElapsedTime(&ms, ev[1], ev[2]); timings->score_ms = ms;
+    cudaEventElapsedTime(&ms, ev[2], ev[3]); timings->threshold_ms = ms;
+    cudaEventElapsedTime(&ms, ev[3], ev[4]); timings->refine_ms = ms;
+    timings->flops = 2.0 * (double)nq_pad * (double)n_ytiles * BN * (double)kpad;
+  }
+  return ORYX_OK;
+}
+
+}  // namespace oryx

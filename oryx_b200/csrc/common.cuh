@@ -130,6 +130,10 @@ struct QueryCtx {
   int32_t* h_out_n = nullptr;
 };
 
+struct BatchTimings {
+  double convert_ms = 0, score_ms = 0, threshold_ms = 0, refine_ms = 0, flops = 0;
+};
+
 struct Model {
   oryx_config cfg{};
   int device = 0;
@@ -149,6 +153,7 @@ struct Model {
   std::vector<QueryCtx*> pool_free;
   std::vector<std::unique_ptr<QueryCtx>> pool_all;
   int pool_limit = 8;
+  BatchTimings last_batch;  // phase timings of the most recent tensor-core batch (oryx_debug_batch_timings)
   unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
 
@@ -204,6 +209,12 @@ int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const i
 int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_bytes, int how_many,
                                  int64_t row_stride, int64_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
                                  cudaStream_t stream);
+
+// batch_topn.cu
+bool batch_topn_supported(Model* m, int nq);
+int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
+                       const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
+                       cudaStream_t st, BatchTimings* timings);
 
 // gram.cu
 int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);

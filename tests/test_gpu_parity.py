@@ -392,3 +392,29 @@ def test_cross_shard_merge_kernels():
         stream.synchronize()
         assert int(o_n.item()) == how_many
         assert np.array_equal(o_rows.cpu().numpy(), e_rows) and np.array_equal(o_scores.cpu().numpy(), e_scores)
+
+
+@pytest.mark.parametrize("n,f,nq,how_many", [(20000, 128, 64, 10), (9000, 50, 130, 100), (33000, 256, 40, 10),
+                                             (5000, 64, 32, 1)])
+def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
+    """oryx_topn_batch (tcgen05 scoring + exact pruning/refinement) == one exact topN per query."""
+    y = random_model(n, f, seed=n + 7 * f)
+    rng = np.random.default_rng(nq + f)
+    queries = rng.standard_normal((nq, f), dtype=np.float32)
+    queries[3] *= 0.01          # a low-norm query
+    queries[5] = -queries[5]
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        m.remove(ob.Y, [17, 4000])  # tombstones must be ignored by the tensor-core pass as well
+        keep = np.ones(n, bool)
+        keep[[17, 4000]] = False
+        part = np.where(keep, 0, -1).astype(np.int32)
+        for kind in (ob.DOT, ob.COSINE):
+            excl = [rng.integers(0, n, 5).astype(np.int32) if i % 3 == 0 else np.zeros(0, np.int32) for i in range(nq)]
+            rows, scores, cnt = m.topn_batch(kind, queries, how_many, excluded_lists=excl)
+            for i in range(nq):
+                e_rows, e_scores = oracle.topn(kind, queries[i], y, how_many, part=part,
+                                               excluded=np.unique(excl[i]) if len(excl[i]) else None)
+                assert cnt[i] == len(e_rows), (i, cnt[i], len(e_rows))
+                _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), (e_rows, e_scores),
+                                  oracle.scores_all(kind, queries[i], y))
