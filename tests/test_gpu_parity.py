@@ -418,3 +418,21 @@ def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
                 assert cnt[i] == len(e_rows), (i, cnt[i], len(e_rows))
                 _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), (e_rows, e_scores),
                                   oracle.scores_all(kind, queries[i], y))
+
+
+@pytest.mark.parametrize("n,f", [(70000, 100), (66000, 256)])
+def test_gram_large_store_fast_path(n, f):
+    """Stores of >= 65536 slots use fp32-FMA tiles with binary64 flushes; agreement with the exact
+    float-multiply / double-accumulate Gram must stay far below what Solver.solveFToF's float output
+    can resolve (tolerance 1e-8 relative to the largest entry)."""
+    y = random_model(n, f, seed=n + f) * 0.3
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        m.remove(ob.Y, [5, 60000])
+        g, used = m.gram(ob.Y)
+        keep = np.ones(n, bool)
+        keep[[5, 60000]] = False
+        exp = oracle.transpose_times_self(y[keep])
+        assert used == n - 2
+        assert np.max(np.abs(g - exp)) <= 1e-8 * np.max(np.abs(exp))
+        assert np.array_equal(g, g.T)

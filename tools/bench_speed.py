@@ -1,0 +1,32 @@
+"""C4 measurement: YtY Gram over n x f items, solver, and a batch of computeUpdatedXu fold-ins."""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import oryx_b200 as ob
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
+F = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+n_upd = int(sys.argv[3]) if len(sys.argv) > 3 else 1_000_000
+dev = torch.device("cuda", 0)
+m = ob.Model(F, capacity_hint=n)
+g = torch.Generator(device=dev); g.manual_seed(5)
+for off in range(0, n, 1_000_000):
+    c = min(1_000_000, n - off)
+    blk = torch.randn((c, F), generator=g, device=dev) * 0.1; torch.cuda.synchronize()
+    m.upsert_device(ob.Y, off, blk.data_ptr(), c)
+    del blk
+out = {}
+for rep in range(2):
+    t0 = time.perf_counter(); G, used = m.gram(ob.Y); out["gram_ms"] = (time.perf_counter() - t0) * 1e3
+out["gram_gbps_algorithmic"] = n * F * 4 / (out["gram_ms"] * 1e-3) / 1e9
+out["gram_tflops"] = 2.0 * n * F * F / (out["gram_ms"] * 1e-3) / 1e12
+t0 = time.perf_counter(); s = ob.Solver(G); out["solver_create_ms"] = (time.perf_counter() - t0) * 1e3
+rng = np.random.default_rng(1)
+xu = (rng.standard_normal((n_upd, F), dtype=np.float32) * 0.1)
+yi = (rng.standard_normal((n_upd, F), dtype=np.float32) * 0.1)
+vals = np.ones(n_upd)
+for rep in range(2):
+    t0 = time.perf_counter(); o, v = s.fold_in_batch(True, xu, None, yi, vals); out["fold_in_ms_wall_host_buffers"] = (time.perf_counter() - t0) * 1e3
+out["fold_in_updates_per_sec"] = n_upd / (out["fold_in_ms_wall_host_buffers"] * 1e-3)
+out["config"] = f"gram {n} x {F}; fold-in {n_upd} x {F}"
+print(json.dumps(out))
