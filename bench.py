@@ -336,7 +336,7 @@ def run_ours(args):
     if world == 1:
         def step_e2e(i):
             return model.topn(ob.DOT, q_host[i % N_QUERIES], HOW_MANY)
-        h2d, d2h = ((F + 3) // 4 * 4) * 4, 4 + HOW_MANY * 4 + HOW_MANY * 8
+        h2d, d2h = ((F + 3) // 4 * 4) * 4, 8 + (HOW_MANY * 4 + 7) // 8 * 8 + HOW_MANY * 8
     else:
         d_qe = torch.zeros(F, dtype=torch.float32, device=dev)
         h_res_rows = torch.zeros(HOW_MANY, dtype=torch.int64).pin_memory()

@@ -26,9 +26,8 @@ void ctx_destroy(QueryCtx* c) {
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter);
-  cudaFree(c->d_main_index); cudaFree(c->d_out_rows); cudaFree(c->d_out_scores); cudaFree(c->d_out_n);
-  cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_rows);
-  cudaFreeHost(c->h_out_scores); cudaFreeHost(c->h_out_n);
+  cudaFree(c->d_main_index); cudaFree(c->d_worklist); cudaFree(c->d_out_n);
+  cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_n);
 }
 
 static int32_t ctx_create(Model* m, QueryCtx* c) {
@@ -46,14 +45,16 @@ static int32_t ctx_create(Model* m, QueryCtx* c) {
   ORYX_CUDA(cudaMemset(c->d_counter, 0, 32 * sizeof(unsigned int)));
   ORYX_CUDA(cudaMalloc(&c->d_main_index, sizeof(int32_t)));
   ORYX_CUDA(cudaMemset(c->d_main_index, 0, sizeof(int32_t)));
-  ORYX_CUDA(cudaMalloc(&c->d_out_rows, (size_t)kMaxK * sizeof(int32_t)));
-  ORYX_CUDA(cudaMalloc(&c->d_out_scores, (size_t)kMaxK * sizeof(double)));
-  ORYX_CUDA(cudaMalloc(&c->d_out_n, sizeof(int32_t)));
+  // one packed result record: [count i32, pad][rows i32 x how_many, padded to 8][scores f64 x how_many]
+  // so a query's result comes back in a single device-to-host copy
+  ORYX_CUDA(cudaMalloc(&c->d_out_n, (size_t)kMaxK * 12 + 16));
+  c->d_out_rows = nullptr;
+  c->d_out_scores = nullptr;
   ORYX_CUDA(cudaMallocHost(&c->h_query, (size_t)fpad * sizeof(float)));
   ORYX_CUDA(cudaMallocHost(&c->h_excl, (size_t)c->excl_cap * sizeof(int32_t)));
-  ORYX_CUDA(cudaMallocHost(&c->h_out_rows, (size_t)kMaxK * sizeof(int32_t)));
-  ORYX_CUDA(cudaMallocHost(&c->h_out_scores, (size_t)kMaxK * sizeof(double)));
-  ORYX_CUDA(cudaMallocHost(&c->h_out_n, sizeof(int32_t)));
+  ORYX_CUDA(cudaMallocHost(&c->h_out_n, (size_t)kMaxK * 12 + 16));
+  c->h_out_rows = nullptr;
+  c->h_out_scores = nullptr;
   return ORYX_OK;
 }
 
@@ -137,29 +138,32 @@ static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query,
       ORYX_CUDA(cudaMemcpyAsync(c->d_excl, c->h_excl, (size_t)n_excl_slots * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     }
   }
+  // packed result record (see ctx_create)
+  const size_t rows_off = 8, scores_off = 8 + (((size_t)how_many * 4 + 7) & ~(size_t)7);
+  const size_t rec_bytes = scores_off + (size_t)how_many * 8;
+  unsigned char* d_rec = reinterpret_cast<unsigned char*>(c->d_out_n);
+  unsigned char* h_rec = reinterpret_cast<unsigned char*>(c->h_out_n);
   TopnRequest rq{};
   rq.kind = kind;
   rq.d_query = c->d_query;
   rq.how_many = how_many;
   rq.d_excl = c->d_excl;
   rq.n_excl = n_excl_slots;
-  rq.d_out_rows = c->d_out_rows;
-  rq.d_out_scores = c->d_out_scores;
-  rq.d_out_n = c->d_out_n;
+  rq.d_out_n = reinterpret_cast<int32_t*>(d_rec);
+  rq.d_out_rows = reinterpret_cast<int32_t*>(d_rec + rows_off);
+  rq.d_out_scores = reinterpret_cast<double*>(d_rec + scores_off);
   ORYX_CUDA(cudaEventRecord(c->ev0, c->stream));
   ORYX_TRY(scan_topn_launch(m, c, rq, c->stream));
   ORYX_CUDA(cudaEventRecord(c->ev1, c->stream));
-  ORYX_CUDA(cudaMemcpyAsync(c->h_out_n, c->d_out_n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-  ORYX_CUDA(cudaMemcpyAsync(c->h_out_rows, c->d_out_rows, (size_t)how_many * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-  ORYX_CUDA(cudaMemcpyAsync(c->h_out_scores, c->d_out_scores, (size_t)how_many * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  ORYX_CUDA(cudaMemcpyAsync(h_rec, d_rec, rec_bytes, cudaMemcpyDeviceToHost, c->stream));
   ORYX_CUDA(cudaStreamSynchronize(c->stream));
-  int32_t n = *c->h_out_n;
+  int32_t n = *reinterpret_cast<int32_t*>(h_rec);
   if (n < 0 || n > how_many) {
     set_error("device returned an impossible result count %d", n);
     return ORYX_E_CUDA;
   }
-  std::memcpy(out_rows, c->h_out_rows, (size_t)n * sizeof(int32_t));
-  std::memcpy(out_scores, c->h_out_scores, (size_t)n * sizeof(double));
+  std::memcpy(out_rows, h_rec + rows_off, (size_t)n * sizeof(int32_t));
+  std::memcpy(out_scores, h_rec + scores_off, (size_t)n * sizeof(double));
   *out_n = n;
   float ms = 0.f;
   if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);

@@ -84,6 +84,7 @@ __device__ __forceinline__ double exact_step(double acc, float a, float b) {
 //             16-byte aligned and can be read with 128-bit loads; padding floats are zero.
 //   slot_row  [cap_slots] int32: caller's row id living in the slot, -1 = empty / tombstone.
 //   slot_part [cap_slots] int32: LSH partition of the row (0 when the store is not hashed), -1 = empty.
+//   block_part [cap_slots/256] int32: partition summary of each 256-slot block (see below).
 // The host keeps row -> slot and a free list; removed slots (tombstones) are NaN-filled and reused.
 struct Store {
   int features = 0;
@@ -93,6 +94,9 @@ struct Store {
   float* d_vec = nullptr;
   int32_t* d_slot_row = nullptr;
   int32_t* d_slot_part = nullptr;
+  // per 256-slot block: the partition shared by all its live rows, -1 if it has no live row, -2 if
+  // mixed.  Lets an LSH-filtered scan skip or stream whole blocks without per-row metadata.
+  int32_t* d_block_part = nullptr;
   int64_t cap_slots = 0;
   int64_t n_slots = 0;  // high-water mark
   int64_t live = 0;
@@ -119,6 +123,11 @@ struct QueryCtx {
   int scratch_sets = 1;
   int flip = 0;
   int32_t* d_main_index = nullptr;
+  // LSH-filtered scans: the candidate (or mixed) 256-slot blocks of the current query, built on the
+  // device right after the query is hashed; [0] = count, [1..] = block ids.  Null in a context that
+  // owns no memory (the scan then tests every block itself).
+  int32_t* d_worklist = nullptr;
+  int64_t worklist_cap = 0;
   int32_t* d_out_rows = nullptr;  // [max_k]
   double* d_out_scores = nullptr; // [max_k]
   int32_t* d_out_n = nullptr;
@@ -162,6 +171,7 @@ struct Model {
   std::atomic<double> last_query_ms{0.0};
 };
 
+constexpr int kBlockRows = 256;                    // slots per block_part entry
 constexpr int kTopnMargin = 8;                      // extra candidates re-scored exactly
 constexpr int kMaxK = ORYX_MAX_HOW_MANY + kTopnMargin;  // 1024
 constexpr int kMaxGrid = 148 * 8;
@@ -181,6 +191,7 @@ int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits);
 // Hash n packed rows (row stride `stride` floats) on `stream`; writes int32 partition per row.
 int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int stride, int32_t* d_out,
                              cudaStream_t stream);
+int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream);
 int32_t lsh_candidates_device(Model* m, const int32_t* d_main_index, int32_t* d_out, int32_t* d_out_n,
                               cudaStream_t stream);
 

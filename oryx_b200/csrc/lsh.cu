@@ -120,6 +120,29 @@ __global__ void lsh_candidates_kernel(int num_hashes, int max_bits, const int32_
   }
 }
 
+// Work list of an LSH-filtered scan: ids of the 256-slot blocks that hold (or may hold) rows of a
+// candidate partition.  worklist[0] is the count (zeroed by the launcher), worklist[1..] the ids, in
+// no particular order.
+__global__ void lsh_worklist_kernel(const int32_t* __restrict__ block_part, int64_t n_blocks,
+                                    const int32_t* __restrict__ main_index, int max_bits,
+                                    int32_t* __restrict__ worklist) {
+  const int main_idx = *main_index;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_blocks; b += (int64_t)gridDim.x * blockDim.x) {
+    const int bp = block_part[b];
+    const bool want = bp == -2 || (bp >= 0 && __popc(bp ^ main_idx) <= max_bits);
+    // warp-aggregated append
+    const unsigned ball = __ballot_sync(__activemask(), want);
+    if (want) {
+      const int lane = threadIdx.x & 31;
+      const int leader = __ffs(ball) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(worklist, __popc(ball));
+      base = __shfl_sync(ball, base, leader);
+      worklist[1 + base + __popc(ball & ((1u << lane) - 1u))] = (int32_t)b;
+    }
+  }
+}
+
 }  // namespace
 
 // LSH.java:45-74.  Configuration-time integer arithmetic (runs once per model), kept on the host.
@@ -167,6 +190,18 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
   int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
   lsh_hash_kernel<<<grid, tile_rows, smem, stream>>>(d_rows, n, stride, F, m->d_hash_vectors,
                                                     m->store[ORYX_Y].fpad, H, tile_rows, d_out);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream) {
+  Store* s = &m->store[ORYX_Y];
+  const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
+  ORYX_CUDA(cudaMemsetAsync(d_worklist, 0, sizeof(int32_t), stream));
+  const int threads = 256;
+  const int grid = (int)std::min<int64_t>((n_blocks + threads - 1) / threads, (int64_t)m->num_sms * 4);
+  lsh_worklist_kernel<<<grid, threads, 0, stream>>>(s->d_block_part, n_blocks, d_main_index, m->max_bits, d_worklist);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;

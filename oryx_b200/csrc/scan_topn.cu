@@ -50,6 +50,8 @@ struct ScanParams {
   const float4* y;
   const int32_t* slot_row;
   const int32_t* slot_part;
+  const int32_t* block_part;  // per 256-slot block: shared partition, -1 empty, -2 mixed
+  const int32_t* worklist;    // LSH scans: [0] = number of candidate blocks, [1..] their ids (may be null)
   const float* q;  // [fpad]
   const int32_t* excl;  // sorted SLOT ids the allowed-predicate rejects
   int n_excl;
@@ -277,8 +279,9 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
     offer(score, gl < U && score == score && float_key(score) > thr_key, tile);
   };
 
-  // Any tile: LSH-filtered scans, ragged widths, the final partial tile.
-  auto general_tile = [&](int tile) {
+  // Any tile: LSH-filtered scans, ragged widths, the final partial tile.  `check_part` = test each
+  // row's partition (mixed blocks); uniform candidate blocks skip that.
+  auto general_tile = [&](int tile, bool check_part) {
     const int row0 = tile * RPT + grp;
     float4 d[U][NV];
     bool act[U];
@@ -286,7 +289,7 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
     for (int u = 0; u < U; u++) {
       const int row = row0 + u * RPI;
       act[u] = row < n_slots;
-      if (LSH) {
+      if (LSH && check_part) {
         int part = act[u] ? __ldg(p.slot_part + row) : -1;
         act[u] = part >= 0 && __popc(part ^ main_idx) <= p.max_bits;
       }
@@ -334,11 +337,45 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
     }
   };
 
-  if (!LSH && full_width) {
+  if (LSH) {
+    // Filtered scan, scheduled by 256-slot blocks: a block whose live rows all sit in one partition is
+    // skipped outright or streamed like an unfiltered tile run; only mixed blocks pay for per-row
+    // metadata.  After oryx_items_compact nearly every block is uniform.
+    // Work is handed out in 32-row units (8 per block) so that the few candidate blocks spread evenly
+    // over all warps.
+    constexpr int kUnitRows = 32;
+    constexpr int tiles_per_unit = kUnitRows / RPT;
+    constexpr int units_per_block = kBlockRows / kUnitRows;
+    auto scan_unit = [&](int unit, int bp) {
+      const bool uniform = bp >= 0;
+      const int t0 = unit * tiles_per_unit, t1 = min(n_tiles, t0 + tiles_per_unit);
+      for (int t = t0; t < t1; t++) {
+        if (uniform && full_width && t < n_full_tiles) fast_tile(t);
+        else general_tile(t, !uniform);
+      }
+    };
+    if (p.worklist != nullptr) {
+      // the candidate blocks were listed on the device after the query was hashed: every work item
+      // below is real work, so the hybrid schedule balances it like an unfiltered scan
+      const int n_items = __ldg(p.worklist) * units_per_block;
+      for_each_tile(n_items, [&](int w) {
+        const int b = __ldg(p.worklist + 1 + w / units_per_block);
+        scan_unit(b * units_per_block + (w % units_per_block), __ldg(p.block_part + b));
+      });
+    } else {
+      const int n_units = (n_slots + kUnitRows - 1) / kUnitRows;
+      for_each_tile(n_units, [&](int unit) {
+        const int bp = __ldg(p.block_part + unit / units_per_block);
+        if (bp == -1) return;
+        if (bp >= 0 && __popc(bp ^ main_idx) > p.max_bits) return;
+        scan_unit(unit, bp);
+      });
+    }
+  } else if (full_width) {
     for_each_tile(n_full_tiles, fast_tile);
-    if (n_tiles > n_full_tiles && gw == n_full_tiles % warps_total) general_tile(n_full_tiles);
+    if (n_tiles > n_full_tiles && gw == n_full_tiles % warps_total) general_tile(n_full_tiles, false);
   } else {
-    for_each_tile(n_tiles, general_tile);
+    for_each_tile(n_tiles, [&](int t) { general_tile(t, false); });
   }
 
   // publish this CTA's candidates (key, slot); unused entries still carry the empty sentinel key 0.
@@ -721,11 +758,25 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;  // LSH.java:160-162: all partitions otherwise
   if (lsh) {
     ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream));
+    if (ctx->scratch_sets == 2) {  // a context that owns memory: list the candidate blocks
+      const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
+      if (ctx->worklist_cap < n_blocks + 1) {
+        cudaFree(ctx->d_worklist);
+        ctx->d_worklist = nullptr;
+        ctx->worklist_cap = 0;
+        const int64_t cap = (s->cap_slots + kBlockRows - 1) / kBlockRows + 2;
+        ORYX_CUDA(cudaMalloc(&ctx->d_worklist, (size_t)cap * sizeof(int32_t)));
+        ctx->worklist_cap = cap;
+      }
+      ORYX_TRY(lsh_worklist_device(m, ctx->d_main_index, ctx->d_worklist, stream));
+    }
   }
   ScanParams p{};
   p.y = reinterpret_cast<const float4*>(s->d_vec);
   p.slot_row = s->d_slot_row;
   p.slot_part = s->d_slot_part;
+  p.block_part = s->d_block_part;
+  p.worklist = (lsh && ctx->scratch_sets == 2) ? ctx->d_worklist : nullptr;
   p.q = rq.d_query;
   p.excl = rq.d_excl;
   p.n_excl = rq.n_excl;

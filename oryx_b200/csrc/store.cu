@@ -57,6 +57,23 @@ __global__ void clear_slots_kernel(const int32_t* __restrict__ slots, int64_t n,
   }
 }
 
+// One warp per 256-slot block: summarise the partitions of its live rows.
+__global__ void block_part_kernel(const int32_t* __restrict__ slot_part, int64_t n_slots, int64_t n_blocks,
+                                  int32_t* __restrict__ block_part) {
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (b >= n_blocks) return;
+  int mn = 0x7fffffff, mx = -1;
+  for (int i = lane; i < kBlockRows; i += 32) {
+    const int64_t slot = b * kBlockRows + i;
+    const int part = slot < n_slots ? slot_part[slot] : -1;
+    if (part >= 0) { mn = min(mn, part); mx = max(mx, part); }
+  }
+  mn = __reduce_min_sync(0xffffffffu, mn);
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  if (lane == 0) block_part[b] = mx < 0 ? -1 : (mn == mx ? mn : -2);
+}
+
 __global__ void fill_i32_kernel(int32_t* p, int64_t n, int32_t v) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -90,12 +107,13 @@ int32_t grow(Model* m, Store* s, int64_t need) {
   int64_t cap = std::max<int64_t>(need, s->cap_slots + s->cap_slots / 2);
   cap = std::max<int64_t>(cap, 1024);
   float* nv = nullptr;
-  int32_t *nr = nullptr, *np = nullptr;
+  int32_t *nr = nullptr, *np = nullptr, *nbp = nullptr;
   cudaError_t e = cudaMalloc(&nv, (size_t)cap * s->fpad * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&nr, (size_t)cap * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&np, (size_t)cap * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&nbp, (size_t)(cap / kBlockRows + 1) * sizeof(int32_t));
   if (e != cudaSuccess) {
-    cudaFree(nv); cudaFree(nr); cudaFree(np);
+    cudaFree(nv); cudaFree(nr); cudaFree(np); cudaFree(nbp);
     cudaGetLastError();
     set_error("device allocation of %lld slots x %d floats failed: %s", (long long)cap, s->fpad,
               cudaGetErrorString(e));
@@ -120,9 +138,22 @@ int32_t grow(Model* m, Store* s, int64_t need) {
     ORYX_CUDA(cudaMemsetAsync(nv + s->n_slots * s->fpad, 0, (size_t)tail * s->fpad * sizeof(float), st));
   }
   ORYX_CUDA(cudaStreamSynchronize(st));
-  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part);
-  s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np;
+  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(s->d_block_part);
+  s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np; s->d_block_part = nbp;
   s->cap_slots = cap;
+  return ORYX_OK;
+}
+
+// Recompute the per-block partition summaries after a mutation (cheap: reads 4 bytes per slot).
+int32_t refresh_block_parts(Model* m, Store* s) {
+  if (s->n_slots == 0) return ORYX_OK;
+  const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
+  const int threads = 256;
+  const int64_t blocks = (n_blocks * 32 + threads - 1) / threads;
+  block_part_kernel<<<(unsigned)blocks, threads, 0, m->update_stream>>>(s->d_slot_part, s->n_slots, n_blocks,
+                                                                        s->d_block_part);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }
 
@@ -224,8 +255,8 @@ int32_t store_init(Model* m, int which, int64_t capacity_hint) {
 }
 
 void store_free(Store* s) {
-  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part);
-  s->d_vec = nullptr; s->d_slot_row = nullptr; s->d_slot_part = nullptr;
+  cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(s->d_block_part);
+  s->d_vec = nullptr; s->d_slot_row = nullptr; s->d_slot_part = nullptr; s->d_block_part = nullptr;
   s->cap_slots = s->n_slots = s->live = 0;
   s->row2slot.clear(); s->free_slots.clear();
 }
@@ -269,6 +300,10 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
       else std::fill(out_partitions + off, out_partitions + off + c, 0);
     }
   }
+  if (s->hashed) {
+    ORYX_TRY(refresh_block_parts(m, s));
+    ORYX_CUDA(cudaStreamSynchronize(st));
+  }
   return ORYX_OK;
 }
 
@@ -300,6 +335,10 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
     ORYX_CUDA(cudaGetLastError());
     ORYX_CUDA(cudaStreamSynchronize(st));
   }
+  if (s->hashed) {
+    ORYX_TRY(refresh_block_parts(m, s));
+    ORYX_CUDA(cudaStreamSynchronize(st));
+  }
   return ORYX_OK;
 }
 
@@ -327,6 +366,7 @@ int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
                                                           s->d_slot_row, s->d_slot_part);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
+  if (s->hashed) ORYX_TRY(refresh_block_parts(m, s));
   ORYX_CUDA(cudaStreamSynchronize(st));
   return ORYX_OK;
 }
@@ -400,10 +440,14 @@ int32_t store_compact(Model* m, int which) {
   ORYX_CUDA(cudaStreamSynchronize(st));
   cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(d_src);
   s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np;
-  s->cap_slots = cap;
+  s->cap_slots = cap;  // unchanged, so d_block_part keeps its size
   s->n_slots = live;
   s->free_slots.clear();
   for (int64_t i = 0; i < live; i++) s->row2slot[rowid[src[i]]] = (int32_t)i;
+  if (s->hashed) {
+    ORYX_TRY(refresh_block_parts(m, s));
+    ORYX_CUDA(cudaStreamSynchronize(st));
+  }
   return ORYX_OK;
 }
 

@@ -6,14 +6,23 @@ import numpy as np, torch
 import oryx_b200 as ob
 from oryx_b200 import native
 
-n, F = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000, 128
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
+F = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+lsh = len(sys.argv) > 3 and sys.argv[3] == "lsh"
 dev = torch.device("cuda", 0)
-m = ob.Model(F, capacity_hint=n)
+if lsh:
+    H, bits = ob.lsh_plan(0.3, 32)
+    hv = np.random.default_rng(4).standard_normal((H, F), dtype=np.float32)
+    m = ob.Model(F, hash_vectors=hv, max_bits_differing=bits, capacity_hint=n)
+else:
+    m = ob.Model(F, capacity_hint=n)
 g = torch.Generator(device=dev); g.manual_seed(1)
 for off in range(0, n, 1_000_000):
     c = min(1_000_000, n - off)
     blk = torch.randn((c, F), generator=g, device=dev); torch.cuda.synchronize()
     m.upsert_device(ob.Y, off, blk.data_ptr(), c)
+if lsh:
+    m.compact(ob.Y)
 q = np.random.default_rng(0).standard_normal((8, F), dtype=np.float32)
 L = native.lib()
 L.oryx_debug_scan_timestamps.restype = C.c_int32
