@@ -1,0 +1,457 @@
+// oryx_host.cpp -- see oryx_host.hpp.  Host bookkeeping only; all arithmetic on vectors of the model
+// goes through the C ABI to the device.
+#include "oryx_host.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <limits>
+#include <random>
+#include <thread>
+
+namespace oryx {
+namespace host {
+
+void check_status(int32_t status) {
+  if (status == ORYX_OK) return;
+  char buf[512];
+  oryx_last_error(buf, sizeof(buf));
+  if (status == ORYX_E_INVALID) throw std::invalid_argument(buf);  // IllegalArgumentException
+  throw std::runtime_error(buf);                                   // IllegalStateException
+}
+
+namespace {
+// VectorMath.dot / norm (VectorMath.java:38-58) for the handful of host-side uses (query-vector
+// construction, hash-vector selection): float product, double accumulate, index order.
+double vm_dot(const float* x, const float* y, size_t n) {
+  double d = 0.0;
+  for (size_t i = 0; i < n; i++) {
+    volatile float p = x[i] * y[i];
+    d += (double)p;
+  }
+  return d;
+}
+double vm_norm(const float* x, size_t n) { return std::sqrt(vm_dot(x, x, n)); }
+}  // namespace
+
+// ---------------------------------------------------------------- LocalitySensitiveHash
+LocalitySensitiveHash::LocalitySensitiveHash(double sampleRate, int numFeatures, int numCores, uint64_t seed) {
+  int32_t h = 0, b = 0;
+  check_status(oryx_lsh_plan(sampleRate, numCores, &h, &b));  // LocalitySensitiveHash.java:45-74
+  num_hashes_ = h;
+  max_bits_ = b;
+  hash_vectors_.assign((size_t)h * numFeatures, 0.0f);
+  std::mt19937_64 rng(seed);
+  std::normal_distribution<double> gauss(0.0, 1.0);
+  std::vector<float> cand((size_t)numFeatures), best((size_t)numFeatures);
+  for (int i = 0; i < h; i++) {  // :80-104: most-orthogonal next random vector
+    double bestTotal = std::numeric_limits<double>::infinity();
+    int sinceBest = 0;
+    bool have = false;
+    while (sinceBest < 1000) {
+      for (int j = 0; j < numFeatures; j++) cand[j] = (float)gauss(rng);  // VectorMath.randomVectorF
+      double newNorm = vm_norm(cand.data(), numFeatures), score = 0.0;
+      for (int e = 0; e < i; e++) {  // totalAbsCos :179-186
+        const float* ex = &hash_vectors_[(size_t)e * numFeatures];
+        score += std::fabs(vm_dot(ex, cand.data(), numFeatures)) / vm_norm(ex, numFeatures) / newNorm;
+      }
+      if (score < bestTotal) {
+        best = cand;
+        have = true;
+        if (score == 0.0) break;
+        bestTotal = score;
+        sinceBest = 0;
+      } else {
+        sinceBest++;
+      }
+    }
+    if (have) std::copy(best.begin(), best.end(), hash_vectors_.begin() + (size_t)i * numFeatures);
+  }
+}
+
+// ---------------------------------------------------------------- score functions
+ScoreFunction DotsFunction(const FloatVec& userVector) { return ScoreFunction{userVector, ORYX_DOT}; }
+
+ScoreFunction DotsFunction(const std::vector<FloatVec>& vecs) {  // DotsFunction.java:34-45
+  if (vecs.empty()) throw std::invalid_argument("need at least one user vector");
+  FloatVec t(vecs[0].size(), 0.0f);
+  for (const auto& v : vecs)
+    for (size_t i = 0; i < v.size(); i++) t[i] += v[i];
+  for (auto& x : t) x /= (float)vecs.size();
+  return ScoreFunction{t, ORYX_DOT};
+}
+
+ScoreFunction CosineAverageFunction(const FloatVec& v) {  // CosineAverageFunction.java:29-37
+  FloatVec t(v.size(), 0.0f);
+  double n = vm_norm(v.data(), v.size());
+  for (size_t i = 0; i < v.size(); i++) t[i] = (float)((double)t[i] + (double)v[i] / n);
+  return ScoreFunction{t, ORYX_COSINE};
+}
+
+ScoreFunction CosineAverageFunction(const std::vector<FloatVec>& vecs) {  // :39-51
+  if (vecs.empty()) throw std::invalid_argument("need at least one item vector");
+  FloatVec t(vecs[0].size(), 0.0f);
+  for (const auto& v : vecs) {
+    double n = vm_norm(v.data(), v.size());
+    for (size_t i = 0; i < v.size(); i++) t[i] = (float)((double)t[i] + (double)v[i] / n);
+  }
+  for (auto& x : t) x /= (float)vecs.size();
+  return ScoreFunction{t, ORYX_COSINE};
+}
+
+// ---------------------------------------------------------------- Solver / ALSUtils
+Solver::Solver(const std::vector<double>& gram, int features, int device) : features_(features) {
+  int32_t rank = 0;
+  int32_t st = oryx_solver_create(gram.data(), features, device, &h_, &rank);
+  if (st == ORYX_E_SINGULAR) {
+    throw SingularMatrixSolverException(rank, "Apparent rank: " + std::to_string(rank));  // LinearSystemSolver.java:54
+  }
+  check_status(st);
+}
+Solver::~Solver() { oryx_solver_destroy(h_); }
+
+FloatVec Solver::solveFToF(const FloatVec& b) const {
+  FloatVec x((size_t)features_);
+  check_status(oryx_solve_f2f(h_, b.data(), x.data()));
+  return x;
+}
+
+namespace ALSUtils {
+double computeTargetQui(bool implicit, double value, double currentValue) {
+  if (implicit) {
+    if (value > 0.0f && currentValue < 1.0) {
+      double diff = 1.0 - std::max(0.0, currentValue);
+      return currentValue + (value / (1.0 + value)) * diff;
+    }
+    if (value < 0.0f && currentValue > 0.0) {
+      double diff = -std::min(1.0, currentValue);
+      return currentValue + (value / (value - 1.0)) * diff;
+    }
+    return std::numeric_limits<double>::quiet_NaN();
+  }
+  return value;
+}
+
+std::unique_ptr<FloatVec> computeUpdatedXu(const Solver& solver, double value, const FloatVec* Xu,
+                                           const FloatVec* Yi, bool implicit) {
+  if (Yi == nullptr) return nullptr;  // ALSUtils.java:79-81
+  const int f = solver.features();
+  uint8_t has = Xu ? 1 : 0, valid = 0;
+  FloatVec zero((size_t)f, 0.0f), out((size_t)f);
+  check_status(oryx_fold_in_batch(solver.handle(), implicit ? 1 : 0, Xu ? Xu->data() : zero.data(), &has,
+                                  Yi->data(), &value, 1, out.data(), &valid));
+  if (!valid) return nullptr;
+  return std::make_unique<FloatVec>(std::move(out));
+}
+}  // namespace ALSUtils
+
+// ---------------------------------------------------------------- ALSServingModel
+static int default_cores(int numCores) {
+  if (numCores > 0) return numCores;
+  unsigned hc = std::thread::hardware_concurrency();  // Runtime.availableProcessors()
+  return hc ? (int)hc : 1;
+}
+
+ALSServingModel::ALSServingModel(int features, bool implicit, double sampleRate, int numCores, int device)
+    : features_(features), implicit_(implicit), device_(device),
+      lsh_((features > 0 && sampleRate > 0.0 && sampleRate <= 1.0)
+               ? LocalitySensitiveHash(sampleRate, features, default_cores(numCores))
+               : throw std::invalid_argument("features must be > 0 and sampleRate in (0,1]")) {  // :98-99
+  oryx_config cfg{};
+  cfg.features = features;
+  cfg.implicit = implicit ? 1 : 0;
+  cfg.num_hashes = lsh_.getNumHashes();
+  cfg.max_bits_differing = lsh_.getMaxBitsDiffering();
+  cfg.hash_vectors = lsh_.hashVectors().empty() ? nullptr : lsh_.hashVectors().data();
+  cfg.device = device;
+  check_status(oryx_model_create(&cfg, &h_));
+}
+
+ALSServingModel::~ALSServingModel() { oryx_model_destroy(h_); }
+
+int ALSServingModel::rowOf(const std::string& item) const {
+  auto it = item_row_.find(item);
+  return it == item_row_.end() ? -1 : it->second;
+}
+
+std::unique_ptr<FloatVec> ALSServingModel::getUserVector(const std::string& user) const {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto it = X_.find(user);
+  return it == X_.end() ? nullptr : std::make_unique<FloatVec>(it->second);
+}
+
+std::unique_ptr<FloatVec> ALSServingModel::getItemVector(const std::string& item) const {
+  int row;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    row = rowOf(item);
+  }
+  if (row < 0) return nullptr;
+  FloatVec v((size_t)features_);
+  int32_t found = 0;
+  check_status(oryx_items_get(h_, ORYX_Y, row, v.data(), &found));
+  return found ? std::make_unique<FloatVec>(std::move(v)) : nullptr;
+}
+
+void ALSServingModel::setUserVector(const std::string& user, const FloatVec& vector) {
+  if ((int)vector.size() != features_) throw std::invalid_argument("vector.length != features");  // :154
+  std::lock_guard<std::mutex> lk(mu_);
+  X_[user] = vector;
+  expected_users_.erase(user);
+}
+
+void ALSServingModel::setItemVector(const std::string& item, const FloatVec& vector) {
+  setItemVectors({item}, vector);
+}
+
+void ALSServingModel::setItemVectors(const std::vector<std::string>& items, const std::vector<float>& vecs) {
+  if (vecs.size() != items.size() * (size_t)features_) throw std::invalid_argument("vector.length != features");  // :162
+  std::vector<int32_t> rows(items.size()), parts(items.size());
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (size_t i = 0; i < items.size(); i++) {
+      int row = rowOf(items[i]);
+      if (row < 0) {
+        if (!free_rows_.empty()) { row = free_rows_.back(); free_rows_.pop_back(); }
+        else { row = (int)row_item_.size(); row_item_.emplace_back(); }
+        row_item_[row] = items[i];
+        item_row_[items[i]] = row;
+      }
+      rows[i] = row;
+    }
+  }
+  // hashing (getIndexFor), partition move and storage happen on the device (:163-178)
+  check_status(oryx_items_upsert(h_, ORYX_Y, rows.data(), vecs.data(), (int32_t)items.size(), parts.data()));
+  std::lock_guard<std::mutex> lk(mu_);
+  for (size_t i = 0; i < items.size(); i++) {
+    item_partition_[items[i]] = parts[i];
+    expected_items_.erase(items[i]);
+  }
+  cached_yty_.reset();  // :182 cachedYTYSolver.set(null)
+}
+
+std::unordered_set<std::string> ALSServingModel::getKnownItems(const std::string& user) const {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto it = known_items_.find(user);
+  return it == known_items_.end() ? std::unordered_set<std::string>{} : it->second;
+}
+
+void ALSServingModel::addKnownItems(const std::string& user, const std::vector<std::string>& items) {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto& s = known_items_[user];
+  s.insert(items.begin(), items.end());
+}
+
+std::unique_ptr<std::vector<std::pair<std::string, FloatVec>>> ALSServingModel::getKnownItemVectorsForUser(
+    const std::string& user) const {
+  if (!getUserVector(user)) return nullptr;
+  auto known = getKnownItems(user);
+  if (known.empty()) return nullptr;
+  auto out = std::make_unique<std::vector<std::pair<std::string, FloatVec>>>();
+  for (const auto& id : known) {
+    auto v = getItemVector(id);
+    if (v) out->emplace_back(id, *v);
+  }
+  if (out->empty()) return nullptr;
+  return out;
+}
+
+std::vector<IDValue> ALSServingModel::topN(const ScoreFunction& scoreFn, const Rescorer* rescorer, int howMany,
+                                           const std::unordered_set<std::string>* excludedIDs) const {
+  if ((int)scoreFn.target.size() != features_) throw std::invalid_argument("target vector length != features");
+  std::vector<int32_t> excl;
+  int n_rows;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    n_rows = (int)row_item_.size();
+    if (excludedIDs) {
+      for (const auto& id : *excludedIDs) {
+        int r = rowOf(id);
+        if (r >= 0) excl.push_back(r);
+      }
+    }
+  }
+  std::vector<IDValue> out;
+  if (rescorer == nullptr) {
+    // allowedPredicate = "not a known item": the device applies it (TopNConsumer.java:57)
+    std::vector<int32_t> rows((size_t)howMany);
+    std::vector<double> scores((size_t)howMany);
+    int32_t n = 0;
+    check_status(oryx_topn(h_, scoreFn.kind, scoreFn.target.data(), howMany, excl.empty() ? nullptr : excl.data(),
+                           (int32_t)excl.size(), rows.data(), scores.data(), &n));
+    std::lock_guard<std::mutex> lk(mu_);
+    for (int i = 0; i < n; i++) out.emplace_back(row_item_[rows[i]], scores[i]);
+    return out;
+  }
+  // Arbitrary Rescorer callbacks: exact scores of every row from the device, then the reference's
+  // TopNConsumer logic on the host (TopNConsumer.java:56-74; ALSServingModel.java:334).
+  std::vector<double> all((size_t)std::max(n_rows, 1));
+  if (n_rows > 0) check_status(oryx_scores_all(h_, scoreFn.kind, scoreFn.target.data(), n_rows, all.data()));
+  std::unordered_set<int32_t> excl_set(excl.begin(), excl.end());
+  std::vector<std::pair<double, int>> heap;  // min-heap on score
+  auto cmp = [](const std::pair<double, int>& a, const std::pair<double, int>& b) { return a.first > b.first; };
+  double lower = -std::numeric_limits<double>::infinity();
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (int r = 0; r < n_rows; r++) {
+      if (std::isnan(all[r]) || row_item_[r].empty() || excl_set.count(r)) continue;  // absent rows score NaN
+      const std::string& id = row_item_[r];
+      if (rescorer->isFiltered && rescorer->isFiltered(id)) continue;
+      double s = rescorer->rescore ? rescorer->rescore(id, all[r]) : all[r];
+      if (s > lower) {
+        if ((int)heap.size() >= howMany) {
+          lower = heap.front().first;
+          if (s > lower) {
+            std::pop_heap(heap.begin(), heap.end(), cmp);
+            heap.back() = {s, r};
+            std::push_heap(heap.begin(), heap.end(), cmp);
+          }
+        } else {
+          heap.emplace_back(s, r);
+          std::push_heap(heap.begin(), heap.end(), cmp);
+        }
+      }
+    }
+    std::stable_sort(heap.begin(), heap.end(), [](const auto& a, const auto& b) { return a.first > b.first; });
+    for (const auto& e : heap) out.emplace_back(row_item_[e.second], e.first);
+  }
+  return out;
+}
+
+std::shared_ptr<Solver> ALSServingModel::getYTYSolver() {
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (cached_yty_) return cached_yty_;
+  }
+  std::vector<double> g((size_t)features_ * features_);
+  int64_t used = 0;
+  check_status(oryx_gram(h_, ORYX_Y, g.data(), &used));
+  if (used == 0) return nullptr;  // LinearSystemSolver.getSolver(null) == null
+  auto s = std::make_shared<Solver>(g, features_, device_);
+  std::lock_guard<std::mutex> lk(mu_);
+  cached_yty_ = s;
+  return s;
+}
+
+void ALSServingModel::retainRecentAndUserIDs(const std::vector<std::string>& users) {
+  std::unordered_set<std::string> keep(users.begin(), users.end());
+  std::lock_guard<std::mutex> lk(mu_);
+  for (auto it = X_.begin(); it != X_.end();) it = keep.count(it->first) ? std::next(it) : X_.erase(it);
+  expected_users_.clear();
+  for (const auto& u : users) if (!X_.count(u)) expected_users_.insert(u);
+}
+
+void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& items) {
+  std::unordered_set<std::string> keep(items.begin(), items.end());
+  std::vector<int32_t> drop;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (auto it = item_row_.begin(); it != item_row_.end();) {
+      if (keep.count(it->first)) { ++it; continue; }
+      drop.push_back(it->second);
+      row_item_[it->second].clear();
+      free_rows_.push_back(it->second);
+      item_partition_.erase(it->first);
+      it = item_row_.erase(it);
+    }
+    expected_items_.clear();
+    for (const auto& i : items) if (!item_row_.count(i)) expected_items_.insert(i);
+    cached_yty_.reset();
+  }
+  if (!drop.empty()) check_status(oryx_items_remove(h_, ORYX_Y, drop.data(), (int32_t)drop.size()));
+}
+
+int ALSServingModel::getNumUsers() const { std::lock_guard<std::mutex> lk(mu_); return (int)X_.size(); }
+int ALSServingModel::getNumItems() const { std::lock_guard<std::mutex> lk(mu_); return (int)item_row_.size(); }
+
+float ALSServingModel::getFractionLoaded() const {
+  std::lock_guard<std::mutex> lk(mu_);
+  int expected = (int)expected_users_.size() + (int)expected_items_.size();
+  if (expected == 0) return 1.0f;
+  float loaded = (float)X_.size() + (float)item_row_.size();
+  return loaded / (loaded + expected);
+}
+
+int ALSServingModel::partitionOf(const std::string& item) const {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto it = item_partition_.find(item);
+  return it == item_partition_.end() ? -1 : it->second;
+}
+
+// ---------------------------------------------------------------- ALSSpeedModel
+ALSSpeedModel::ALSSpeedModel(int features, bool implicit, int device)
+    : features_(features), implicit_(implicit), device_(device) {
+  if (features <= 0) throw std::invalid_argument("features must be > 0");  // ALSSpeedModel.java:57
+  oryx_config cfg{};
+  cfg.features = features;
+  cfg.implicit = implicit ? 1 : 0;
+  cfg.device = device;
+  check_status(oryx_model_create(&cfg, &h_));
+}
+ALSSpeedModel::~ALSSpeedModel() { oryx_model_destroy(h_); }
+
+void ALSSpeedModel::set(Side& side, int which, const std::string& id, const FloatVec& v) {
+  if ((int)v.size() != features_) throw std::invalid_argument("vector.length != features");
+  auto it = side.row.find(id);
+  int32_t row = it == side.row.end() ? (int32_t)side.row.size() : it->second;
+  side.row[id] = row;
+  side.vec[id] = v;
+  check_status(oryx_items_upsert(h_, which, &row, v.data(), 1, nullptr));
+}
+void ALSSpeedModel::setUserVector(const std::string& user, const FloatVec& v) { set(x_, ORYX_X, user, v); }
+void ALSSpeedModel::setItemVector(const std::string& item, const FloatVec& v) { set(y_, ORYX_Y, item, v); }
+
+std::unique_ptr<FloatVec> ALSSpeedModel::getUserVector(const std::string& user) const {
+  auto it = x_.vec.find(user);
+  return it == x_.vec.end() ? nullptr : std::make_unique<FloatVec>(it->second);
+}
+std::unique_ptr<FloatVec> ALSSpeedModel::getItemVector(const std::string& item) const {
+  auto it = y_.vec.find(item);
+  return it == y_.vec.end() ? nullptr : std::make_unique<FloatVec>(it->second);
+}
+
+std::shared_ptr<Solver> ALSSpeedModel::solver(int which) {
+  std::vector<double> g((size_t)features_ * features_);
+  int64_t used = 0;
+  check_status(oryx_gram(h_, which, g.data(), &used));  // uncached, as ALSSpeedModel.java:118-126
+  if (used == 0) return nullptr;
+  return std::make_shared<Solver>(g, features_, device_);
+}
+std::shared_ptr<Solver> ALSSpeedModel::getXTXSolver() { return solver(ORYX_X); }
+std::shared_ptr<Solver> ALSSpeedModel::getYTYSolver() { return solver(ORYX_Y); }
+
+std::vector<Update> ALSSpeedModel::buildUpdates(const std::vector<UserItemStrength>& input) {
+  std::vector<Update> out;
+  if (input.empty()) return out;
+  auto xtx = getXTXSolver();  // ALSSpeedModelManager.java:173-180
+  auto yty = getYTYSolver();
+  if (!xtx || !yty) return out;
+  const size_t n = input.size(), f = (size_t)features_;
+  // gather the snapshot vectors of every interaction (:186-187), then two device batches:
+  //   newXu = computeUpdatedXu(YTYsolver, value, Xu, Yi)   :192
+  //   newYi = computeUpdatedXu(XTXsolver, value, Yi, Xu)   :194
+  std::vector<float> xu(n * f, 0.0f), yi(n * f, 0.0f);
+  std::vector<uint8_t> has_x(n, 0), has_y(n, 0);
+  std::vector<double> values(n);
+  for (size_t k = 0; k < n; k++) {
+    values[k] = input[k].strength;
+    auto ix = x_.vec.find(input[k].user);
+    auto iy = y_.vec.find(input[k].item);
+    if (ix != x_.vec.end()) { has_x[k] = 1; std::copy(ix->second.begin(), ix->second.end(), xu.begin() + k * f); }
+    if (iy != y_.vec.end()) { has_y[k] = 1; std::copy(iy->second.begin(), iy->second.end(), yi.begin() + k * f); }
+  }
+  std::vector<float> new_x(n * f), new_y(n * f);
+  std::vector<uint8_t> ok_x(n), ok_y(n);
+  check_status(oryx_fold_in_batch(yty->handle(), implicit_ ? 1 : 0, xu.data(), has_x.data(), yi.data(), values.data(),
+                                  (int64_t)n, new_x.data(), ok_x.data()));
+  check_status(oryx_fold_in_batch(xtx->handle(), implicit_ ? 1 : 0, yi.data(), has_y.data(), xu.data(), values.data(),
+                                  (int64_t)n, new_y.data(), ok_y.data()));
+  for (size_t k = 0; k < n; k++) {
+    // computeUpdatedXu returns null when its "Yi" argument is null (ALSUtils.java:79-81)
+    if (ok_x[k] && has_y[k]) out.push_back(Update{'X', input[k].user, FloatVec(new_x.begin() + k * f, new_x.begin() + (k + 1) * f), input[k].item});
+    if (ok_y[k] && has_x[k]) out.push_back(Update{'Y', input[k].item, FloatVec(new_y.begin() + k * f, new_y.begin() + (k + 1) * f), input[k].user});
+  }
+  return out;
+}
+
+}  // namespace host
+}  // namespace oryx
