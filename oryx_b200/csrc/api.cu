@@ -250,6 +250,8 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     store_free(&m->store[0]);
     store_free(&m->store[1]);
     cudaFree(m->d_hash_vectors);
+    for (auto& b : m->batch.buf) cudaFree(b);
+    cudaFree(m->d_debug_ts);
     if (m->update_stream) cudaStreamDestroy(m->update_stream);
     cudaGetLastError();
   }

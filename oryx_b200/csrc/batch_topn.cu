@@ -436,8 +436,8 @@ __device__ __forceinline__ bool excluded_slot(const int32_t* excl, int n, int32_
   return false;
 }
 
-// One CTA per query: fp32 scores of every row of the candidate sub-blocks (one warp per sub-block,
-// one lane per row -- sub-blocks are few, this phase is small), the k best kept in a shared
+// One CTA per query: fp32 scores of every row of the candidate sub-blocks (one warp per sub-block),
+// the k best kept in a shared
 // candidate array, then the exact finishing pass.  Same selection rule and the same exact arithmetic
 // as scan_topn.cu, so results are identical to the single-query path.
 __global__ void __launch_bounds__(kRefineThreads)
@@ -467,55 +467,68 @@ batch_refine_kernel(const float* __restrict__ y, const int32_t* __restrict__ slo
   const int n_excl = excl_offsets ? excl_offsets[qi + 1] - excl_offsets[qi] : 0;
   const int32_t* my_cand = cand + (int64_t)qi * cand_cap;
 
+  // one warp per candidate sub-block; 8 lanes share a row (coalesced 128-byte segments, as in the
+  // single-query scan), 4 rows per pass, 8 passes per sub-block
+  const int gl = lane & 7, grp = lane >> 3;
+  const int f4 = fpad >> 2;
+  const float4* q4 = reinterpret_cast<const float4*>(s_q);
   for (int c = warp; c < nc; c += kRefineThreads / 32) {
-    const int64_t slot = (int64_t)my_cand[c] * SUB + lane;
-    float acc = 0.f, nrm = 0.f;
-    const bool in = slot < n_slots;
-    if (in) {
-      const float4* r4 = reinterpret_cast<const float4*>(y + slot * fpad);
-      const float4* q4 = reinterpret_cast<const float4*>(s_q);
-      for (int j = 0; j < (fpad >> 2); j++) {
-        const float4 a = __ldg(r4 + j);
-        const float4 b = q4[j];
-        acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
-        if (kind == ORYX_COSINE) {
-          nrm = fmaf(a.x, a.x, nrm); nrm = fmaf(a.y, a.y, nrm); nrm = fmaf(a.z, a.z, nrm); nrm = fmaf(a.w, a.w, nrm);
+    const int64_t sub0 = (int64_t)my_cand[c] * SUB;
+#pragma unroll 2
+    for (int pass = 0; pass < SUB / 4; pass++) {
+      const int64_t slot = sub0 + pass * 4 + grp;
+      const bool in = slot < n_slots;
+      float acc = 0.f, nrm = 0.f;
+      if (in) {
+        const float4* r4 = reinterpret_cast<const float4*>(y + slot * fpad);
+        for (int j = gl; j < f4; j += 8) {
+          const float4 a = __ldg(r4 + j);
+          const float4 b = q4[j];
+          acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
+          if (kind == ORYX_COSINE) {
+            nrm = fmaf(a.x, a.x, nrm); nrm = fmaf(a.y, a.y, nrm); nrm = fmaf(a.z, a.z, nrm); nrm = fmaf(a.w, a.w, nrm);
+          }
         }
       }
-    }
-    const float score = (kind == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc;
-    const uint32_t key = float_key(score);
-    bool hit = in && score == score && key > *(volatile unsigned int*)&s_thr_key;
-    if (hit && n_excl > 0 && excluded_slot(excl, n_excl, (int32_t)slot)) hit = false;
-    unsigned ball = __ballot_sync(0xffffffffu, hit);
-    while (ball != 0u) {
-      const int src = __ffs(ball) - 1;
-      ball &= ball - 1;
-      const uint32_t ky = __shfl_sync(0xffffffffu, key, src);
-      const int32_t sl = __shfl_sync(0xffffffffu, (int32_t)slot, src);
-      // replace-the-minimum with a 64-bit CAS, whole warp searches (as in scan_topn.cu)
-      const unsigned long long x = ((unsigned long long)ky << 32) | (unsigned long long)(uint32_t)sl;
-      for (;;) {
-        unsigned long long best = ~0ull;
-        int best_idx = 0;
-        for (int i = lane; i < k; i += 32) {
-          unsigned long long v = *(const volatile unsigned long long*)(arr + i);
-          if (v < best) { best = v; best_idx = i; }
-        }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
-          int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
-          if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
+      for (int o = 4; o > 0; o >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (kind == ORYX_COSINE) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+      }
+      const float score = (kind == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc;
+      const uint32_t key = float_key(score);
+      bool hit = in && gl == 0 && score == score && key > *(volatile unsigned int*)&s_thr_key;
+      if (hit && n_excl > 0 && excluded_slot(excl, n_excl, (int32_t)slot)) hit = false;
+      unsigned ball = __ballot_sync(0xffffffffu, hit);
+      while (ball != 0u) {
+        const int src = __ffs(ball) - 1;
+        ball &= ball - 1;
+        const uint32_t ky = __shfl_sync(0xffffffffu, key, src);
+        const int32_t sl = __shfl_sync(0xffffffffu, (int32_t)slot, src);
+        // replace-the-minimum with a 64-bit CAS, whole warp searches (as in scan_topn.cu)
+        const unsigned long long x = ((unsigned long long)ky << 32) | (unsigned long long)(uint32_t)sl;
+        for (;;) {
+          unsigned long long best = ~0ull;
+          int best_idx = 0;
+          for (int i = lane; i < k; i += 32) {
+            unsigned long long v = *(const volatile unsigned long long*)(arr + i);
+            if (v < best) { best = v; best_idx = i; }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
+            int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+            if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
+          }
+          if (ky <= (uint32_t)(best >> 32)) {
+            if (lane == 0) atomicMax(&s_thr_key, (uint32_t)(best >> 32));
+            break;
+          }
+          unsigned long long old = 0ull;
+          if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
+          old = __shfl_sync(0xffffffffu, old, 0);
+          if (old == best) break;
         }
-        if (ky <= (uint32_t)(best >> 32)) {
-          if (lane == 0) atomicMax(&s_thr_key, (uint32_t)(best >> 32));
-          break;
-        }
-        unsigned long long old = 0ull;
-        if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
-        old = __shfl_sync(0xffffffffu, old, 0);
-        if (old == best) break;
       }
     }
   }
@@ -622,19 +635,24 @@ int32_t launch_score(const CUtensorMap& tq, const CUtensorMap& ty, int n_qtiles,
   return ORYX_OK;
 }
 
-struct DevBuf {
-  void* p = nullptr;
-  ~DevBuf() { cudaFree(p); }
-  int32_t alloc(size_t bytes) {
-    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+// Slot `i` of the model's grow-only batch scratch, at least `bytes` large.
+int32_t scratch(BatchScratch& bs, int i, size_t bytes, void** out, bool* grew = nullptr) {
+  if (grew) *grew = false;
+  if (bs.bytes[i] < bytes) {
+    cudaFree(bs.buf[i]);
+    bs.buf[i] = nullptr;
+    bs.bytes[i] = 0;
+    if (cudaMalloc(&bs.buf[i], bytes) != cudaSuccess) {
       cudaGetLastError();
-      p = nullptr;
       set_error("device allocation of %zu bytes failed (batched top-N scratch)", bytes);
       return ORYX_E_NOMEM;
     }
-    return ORYX_OK;
+    bs.bytes[i] = bytes;
+    if (grew) *grew = true;
   }
-};
+  *out = bs.buf[i];
+  return ORYX_OK;
+}
 
 }  // namespace
 
@@ -662,35 +680,46 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   const int64_t bmax_stride = n_sub;
   const int cand_cap = 4096;
 
-  DevBuf d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
-  ORYX_TRY(d_ybf.alloc((size_t)n * kpad * 2));
-  ORYX_TRY(d_qbf.alloc((size_t)nq_pad * kpad * 2));
-  ORYX_TRY(d_q.alloc((size_t)nq * F * 4));
-  ORYX_TRY(d_qnorm.alloc((size_t)nq_pad * 4));
-  ORYX_TRY(d_maxn.alloc(4));
-  ORYX_TRY(d_bmax.alloc((size_t)nq_pad * bmax_stride * 4));
-  ORYX_TRY(d_cand.alloc((size_t)nq * cand_cap * 4));
-  ORYX_TRY(d_candn.alloc((size_t)nq * 4));
-  ORYX_TRY(d_orows.alloc((size_t)nq * how_many * 4));
-  ORYX_TRY(d_oscores.alloc((size_t)nq * how_many * 8));
-  ORYX_TRY(d_on.alloc((size_t)nq * 4));
+  BatchScratch& bs = m->batch;
+  std::lock_guard<std::mutex> batch_lock(bs.mu);
+  struct P { void* p = nullptr; } d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
+  bool y_grew = false;
+  ORYX_TRY(scratch(bs, 0, (size_t)n * kpad * 2, &d_ybf.p, &y_grew));
+  ORYX_TRY(scratch(bs, 1, (size_t)nq_pad * kpad * 2, &d_qbf.p));
+  ORYX_TRY(scratch(bs, 2, (size_t)nq * F * 4, &d_q.p));
+  ORYX_TRY(scratch(bs, 3, (size_t)nq_pad * 4, &d_qnorm.p));
+  ORYX_TRY(scratch(bs, 4, 4, &d_maxn.p));
+  ORYX_TRY(scratch(bs, 5, (size_t)nq_pad * bmax_stride * 4, &d_bmax.p));
+  ORYX_TRY(scratch(bs, 6, (size_t)nq * cand_cap * 4, &d_cand.p));
+  ORYX_TRY(scratch(bs, 7, (size_t)nq * 4, &d_candn.p));
+  ORYX_TRY(scratch(bs, 8, (size_t)nq * how_many * 4, &d_orows.p));
+  ORYX_TRY(scratch(bs, 9, (size_t)nq * how_many * 8, &d_oscores.p));
+  ORYX_TRY(scratch(bs, 10, (size_t)nq * 4, &d_on.p));
   const int n_excl_total = excl_offsets ? excl_offsets[nq] : 0;
   if (excl_offsets) {
-    ORYX_TRY(d_eo.alloc((size_t)(nq + 1) * 4));
-    ORYX_TRY(d_es.alloc((size_t)std::max(n_excl_total, 1) * 4));
+    ORYX_TRY(scratch(bs, 11, (size_t)(nq + 1) * 4 + (size_t)std::max(n_excl_total, 1) * 4, &d_eo.p));
+    d_es.p = reinterpret_cast<unsigned char*>(d_eo.p) + (size_t)(nq + 1) * 4;
     ORYX_CUDA(cudaMemcpyAsync(d_eo.p, excl_offsets, (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice, st));
     if (n_excl_total > 0)
       ORYX_CUDA(cudaMemcpyAsync(d_es.p, excl_slots, (size_t)n_excl_total * 4, cudaMemcpyHostToDevice, st));
   }
+  // the bf16 shadow of Y (and the norm bound that goes with it) is reused while the store is unchanged
+  const int normalized = kind == ORYX_COSINE ? 1 : 0;
+  const bool y_fresh = !y_grew && bs.y_version == s->version && bs.y_normalized == normalized && bs.y_rows == n;
   cudaEvent_t ev[5];
   for (auto& e : ev) ORYX_CUDA(cudaEventCreate(&e));
   struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 5; i++) cudaEventDestroy(e[i]); } } evg{ev};
 
   ORYX_CUDA(cudaMemcpyAsync(d_q.p, queries, (size_t)nq * F * 4, cudaMemcpyHostToDevice, st));
-  ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 4, st));
   ORYX_CUDA(cudaEventRecord(ev[0], st));
-  convert_y_kernel<<<m->num_sms * 8, 256, 0, st>>>(s->d_vec, n, fpad, F, kpad, kind == ORYX_COSINE ? 1 : 0,
-                                                  (__nv_bfloat16*)d_ybf.p, (unsigned int*)d_maxn.p);
+  if (!y_fresh) {
+    ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 4, st));
+    convert_y_kernel<<<m->num_sms * 8, 256, 0, st>>>(s->d_vec, n, fpad, F, kpad, normalized,
+                                                    (__nv_bfloat16*)d_ybf.p, (unsigned int*)d_maxn.p);
+    bs.y_version = s->version;
+    bs.y_normalized = normalized;
+    bs.y_rows = n;
+  }
   convert_q_kernel<<<(nq_pad + 7) / 8, 256, 0, st>>>((const float*)d_q.p, nq, nq_pad, F, kpad,
                                                     (__nv_bfloat16*)d_qbf.p, (float*)d_qnorm.p);
   ORYX_CUDA(cudaGetLastError());

@@ -100,6 +100,7 @@ struct Store {
   int64_t cap_slots = 0;
   int64_t n_slots = 0;  // high-water mark
   int64_t live = 0;
+  uint64_t version = 0;  // bumped by every mutation; lets derived buffers (the bf16 shadow) be reused
 
   std::vector<int32_t> row2slot;
   std::vector<int32_t> free_slots;
@@ -143,6 +144,16 @@ struct BatchTimings {
   double convert_ms = 0, score_ms = 0, threshold_ms = 0, refine_ms = 0, flops = 0;
 };
 
+// Grow-only device scratch of the tensor-core batch path, kept across calls (one batch at a time).
+struct BatchScratch {
+  std::mutex mu;
+  void* buf[12] = {nullptr};
+  size_t bytes[12] = {0};
+  uint64_t y_version = ~0ull;  // store version the bf16 shadow of Y was converted from
+  int y_normalized = -1;       // ... and whether it holds y/||y|| (cosine) or y (dot)
+  int64_t y_rows = -1;
+};
+
 struct Model {
   oryx_config cfg{};
   int device = 0;
@@ -162,6 +173,7 @@ struct Model {
   std::vector<QueryCtx*> pool_free;
   std::vector<std::unique_ptr<QueryCtx>> pool_all;
   int pool_limit = 8;
+  BatchScratch batch;
   BatchTimings last_batch;  // phase timings of the most recent tensor-core batch (oryx_debug_batch_timings)
   unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)

@@ -264,6 +264,7 @@ void store_free(Store* s) {
 int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs, int32_t n,
                      int32_t* out_partitions) {
   Store* s = &m->store[which];
+  s->version++;
   cudaStream_t st = m->update_stream;
   const int F = s->features;
   for (int64_t off = 0; off < n; off += kChunkRows) {
@@ -309,6 +310,7 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
 
 int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float* d_vecs, int64_t n) {
   Store* s = &m->store[which];
+  s->version++;
   cudaStream_t st = m->update_stream;
   const int F = s->features;
   const int64_t chunk = 1 << 20;
@@ -344,6 +346,7 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
 
 int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
   Store* s = &m->store[which];
+  s->version++;
   cudaStream_t st = m->update_stream;
   ORYX_TRY(staging_reserve(std::max(n, 1), s->features, false));
   Staging& g = g_staging;
@@ -385,6 +388,7 @@ int32_t store_get(Model* m, int which, int32_t row, float* out, int32_t* found) 
 
 int32_t store_compact(Model* m, int which) {
   Store* s = &m->store[which];
+  s->version++;
   cudaStream_t st = m->update_stream;
   int64_t n = s->n_slots;
   if (n == 0) return ORYX_OK;
