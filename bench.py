@@ -235,7 +235,7 @@ def run_ours(args):
     H, bits = ob.lsh_plan(1.0, LSH_CORES)
     hv = np.random.default_rng(SEED_H).standard_normal((H, F), dtype=np.float32)
     model = ob.Model(F, implicit=True, hash_vectors=hv, max_bits_differing=bits, device=local_rank,
-                     capacity_hint=n_items)
+                     capacity_hint=n_items, reserved_sms=1 if world > 1 else 0)
 
     # ---- synthetic model, generated on the device shard-locally and bulk-loaded through the C ABI
     want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)
@@ -264,8 +264,9 @@ def run_ours(args):
     d_rows = d_rec[HOW_MANY * 8: HOW_MANY * 12].view(torch.int32)
     d_n = d_rec[HOW_MANY * 12: HOW_MANY * 12 + 4].view(torch.int32)
     if world > 1:
-        from oryx_b200.sharded import ShardPlan, exchange_packed
+        from oryx_b200.sharded import PipelinedShardedTopN, ShardPlan, exchange_packed
         plan = ShardPlan(world, n_items)   # rank r owns global rows [r*n_items, (r+1)*n_items)
+        pipe = PipelinedShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
         g_rec = torch.zeros(world * rec_bytes, dtype=torch.uint8, device=dev)
         m_rows = torch.zeros(HOW_MANY, dtype=torch.int64, device=dev)
         m_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
@@ -282,14 +283,18 @@ def run_ours(args):
     def step_device(i: int):
         """One query with inputs resident in HBM, enqueued on torch's current stream."""
         nonlocal launches_extra
-        model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
-                          d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
         if world > 1:
-            # the one exchange step: N x (10 scores, 10 rows, count) over NCCL / NVLink, then merge
-            exchange_merge()
+            # scan on this stream; the one exchange step (a 128-byte record per rank over NCCL / NVLink)
+            # and the merge follow on a side stream while the next query's scan already runs
+            pipe.submit(ob.DOT, d_q[i % N_QUERIES].data_ptr())
             launches_extra += 1
+        else:
+            model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
+                              d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
 
     def barrier():
+        if world > 1:
+            pipe.drain()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -322,6 +327,8 @@ def run_ours(args):
     e0.record(stream)
     for i in range(args.steps):
         step_device(i)
+    if world > 1:
+        pipe.drain()   # the timed region ends when every exchange and merge has finished too
     e1.record(stream)
     barrier()
     ms_total = e0.elapsed_time(e1)

@@ -693,7 +693,8 @@ int32_t launch_variant(Model* m, const ScanParams& p, int kind, bool lsh, bool o
     int64_t want = (n_tiles + (T / 32) - 1) / (T / 32);
     const size_t smem = scan_smem_bytes(p.k, p.excl_in_smem ? p.n_excl : 0);
     int per_sm = occupancy_cached(reinterpret_cast<const void*>(kern), T, smem, scan_smem_bytes(kMaxK, kExclSmemMax));
-    int grid = (int)std::min<int64_t>(std::min<int64_t>((int64_t)m->num_sms * per_sm, kMaxGrid), std::max<int64_t>(want, 1));
+    const int sms = std::max(1, m->num_sms - std::max(0, m->cfg.reserved_sms));
+    int grid = (int)std::min<int64_t>(std::min<int64_t>((int64_t)sms * per_sm, kMaxGrid), std::max<int64_t>(want, 1));
     *grid_out = grid;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)grid);

@@ -35,7 +35,7 @@ class SingularMatrixSolverException(OryxError):
 class _Config(C.Structure):
     _fields_ = [("features", C.c_int32), ("implicit", C.c_int32), ("num_hashes", C.c_int32),
                 ("max_bits_differing", C.c_int32), ("hash_vectors", C.POINTER(C.c_float)),
-                ("device", C.c_int32), ("reserved", C.c_int32), ("capacity_hint", C.c_int64)]
+                ("device", C.c_int32), ("reserved_sms", C.c_int32), ("capacity_hint", C.c_int64)]
 
 
 class _Stats(C.Structure):
@@ -133,7 +133,7 @@ class Model:
     """Handle over oryx_model: the device-resident X/Y stores plus the LSH geometry."""
 
     def __init__(self, features: int, implicit: bool = True, hash_vectors=None, max_bits_differing: int = 0,
-                 device: int = 0, capacity_hint: int = 0):
+                 device: int = 0, capacity_hint: int = 0, reserved_sms: int = 0):
         hv = None if hash_vectors is None or len(hash_vectors) == 0 else _f32(hash_vectors)
         cfg = _Config()
         cfg.features = features
@@ -142,6 +142,7 @@ class Model:
         cfg.max_bits_differing = max_bits_differing
         cfg.hash_vectors = _ptr(hv, C.c_float)
         cfg.device = device
+        cfg.reserved_sms = reserved_sms
         cfg.capacity_hint = capacity_hint
         self.features = features
         self.num_hashes = cfg.num_hashes

@@ -94,6 +94,63 @@ def exchange_packed(dist, torch, plan: ShardPlan, local_record, gathered=None):
     return gathered
 
 
+class PipelinedShardedTopN:
+    """Back-to-back sharded queries without a bubble between them.
+
+    The scan of query i+1 does not depend on the exchange of query i, so the all-gather and the merge
+    run on a side stream (on the SM the model leaves free, ``reserved_sms=1``) while the main stream
+    already scans the next query.  Two packed result records alternate; ``ready`` events order
+    scan -> exchange, ``consumed`` events keep scan i+2 from overwriting a record the all-gather of
+    query i still reads.  (Measured alternative, rejected: three records with the exchange trailing by
+    one query so that no event sits between a finishing kernel and the next scan -- 0.857 ms/step
+    against 0.758 ms/step for this arrangement at N=2.)
+    ``drain()`` makes the main stream wait for everything submitted so far.
+    """
+
+    NB = 2
+
+    def __init__(self, ob, model, dist, torch, plan: ShardPlan, how_many: int, device):
+        self.ob, self.model, self.dist, self.torch, self.plan, self.hm = ob, model, dist, torch, plan, how_many
+        self.rec_bytes = ob.packed_record_bytes(how_many)
+        self.side = torch.cuda.Stream(device=device)
+        z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
+        nb = self.NB
+        self.d_rec = [z(self.rec_bytes, torch.uint8) for _ in range(nb)]
+        self.g_rec = [z(plan.world * self.rec_bytes, torch.uint8) for _ in range(nb)]
+        self.m_rows = [z(how_many, torch.int64) for _ in range(nb)]
+        self.m_scores = [z(how_many, torch.float64) for _ in range(nb)]
+        self.m_n = [z(1, torch.int32) for _ in range(nb)]
+        self.ready = [torch.cuda.Event() for _ in range(nb)]
+        self.consumed = [torch.cuda.Event() for _ in range(nb)]
+        self.i = 0
+
+    def submit(self, kind: int, d_query_ptr: int):
+        torch, hm = self.torch, self.hm
+        b = self.i % self.NB
+        main = torch.cuda.current_stream()
+        if self.i >= self.NB:
+            main.wait_event(self.consumed[b])
+        rec = self.d_rec[b]
+        self.model.topn_device(kind, d_query_ptr, hm, rec[hm * 8:].data_ptr(), rec.data_ptr(),
+                               rec[hm * 12:].data_ptr(), main.cuda_stream)
+        self.ready[b].record(main)
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(self.ready[b])
+            self.dist.all_gather_into_tensor(self.g_rec[b], self.d_rec[b])
+            self.consumed[b].record(self.side)
+            self.ob.merge_topn_packed(self.g_rec[b].data_ptr(), self.plan.world, self.rec_bytes, hm,
+                                      self.plan.rows_per_rank, self.m_rows[b].data_ptr(),
+                                      self.m_scores[b].data_ptr(), self.m_n[b].data_ptr(), self.side.cuda_stream)
+        self.i += 1
+
+    def drain(self):
+        self.torch.cuda.current_stream().wait_stream(self.side)
+
+    def merged(self, i: int):
+        b = i % self.NB
+        return self.m_rows[b], self.m_scores[b], self.m_n[b]
+
+
 def allreduce_gram(dist, torch, gram_partial):
     """YtY = sum of per-shard Grams (ALSServingModel.java:362-368), fp64, in place."""
     dist.all_reduce(gram_partial, op=dist.ReduceOp.SUM)
