@@ -195,7 +195,13 @@ std::unique_ptr<FloatVec> ALSServingModel::getItemVector(const std::string& item
 void ALSServingModel::setUserVector(const std::string& user, const FloatVec& vector) {
   if ((int)vector.size() != features_) throw std::invalid_argument("vector.length != features");  // :154
   std::lock_guard<std::mutex> lk(mu_);
-  X_[user] = vector;
+  auto it = X_.find(user);
+  if (it == X_.end()) {
+    X_.emplace(user, vector);
+    recent_users_.insert(user);  // FeatureVectors.java:74-77: ID was actually new
+  } else {
+    it->second = vector;
+  }
   expected_users_.erase(user);
 }
 
@@ -205,26 +211,32 @@ void ALSServingModel::setItemVector(const std::string& item, const FloatVec& vec
 
 void ALSServingModel::setItemVectors(const std::vector<std::string>& items, const std::vector<float>& vecs) {
   if (vecs.size() != items.size() * (size_t)features_) throw std::invalid_argument("vector.length != features");  // :162
-  std::vector<int32_t> rows(items.size()), parts(items.size());
+  setItemVectors(items.data(), vecs.data(), items.size());
+}
+
+void ALSServingModel::setItemVectors(const std::string* items, const float* vecs, size_t n) {
+  if (n == 0) return;
+  std::vector<int32_t> rows(n), parts(n);
   {
     std::lock_guard<std::mutex> lk(mu_);
-    for (size_t i = 0; i < items.size(); i++) {
+    for (size_t i = 0; i < n; i++) {
       int row = rowOf(items[i]);
       if (row < 0) {
         if (!free_rows_.empty()) { row = free_rows_.back(); free_rows_.pop_back(); }
         else { row = (int)row_item_.size(); row_item_.emplace_back(); }
         row_item_[row] = items[i];
         item_row_[items[i]] = row;
+        recent_items_.insert(items[i]);  // FeatureVectors.java:74-77
       }
       rows[i] = row;
     }
   }
   // hashing (getIndexFor), partition move and storage happen on the device (:163-178)
-  check_status(oryx_items_upsert(h_, ORYX_Y, rows.data(), vecs.data(), (int32_t)items.size(), parts.data()));
+  check_status(oryx_items_upsert(h_, ORYX_Y, rows.data(), vecs, (int32_t)n, parts.data()));
   std::lock_guard<std::mutex> lk(mu_);
-  for (size_t i = 0; i < items.size(); i++) {
+  for (size_t i = 0; i < n; i++) {
     item_partition_[items[i]] = parts[i];
-    expected_items_.erase(items[i]);
+    if (!expected_items_.empty()) expected_items_.erase(items[i]);
   }
   cached_yty_.reset();  // :182 cachedYTYSolver.set(null)
 }
@@ -335,7 +347,9 @@ std::shared_ptr<Solver> ALSServingModel::getYTYSolver() {
 void ALSServingModel::retainRecentAndUserIDs(const std::vector<std::string>& users) {
   std::unordered_set<std::string> keep(users.begin(), users.end());
   std::lock_guard<std::mutex> lk(mu_);
-  for (auto it = X_.begin(); it != X_.end();) it = keep.count(it->first) ? std::next(it) : X_.erase(it);
+  for (auto it = X_.begin(); it != X_.end();)
+    it = (keep.count(it->first) || recent_users_.count(it->first)) ? std::next(it) : X_.erase(it);
+  recent_users_.clear();
   expected_users_.clear();
   for (const auto& u : users) if (!X_.count(u)) expected_users_.insert(u);
 }
@@ -346,18 +360,40 @@ void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& ite
   {
     std::lock_guard<std::mutex> lk(mu_);
     for (auto it = item_row_.begin(); it != item_row_.end();) {
-      if (keep.count(it->first)) { ++it; continue; }
+      if (keep.count(it->first) || recent_items_.count(it->first)) { ++it; continue; }
       drop.push_back(it->second);
       row_item_[it->second].clear();
       free_rows_.push_back(it->second);
       item_partition_.erase(it->first);
       it = item_row_.erase(it);
     }
+    recent_items_.clear();
     expected_items_.clear();
     for (const auto& i : items) if (!item_row_.count(i)) expected_items_.insert(i);
     cached_yty_.reset();
   }
   if (!drop.empty()) check_status(oryx_items_remove(h_, ORYX_Y, drop.data(), (int32_t)drop.size()));
+}
+
+void ALSServingModel::retainRecentAndKnownItems(const std::vector<std::string>& users,
+                                                const std::vector<std::string>& items) {
+  std::unordered_set<std::string> keepUsers(users.begin(), users.end()), keepItems(items.begin(), items.end());
+  std::lock_guard<std::mutex> lk(mu_);
+  for (auto it = known_items_.begin(); it != known_items_.end();)
+    it = (keepUsers.count(it->first) || recent_users_.count(it->first)) ? std::next(it) : known_items_.erase(it);
+  for (auto& kv : known_items_) {
+    auto& set = kv.second;
+    for (auto it = set.begin(); it != set.end();)
+      it = (keepItems.count(*it) || recent_items_.count(*it)) ? std::next(it) : set.erase(it);
+  }
+}
+
+std::vector<std::string> ALSServingModel::getAllItemIDs() const {
+  std::lock_guard<std::mutex> lk(mu_);
+  std::vector<std::string> out;
+  out.reserve(item_row_.size());
+  for (const auto& kv : item_row_) out.push_back(kv.first);
+  return out;
 }
 
 int ALSServingModel::getNumUsers() const { std::lock_guard<std::mutex> lk(mu_); return (int)X_.size(); }
@@ -369,6 +405,11 @@ float ALSServingModel::getFractionLoaded() const {
   if (expected == 0) return 1.0f;
   float loaded = (float)X_.size() + (float)item_row_.size();
   return loaded / (loaded + expected);
+}
+
+int ALSServingModel::itemRow(const std::string& item) const {
+  std::lock_guard<std::mutex> lk(mu_);
+  return rowOf(item);
 }
 
 int ALSServingModel::partitionOf(const std::string& item) const {
@@ -391,11 +432,57 @@ ALSSpeedModel::~ALSSpeedModel() { oryx_model_destroy(h_); }
 
 void ALSSpeedModel::set(Side& side, int which, const std::string& id, const FloatVec& v) {
   if ((int)v.size() != features_) throw std::invalid_argument("vector.length != features");
-  auto it = side.row.find(id);
-  int32_t row = it == side.row.end() ? (int32_t)side.row.size() : it->second;
-  side.row[id] = row;
-  side.vec[id] = v;
-  check_status(oryx_items_upsert(h_, which, &row, v.data(), 1, nullptr));
+  (void)side;
+  setVectors(which == ORYX_X ? 'X' : 'Y', &id, v.data(), 1);
+}
+
+void ALSSpeedModel::setVectors(char whichChar, const std::string* ids, const float* vecs, size_t n) {
+  if (n == 0) return;
+  Side& side = whichChar == 'X' ? x_ : y_;
+  const int which = whichChar == 'X' ? ORYX_X : ORYX_Y;
+  const size_t f = (size_t)features_;
+  std::vector<int32_t> rows(n);
+  for (size_t i = 0; i < n; i++) {
+    auto it = side.row.find(ids[i]);
+    int32_t row;
+    if (it == side.row.end()) {
+      if (!side.free_rows.empty()) { row = side.free_rows.back(); side.free_rows.pop_back(); }
+      else row = side.next_row++;
+      side.row.emplace(ids[i], row);
+      side.recent.insert(ids[i]);  // FeatureVectors.java:74-77
+    } else {
+      row = it->second;
+    }
+    rows[i] = row;
+    side.vec[ids[i]].assign(vecs + i * f, vecs + (i + 1) * f);
+    if (!side.expected.empty()) side.expected.erase(ids[i]);
+  }
+  check_status(oryx_items_upsert(h_, which, rows.data(), vecs, (int32_t)n, nullptr));
+}
+
+void ALSSpeedModel::retain(Side& side, int which, const std::vector<std::string>& ids) {
+  std::unordered_set<std::string> keep(ids.begin(), ids.end());
+  std::vector<int32_t> drop;
+  for (auto it = side.row.begin(); it != side.row.end();) {
+    if (keep.count(it->first) || side.recent.count(it->first)) { ++it; continue; }
+    drop.push_back(it->second);
+    side.free_rows.push_back(it->second);
+    side.vec.erase(it->first);
+    it = side.row.erase(it);
+  }
+  side.recent.clear();
+  side.expected.clear();
+  for (const auto& id : ids) if (!side.row.count(id)) side.expected.insert(id);
+  if (!drop.empty()) check_status(oryx_items_remove(h_, which, drop.data(), (int32_t)drop.size()));
+}
+void ALSSpeedModel::retainRecentAndUserIDs(const std::vector<std::string>& users) { retain(x_, ORYX_X, users); }
+void ALSSpeedModel::retainRecentAndItemIDs(const std::vector<std::string>& items) { retain(y_, ORYX_Y, items); }
+
+float ALSSpeedModel::getFractionLoaded() const {
+  int expected = (int)x_.expected.size() + (int)y_.expected.size();
+  if (expected == 0) return 1.0f;
+  float loaded = (float)x_.row.size() + (float)y_.row.size();
+  return loaded / (loaded + expected);
 }
 void ALSSpeedModel::setUserVector(const std::string& user, const FloatVec& v) { set(x_, ORYX_X, user, v); }
 void ALSSpeedModel::setItemVector(const std::string& item, const FloatVec& v) { set(y_, ORYX_Y, item, v); }

@@ -126,6 +126,7 @@ class ALSServingModel {
   void setItemVector(const std::string& item, const FloatVec& vector);              // :161-183
   // bulk form of setItemVector for model load (one C ABI call)
   void setItemVectors(const std::vector<std::string>& items, const std::vector<float>& vectorsRowMajor);
+  void setItemVectors(const std::string* items, const float* vectorsRowMajor, size_t n);
   std::unordered_set<std::string> getKnownItems(const std::string& user) const;     // :189-201
   void addKnownItems(const std::string& user, const std::vector<std::string>& items);  // :241-258
   std::unique_ptr<std::vector<std::pair<std::string, FloatVec>>> getKnownItemVectorsForUser(const std::string& user) const;  // :264-287
@@ -136,11 +137,15 @@ class ALSServingModel {
                             const std::unordered_set<std::string>* excludedIDs) const;
 
   std::shared_ptr<Solver> getYTYSolver();                                           // :357-373
-  void retainRecentAndUserIDs(const std::vector<std::string>& users);               // :382-389 (no "recent" window here)
+  // IDs set since the previous retain call count as "recent" and survive (FeatureVectors.java:72-79, 131-136)
+  void retainRecentAndUserIDs(const std::vector<std::string>& users);               // :382-389
   void retainRecentAndItemIDs(const std::vector<std::string>& items);               // :398-409
+  void retainRecentAndKnownItems(const std::vector<std::string>& users, const std::vector<std::string>& items);  // :418-441
+  std::vector<std::string> getAllItemIDs() const;                                   // :337-343
   int getNumUsers() const;
   int getNumItems() const;
   float getFractionLoaded() const;                                                  // :462-475
+  int itemRow(const std::string& item) const;  // dense device row of an item, -1 when unknown
   int partitionOf(const std::string& item) const;  // LSH partition the device assigned (diagnostics/tests)
   oryx_model* handle() const { return h_; }
 
@@ -159,6 +164,7 @@ class ALSServingModel {
   std::unordered_map<std::string, int> item_partition_;
   std::unordered_map<std::string, std::unordered_set<std::string>> known_items_;
   std::unordered_set<std::string> expected_users_, expected_items_;
+  std::unordered_set<std::string> recent_users_, recent_items_;
   std::shared_ptr<Solver> cached_yty_;
 };
 
@@ -180,8 +186,17 @@ class ALSSpeedModel {
  public:
   ALSSpeedModel(int features, bool implicit, int device = 0);
   ~ALSSpeedModel();
+  int getFeatures() const { return features_; }
+  bool isImplicit() const { return implicit_; }
   void setUserVector(const std::string& user, const FloatVec& vector);
   void setItemVector(const std::string& item, const FloatVec& vector);
+  // bulk form for the update stream: which = 'X' or 'Y'; one C ABI call
+  void setVectors(char which, const std::string* ids, const float* vectorsRowMajor, size_t n);
+  void retainRecentAndUserIDs(const std::vector<std::string>& users);  // ALSSpeedModel.java:98-105
+  void retainRecentAndItemIDs(const std::vector<std::string>& items);  // :107-114
+  float getFractionLoaded() const;                                      // :127-141
+  int getNumUsers() const { return (int)x_.row.size(); }
+  int getNumItems() const { return (int)y_.row.size(); }
   std::unique_ptr<FloatVec> getUserVector(const std::string& user) const;
   std::unique_ptr<FloatVec> getItemVector(const std::string& item) const;
   std::shared_ptr<Solver> getXTXSolver();  // ALSSpeedModel.java:118-121
@@ -194,8 +209,12 @@ class ALSSpeedModel {
   struct Side {
     std::unordered_map<std::string, int> row;
     std::unordered_map<std::string, FloatVec> vec;  // host copy for fold-in gathers
+    std::vector<int> free_rows;
+    int next_row = 0;
+    std::unordered_set<std::string> recent, expected;
   };
   void set(Side& side, int which, const std::string& id, const FloatVec& v);
+  void retain(Side& side, int which, const std::vector<std::string>& ids);
   std::shared_ptr<Solver> solver(int which);
   int features_;
   bool implicit_;

@@ -11,6 +11,7 @@
 #include <string>
 
 #include "oryx_host.hpp"
+#include "update_stream.hpp"
 
 using namespace oryx::host;
 
@@ -177,8 +178,11 @@ static void testServingGoldens() {
     }
     CHECK((items[0] == "I0" || items[0] == "I3") && items[1] == "I4");
   }
-  {  // model bookkeeping: T/model/ALSServingModelTest.java:75-132 (retain) and :222-234 (fraction loaded)
-    model.retainRecentAndItemIDs({"I0", "I1", "I2", "I3", "I4", "I5", "I6", "I7", "I99"});
+  {  // model bookkeeping on the golden model: rows set since the last retain are "recent" and survive one call
+    const std::vector<std::string> keep = {"I0", "I1", "I2", "I3", "I4", "I5", "I6", "I7", "I99"};
+    model.retainRecentAndItemIDs(keep);
+    CHECK(model.getNumItems() == 9 && model.getItemVector("I8") != nullptr);  // protected: recent
+    model.retainRecentAndItemIDs(keep);
     CHECK(model.getNumItems() == 8);
     CHECK(model.getItemVector("I8") == nullptr);
     CHECK(model.getFractionLoaded() < 1.0f);  // I99 is expected but absent
@@ -186,6 +190,60 @@ static void testServingGoldens() {
     CHECK(model.getFractionLoaded() == 1.0f);
     auto recs = recommend(model, "U0", 10, 0, true);
     for (const auto& r : recs) CHECK(r.first != "I8");
+  }
+  {  // T/model/ALSServingModelTest.java:75-103 testRetainUsersItems
+    ALSServingModel m(2, true, 1.0);
+    m.setUserVector("U0", {1.0f, 1.0f});
+    m.retainRecentAndUserIDs({});
+    CHECK(m.getUserVector("U0") != nullptr);  // protected because of recent users/items
+    m.retainRecentAndUserIDs({});
+    CHECK(m.getUserVector("U0") == nullptr);
+    m.setUserVector("U0", {1.0f, 1.0f});
+    m.retainRecentAndUserIDs({"U0"});
+    CHECK(m.getUserVector("U0") != nullptr);
+    m.retainRecentAndUserIDs({"U0"});
+    CHECK(m.getUserVector("U0") != nullptr);
+    m.setItemVector("I0", {1.0f, 1.0f});
+    m.retainRecentAndItemIDs({});
+    CHECK(m.getItemVector("I0") != nullptr);
+    m.retainRecentAndItemIDs({});
+    CHECK(m.getItemVector("I0") == nullptr);
+    m.setItemVector("I0", {1.0f, 1.0f});
+    m.retainRecentAndItemIDs({"I0"});
+    CHECK(m.getItemVector("I0") != nullptr);
+    m.retainRecentAndItemIDs({"I0"});
+    CHECK(m.getItemVector("I0") != nullptr);
+  }
+  {  // T/model/ALSServingModelTest.java:105-132 testRetainKnown (populateKnownItems :142-152)
+    ALSServingModel m(2, true, 1.0);
+    for (int i = 0; i < 10; i++)
+      for (int j = 0; j < 10; j++)
+        if (std::abs(i - j) <= 1) m.addKnownItems("U" + std::to_string(i), {"I" + std::to_string(j)});
+    for (int i = 0; i < 10; i++) {
+      m.setUserVector("U" + std::to_string(i), {0.0f, 0.0f});
+      m.setItemVector("I" + std::to_string(i), {0.0f, 0.0f});
+    }
+    m.retainRecentAndKnownItems({"U4", "U5", "U6"}, {"I4", "I5", "I6"});
+    CHECK(m.getKnownItems("U3").count("I4") && m.getKnownItems("U4").count("I4"));
+    CHECK(m.getKnownItems("U6").count("I6") && m.getKnownItems("U6").count("I7"));
+    CHECK(m.getKnownItems("U2").count("I2"));  // protected because of recent users/items
+    m.retainRecentAndUserIDs({});              // clears recent users/items
+    m.retainRecentAndItemIDs({});
+    m.retainRecentAndKnownItems({"U4", "U5", "U6"}, {"I4", "I5", "I6"});
+    CHECK(m.getKnownItems("U3").empty());
+    CHECK(m.getKnownItems("U4").count("I4") && m.getKnownItems("U6").count("I6"));
+    CHECK(!m.getKnownItems("U6").count("I7") && m.getKnownItems("U2").empty());
+  }
+  {  // T/model/ALSServingModelTest.java:222-234 testFractionLoaded
+    ALSServingModel m(2, true, 1.0);
+    CHECK(m.getFractionLoaded() == 1.0f);
+    m.retainRecentAndUserIDs({"U1"});
+    m.retainRecentAndItemIDs({"I0"});
+    CHECK(m.getFractionLoaded() == 0.0f);
+    m.setUserVector("U1", {1.5f, -2.5f});
+    CHECK(m.getFractionLoaded() == 0.5f);
+    m.setItemVector("I0", {0.5f, 0.0f});
+    CHECK(m.getFractionLoaded() == 1.0f);
   }
   {  // argument checking: ALSServingModel.java:98-99,154,162 -> IllegalArgumentException
     bool threw = false;
@@ -293,12 +351,165 @@ static void testSolverAndALSUtils() {
   CHECK(c && (*c)[0] == 0.16086957f && (*c)[1] == 0.14565217f);
 }
 
+// ---- the update topic as MockALSModelUpdateGenerator.java:67-100 produces it: message 0 is the MODEL
+// skeleton, messages 1..9 are "UP" payloads (ids 1-5 are Y rows with known users, 6-9 X rows with known items)
+static std::string idToStringID(int id) { return std::string(1, (char)('A' + id % 26)) + std::to_string(id); }  // ALSUtilsTest.java:50-52
+static const float GEN_X[4][2] = {{-0.6790019f, 0.1732324f}, {-0.8232442f, -0.9200852f}, {-1.1865344f, 0.44631857f}, {-0.20789514f, 0.5303508f}};
+static const float GEN_Y[5][2] = {{-0.7203235f, 0.45654634f}, {-0.77601856f, -0.34911805f}, {-0.5384191f, 0.7197065f},
+                                  {-1.0381957f, -0.22146331f}, {-0.31787223f, -0.6780096f}};
+static const std::vector<std::vector<std::string>> GEN_A = {{"1", "4"}, {"2", "4", "5"}, {"1", "2", "3", "4"}, {"3"}};        // users 6..9
+static const std::vector<std::vector<std::string>> GEN_At = {{"6", "8"}, {"7", "8"}, {"8", "9"}, {"6", "7", "8"}, {"7"}};     // items 1..5
+static std::vector<KeyMessage> mockUpdateTopic() {
+  std::vector<KeyMessage> out;
+  std::string xids, yids;
+  for (int i = 6; i <= 9; i++) xids += (xids.empty() ? "" : " ") + idToStringID(i);
+  for (int i = 1; i <= 5; i++) yids += (yids.empty() ? "" : " ") + idToStringID(i);
+  out.push_back({"MODEL",
+                 "<?xml version=\"1.0\" encoding=\"UTF-8\" standalone=\"yes\"?>\n<PMML version=\"4.3\" "
+                 "xmlns=\"http://www.dmg.org/PMML-4_3\">\n    <Header>\n        <Application name=\"Oryx\"/>\n"
+                 "        <Timestamp>2026-01-01T00:00:00+0000</Timestamp>\n    </Header>\n"
+                 "    <Extension name=\"features\" value=\"2\"/>\n    <Extension name=\"implicit\" value=\"true\"/>\n"
+                 "    <Extension name=\"XIDs\">" + xids + "</Extension>\n    <Extension name=\"YIDs\">" + yids +
+                 "</Extension>\n</PMML>\n"});
+  auto others = [](const std::vector<std::string>& v) {
+    std::string s = "[";
+    for (size_t i = 0; i < v.size(); i++) s += (i ? ",\"" : "\"") + v[i] + "\"";
+    return s + "]";
+  };
+  for (int id = 1; id <= 9; id++) {
+    std::string msg;
+    if (id >= 6) {
+      msg = toUpdateJSON('X', idToStringID(id), GEN_X[id - 6], 2, nullptr);
+      msg.insert(msg.size() - 1, "," + others(GEN_A[id - 6]));
+    } else {
+      msg = toUpdateJSON('Y', idToStringID(id), GEN_Y[id - 1], 2, nullptr);
+      msg.insert(msg.size() - 1, "," + others(GEN_At[id - 1]));
+    }
+    out.push_back({"UP", msg});
+  }
+  return out;
+}
+
+// SERVING-T/als/model/ALSServingModelManagerIT.java:35-69
+static void testServingModelManager() {
+  ALSServingModelManager manager(1.0, 4);
+  auto topic = mockUpdateTopic();
+  manager.consume({topic[5]});  // an "UP" before any MODEL is skipped (ALSServingModelManager.java:73-75)
+  CHECK(manager.getModel() == nullptr);
+  manager.consume(topic);
+  ALSServingModel* model = manager.getModel();
+  CHECK(model != nullptr);
+  if (!model) return;
+  CHECK(model->getFeatures() == 2 && model->isImplicit());
+  auto ids = model->getAllItemIDs();
+  std::set<std::string> got(ids.begin(), ids.end()), want;
+  for (int i = 1; i <= 5; i++) want.insert(idToStringID(i));
+  CHECK(got == want);
+  CHECK(model->getYTYSolver() != nullptr);
+  for (int i = 6; i <= 9; i++) {
+    auto v = model->getUserVector(idToStringID(i));
+    CHECK(v && (*v)[0] == GEN_X[i - 6][0] && (*v)[1] == GEN_X[i - 6][1]);
+    auto known = model->getKnownItems(idToStringID(i));
+    CHECK(known == std::unordered_set<std::string>(GEN_A[i - 6].begin(), GEN_A[i - 6].end()));
+  }
+  for (int i = 1; i <= 5; i++) {
+    auto v = model->getItemVector(idToStringID(i));
+    CHECK(v && (*v)[0] == GEN_Y[i - 1][0] && (*v)[1] == GEN_Y[i - 1][1]);
+  }
+  CHECK(model->getFractionLoaded() == 1.0f);
+  // a second MODEL naming fewer ids: ids set since the previous MODEL are "recent" and survive once
+  // (FeatureVectors.java:131-136), then go
+  KeyMessage smaller = topic[0];
+  size_t at = smaller.message.find(idToStringID(5));
+  smaller.message.erase(at - 1, idToStringID(5).size() + 1);
+  manager.consume({smaller});
+  CHECK(model->getItemVector(idToStringID(5)) != nullptr);
+  manager.consume({smaller});
+  CHECK(model->getItemVector(idToStringID(5)) == nullptr && model->getNumItems() == 4);
+  // malformed traffic: the stream stops at the bad message, earlier ones are applied
+  bool threw = false;
+  try {
+    manager.consume({{"UP", "[\"Y\",\"N1\",[1.0,2.0]]"}, {"UP", "[\"Q\",\"N2\",[1.0,2.0]]"}, {"UP", "[\"Y\",\"N3\",[1.0,2.0]]"}});
+  } catch (const BadMessage&) { threw = true; }
+  CHECK(threw && model->getItemVector("N1") != nullptr && model->getItemVector("N3") == nullptr);
+  threw = false;
+  try { manager.consume({{"UP", "[\"Y\",\"N4\",[1.0,2.0,3.0]]"}}); } catch (const std::invalid_argument&) { threw = true; }
+  CHECK(threw);  // checkArgument(vector.length == features), ALSServingModel.java:162
+  threw = false;
+  try { manager.consume({{"WHAT", "x"}}); } catch (const std::invalid_argument&) { threw = true; }
+  CHECK(threw);  // ALSServingModelManager.java:125-126
+  // part-file bulk load (ALSUpdate.java:415-428 format)
+  std::string text;
+  std::vector<int64_t> begin{0};
+  for (int i = 0; i < 3000; i++) {
+    float v[2] = {(float)i * 0.25f, -1.0f / (float)(i + 1)};
+    text += toFeatureLine("bulk" + std::to_string(i), v, 2);
+    begin.push_back((int64_t)text.size());
+  }
+  manager.loadFeatureLines('Y', text.data(), begin.data(), 3000);
+  auto v = model->getItemVector("bulk2999");
+  CHECK(v && (*v)[0] == 2999 * 0.25f && (*v)[1] == -1.0f / 3000.0f && model->getNumItems() == 4 + 1 + 3000);
+}
+
+// SPEED-T/ALSSpeedIT.java:50-113 end to end through the text formats: update topic in, input lines in,
+// "UP" payloads out
+static void testSpeedModelManager() {
+  ALSSpeedModelManager manager(/*noKnownItems=*/false);
+  CHECK(manager.buildUpdates({"a,b,1,1"}).empty());  // no model yet (ALSSpeedModelManager.java:136-138)
+  manager.consume(mockUpdateTopic());
+  CHECK(manager.getModel() && manager.getModel()->getFeatures() == 2 && manager.getModel()->isImplicit());
+  std::vector<std::string> lines;  // MockALSInputGenerator.java:26-37, ids 0..8
+  for (int id = 0; id < 9; id++) {
+    std::string large = idToStringID(100 + id), small = idToStringID(1 + id);
+    lines.push_back((id < 5 ? large + "," + small : small + "," + large) + ",1," + std::to_string(1000 + id));
+  }
+  auto updates = manager.buildUpdates(lines);
+  CHECK(updates.size() == 9);
+  const float EX[5][2] = {{-0.20859924f, 0.25232133f}, {-0.22472803f, -0.1929485f}, {-0.15592135f, 0.3977631f},
+                          {-0.3006522f, -0.12239703f}, {-0.09205295f, -0.37471837f}};
+  const float EY[4][2] = {{-0.19663288f, 0.09574106f}, {-0.23840417f, -0.50850725f}, {-0.34360975f, 0.2466687f},
+                          {-0.060204573f, 0.29311115f}};
+  for (const auto& msg : updates) {
+    char matrix;
+    std::string id;
+    std::vector<float> vec;
+    bool has;
+    std::vector<std::string> others;
+    parseFeatureMessage(msg, true, &matrix, &id, &vec, &has, &others);
+    int n = std::atoi(id.c_str() + 1);
+    const float* e = matrix == 'X' ? EX[n - 100] : EY[n - 105];
+    CHECK((matrix == 'X') == (n < 105) && vec.size() == 2);
+    CHECK_NEAR(e[0], vec[0], 1.0e-5);
+    CHECK_NEAR(e[1], vec[1], 1.0e-5);
+    CHECK(has && others.size() == 1 && others[0] == idToStringID(n - 99));  // ALSSpeedIT.java:107-111
+  }
+  // aggregation (ALSSpeedModelManager.java:141-171): timestamp order, implicit sums with NaN as a
+  // delete marker, explicit last-wins
+  std::vector<std::string> agg = {"u,i,2,30", "u,i,1,10", "u,j,NaN,5", "[\"u\",\"i\",\"4\",20]", "v,i,1,7", "v,i,NaN,8", "w,k,3,1", "w,k,NaN,2", "w,k,5,3"};
+  auto imp = manager.aggregate(agg, true);
+  CHECK(imp.size() == 2 && imp[0].user == "w" && imp[0].strength == 5.0 && imp[1].user == "u" && imp[1].item == "i" && imp[1].strength == 7.0);
+  auto exp = manager.aggregate(agg, false);
+  CHECK(exp.size() == 2 && exp[0].user == "w" && exp[0].strength == 5.0 && exp[1].user == "u" && exp[1].strength == 2.0);
+  bool threw = false;
+  try { manager.aggregate({"u,i,,1"}, true); } catch (const BadMessage&) { threw = true; }
+  CHECK(threw);  // Double.valueOf("") -> NumberFormatException
+  threw = false;
+  try { manager.aggregate({"u,i,1"}, true); } catch (const BadMessage&) { threw = true; }
+  CHECK(threw);  // tokens[3] -> ArrayIndexOutOfBoundsException
+  ALSSpeedModelManager quiet(/*noKnownItems=*/true);
+  quiet.consume(mockUpdateTopic());
+  auto q = quiet.buildUpdates({lines[0]});
+  CHECK(q.size() == 1 && q[0].find("],[") == std::string::npos);  // no trailing known-ids element (:209-210)
+}
+
 int main() {
   try {
     testSolverAndALSUtils();
     testServingGoldens();
     testLSH();
     testSpeedFoldIn();
+    testServingModelManager();
+    testSpeedModelManager();
   } catch (const std::exception& e) {
     std::printf("EXCEPTION: %s\n", e.what());
     return 2;
