@@ -372,6 +372,51 @@ def run_ours(args):
         e2e_s = float(t.item())
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- not part of the headline: /recommend by user row, query vector and known items taken from
+    # device-resident state (oryx_recommend) vs the same request shipping its exclusion list (oryx_topn)
+    extras = None
+    if world == 1:
+        rng = np.random.default_rng(0xB2000040)
+        model.upsert(ob.X, np.arange(N_QUERIES, dtype=np.int32), q_host)
+        known = [rng.integers(0, n_items, int(k)).astype(np.int32) for k in rng.poisson(20, N_QUERIES)]
+        model.known_items_add(np.arange(N_QUERIES), known)
+        for i in range(3):
+            model.recommend(i, HOW_MANY)
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            model.recommend(i % N_QUERIES, HOW_MANY)
+        rec_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            model.topn(ob.DOT, q_host[i % N_QUERIES], HOW_MANY, known[i % N_QUERIES])
+        top_s = time.perf_counter() - t0
+        a = model.recommend(5, HOW_MANY)
+        b = model.topn(ob.DOT, q_host[5], HOW_MANY, known[5])
+        # the reference serves many request threads at once (ServingLayer.java:225): the same host-buffer
+        # call from 4 caller threads, each on its own query context / stream
+        import threading
+        n_callers = 4
+        per = max(1, args.steps // n_callers)
+
+        def caller(t):
+            for i in range(per):
+                model.topn(ob.DOT, q_host[(t * per + i) % N_QUERIES], HOW_MANY)
+        threads_ = [threading.Thread(target=caller, args=(t,)) for t in range(n_callers)]
+        t0 = time.perf_counter()
+        for th in threads_:
+            th.start()
+        for th in threads_:
+            th.join()
+        conc_s = time.perf_counter() - t0
+        extras = {"e2e_concurrent_callers": {"callers": n_callers, "value": n_callers * per / conc_s, "unit": UNIT,
+                                             "ms_per_query_aggregate": 1000.0 * conc_s / (n_callers * per)},
+                  "recommend_by_user_row": {
+            "ms_per_call_device_state": 1000.0 * rec_s / args.steps,
+            "ms_per_call_exclusions_shipped": 1000.0 * top_s / args.steps,
+            "known_items_per_user": "Poisson(20), LoadTestALSModelFactory.java:62-95",
+            "h2d_bytes_per_call_device_state": 0,
+            "identical_results": bool(a[0].tolist() == b[0].tolist() and a[1].tobytes() == b[1].tobytes())}}
+
     # ---- numbers
     ms_per_step = ms_total / args.steps
     scans_per_query = world * (n_items / ITEMS_PER_GPU)   # units of "one 10M-item scan"
@@ -426,6 +471,7 @@ def run_ours(args):
                     "ms_per_step": 1000.0 * e2e_s / args.steps},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
+            "extras": extras,
         }
         print(json.dumps(line), flush=True)
     model.close()

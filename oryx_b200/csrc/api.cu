@@ -86,7 +86,7 @@ void ctx_release(Model* m, QueryCtx* ctx) {
   m->pool_cv.notify_one();
 }
 
-static int32_t ensure_excl(QueryCtx* c, int32_t n) {
+int32_t ensure_excl(QueryCtx* c, int32_t n) {
   if (n <= c->excl_cap) return ORYX_OK;
   int32_t cap = std::max(n, c->excl_cap * 2);
   cudaFree(c->d_excl); cudaFreeHost(c->h_excl);
@@ -115,6 +115,44 @@ struct DeviceGuard {
     return ORYX_E_CUDA;                                                  \
   }
 
+// Second half of a query: the query vector and the sorted exclusion slots already sit in device
+// memory (d_query; c->d_excl[0..n_excl_slots)).  Launch, copy the packed record back, wait.
+static int32_t run_topn_staged(Model* m, QueryCtx* c, int32_t kind, const float* d_query, int32_t n_excl_slots,
+                               int32_t how_many, int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  // packed result record (see ctx_create)
+  const size_t rows_off = 8, scores_off = 8 + (((size_t)how_many * 4 + 7) & ~(size_t)7);
+  const size_t rec_bytes = scores_off + (size_t)how_many * 8;
+  unsigned char* d_rec = reinterpret_cast<unsigned char*>(c->d_out_n);
+  unsigned char* h_rec = reinterpret_cast<unsigned char*>(c->h_out_n);
+  TopnRequest rq{};
+  rq.kind = kind;
+  rq.d_query = d_query;
+  rq.how_many = how_many;
+  rq.d_excl = c->d_excl;
+  rq.n_excl = n_excl_slots;
+  rq.d_out_n = reinterpret_cast<int32_t*>(d_rec);
+  rq.d_out_rows = reinterpret_cast<int32_t*>(d_rec + rows_off);
+  rq.d_out_scores = reinterpret_cast<double*>(d_rec + scores_off);
+  ORYX_CUDA(cudaEventRecord(c->ev0, c->stream));
+  ORYX_TRY(scan_topn_launch(m, c, rq, c->stream));
+  ORYX_CUDA(cudaEventRecord(c->ev1, c->stream));
+  ORYX_CUDA(cudaMemcpyAsync(h_rec, d_rec, rec_bytes, cudaMemcpyDeviceToHost, c->stream));
+  ORYX_CUDA(cudaStreamSynchronize(c->stream));
+  int32_t n = *reinterpret_cast<int32_t*>(h_rec);
+  if (n < 0 || n > how_many) {
+    set_error("device returned an impossible result count %d", n);
+    return ORYX_E_CUDA;
+  }
+  std::memcpy(out_rows, h_rec + rows_off, (size_t)n * sizeof(int32_t));
+  std::memcpy(out_scores, h_rec + scores_off, (size_t)n * sizeof(double));
+  *out_n = n;
+  m->queries++;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);
+  else cudaGetLastError();
+  return ORYX_OK;
+}
+
 // One query through a context: stage, launch, copy back, wait.
 static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query, int32_t how_many,
                         const int32_t* excluded_rows, int32_t n_excluded, int32_t* out_rows,
@@ -138,37 +176,7 @@ static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query,
       ORYX_CUDA(cudaMemcpyAsync(c->d_excl, c->h_excl, (size_t)n_excl_slots * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
     }
   }
-  // packed result record (see ctx_create)
-  const size_t rows_off = 8, scores_off = 8 + (((size_t)how_many * 4 + 7) & ~(size_t)7);
-  const size_t rec_bytes = scores_off + (size_t)how_many * 8;
-  unsigned char* d_rec = reinterpret_cast<unsigned char*>(c->d_out_n);
-  unsigned char* h_rec = reinterpret_cast<unsigned char*>(c->h_out_n);
-  TopnRequest rq{};
-  rq.kind = kind;
-  rq.d_query = c->d_query;
-  rq.how_many = how_many;
-  rq.d_excl = c->d_excl;
-  rq.n_excl = n_excl_slots;
-  rq.d_out_n = reinterpret_cast<int32_t*>(d_rec);
-  rq.d_out_rows = reinterpret_cast<int32_t*>(d_rec + rows_off);
-  rq.d_out_scores = reinterpret_cast<double*>(d_rec + scores_off);
-  ORYX_CUDA(cudaEventRecord(c->ev0, c->stream));
-  ORYX_TRY(scan_topn_launch(m, c, rq, c->stream));
-  ORYX_CUDA(cudaEventRecord(c->ev1, c->stream));
-  ORYX_CUDA(cudaMemcpyAsync(h_rec, d_rec, rec_bytes, cudaMemcpyDeviceToHost, c->stream));
-  ORYX_CUDA(cudaStreamSynchronize(c->stream));
-  int32_t n = *reinterpret_cast<int32_t*>(h_rec);
-  if (n < 0 || n > how_many) {
-    set_error("device returned an impossible result count %d", n);
-    return ORYX_E_CUDA;
-  }
-  std::memcpy(out_rows, h_rec + rows_off, (size_t)n * sizeof(int32_t));
-  std::memcpy(out_scores, h_rec + scores_off, (size_t)n * sizeof(double));
-  *out_n = n;
-  float ms = 0.f;
-  if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);
-  else cudaGetLastError();
-  return ORYX_OK;
+  return run_topn_staged(m, c, kind, c->d_query, n_excl_slots, how_many, out_rows, out_scores, out_n);
 }
 
 }  // namespace oryx
@@ -249,6 +257,7 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     for (auto& c : m->pool_all) ctx_destroy(c.get());
     store_free(&m->store[0]);
     store_free(&m->store[1]);
+    known_free(&m->known);
     cudaFree(m->d_hash_vectors);
     for (auto& b : m->batch.buf) cudaFree(b);
     cudaFree(m->d_debug_ts);
@@ -405,6 +414,92 @@ int32_t oryx_topn(oryx_model* mh, int32_t kind, const float* query, int32_t how_
   {
     std::shared_lock<std::shared_mutex> lk(m->mu);
     rc = run_topn(m, c, kind, query, how_many, excluded_rows, n_excluded, out_rows, out_scores, out_n);
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
+  ctx_release(m, c);
+  return rc;
+}
+
+// ---- known items on the device (known.cu)
+
+int32_t oryx_known_items_add(oryx_model* mh, const int32_t* user_rows, const int64_t* begin, const int32_t* item_rows,
+                             int32_t n_users) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(n_users >= 0, "n_users must be >= 0");
+  if (n_users == 0) return ORYX_OK;
+  ORYX_ARG(user_rows && begin, "null argument");
+  ORYX_ARG(begin[n_users] == begin[0] || item_rows, "null item_rows");
+  for (int32_t i = 0; i < n_users; i++) ORYX_ARG(begin[i + 1] >= begin[i], "begin[] must be non-decreasing");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return known_add(m, user_rows, begin, item_rows, n_users);
+}
+
+int32_t oryx_known_items_get(oryx_model* mh, int32_t user_row, int32_t* out_rows, int32_t cap, int32_t* out_n) {
+  ORYX_ARG(mh && out_n, "null argument");
+  ORYX_ARG(cap >= 0 && (cap == 0 || out_rows), "bad output buffer");
+  Model* m = reinterpret_cast<Model*>(mh);
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  *out_n = 0;
+  if (user_row < 0 || (size_t)user_row >= m->known.lists.size()) return ORYX_OK;
+  const std::vector<int32_t>& list = m->known.lists[(size_t)user_row];
+  *out_n = (int32_t)list.size();
+  if ((int32_t)list.size() > cap) {
+    set_error("known-items list of user row %d has %d entries, buffer holds %d", user_row, (int)list.size(), cap);
+    return ORYX_E_NOMEM;
+  }
+  std::copy(list.begin(), list.end(), out_rows);
+  return ORYX_OK;
+}
+
+int32_t oryx_known_items_retain(oryx_model* mh, const uint8_t* keep_users, int32_t n_user_rows,
+                                const uint8_t* keep_items, int32_t n_item_rows) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(n_user_rows >= 0 && n_item_rows >= 0, "row counts must be >= 0");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return known_retain(m, keep_users, n_user_rows, keep_items, n_item_rows);
+}
+
+int32_t oryx_known_counts(oryx_model* mh, int32_t which, int32_t* out_counts, int32_t n_rows) {
+  ORYX_ARG(mh, "null model");
+  ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(n_rows >= 0, "n_rows must be >= 0");
+  if (n_rows == 0) return ORYX_OK;
+  ORYX_ARG(out_counts, "null output");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  // the count kernel runs on the update stream: exclusive, like any other use of that stream
+  std::unique_lock<std::shared_mutex> lk(m->mu);
+  return known_counts(m, which, out_counts, n_rows);
+}
+
+int32_t oryx_recommend(oryx_model* mh, int32_t user_row, int32_t how_many, int32_t consider_known_items,
+                       int32_t* out_rows, double* out_scores, int32_t* out_n, int32_t* found) {
+  ORYX_ARG(mh && out_rows && out_scores && out_n && found, "null argument");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  *out_n = 0;
+  *found = 0;
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc = ORYX_OK;
+  {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    Store* x = &m->store[ORYX_X];
+    const int32_t slot = (user_row >= 0 && (size_t)user_row < x->row2slot.size()) ? x->row2slot[(size_t)user_row] : -1;
+    if (slot >= 0) {
+      *found = 1;
+      // the query vector is the user's row of the device-resident X store (Recommend.java:84-90);
+      // both stores pad rows to the same fpad
+      const float* d_query = x->d_vec + (int64_t)slot * x->fpad;
+      int32_t n_excl = 0;
+      if (!consider_known_items) rc = known_exclusions_device(m, c, user_row, &n_excl, c->stream);
+      if (rc == ORYX_OK) rc = run_topn_staged(m, c, ORYX_DOT, d_query, n_excl, how_many, out_rows, out_scores, out_n);
+    }
   }
   if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
   ctx_release(m, c);

@@ -104,8 +104,26 @@ struct Store {
 
   std::vector<int32_t> row2slot;
   std::vector<int32_t> free_slots;
+  // Device copy of row -> slot (-1 = absent), kept for the Y store only: lets a query translate a
+  // device-resident list of known-item ROWS into the slots the scan filters on (known.cu).
+  bool track_row_slot = false;
+  int32_t* d_row_slot = nullptr;
+  int64_t row_slot_cap = 0;
 
-  int64_t device_bytes() const { return cap_slots * ((int64_t)fpad * 4 + 8); }
+  int64_t device_bytes() const { return cap_slots * ((int64_t)fpad * 4 + 8) + row_slot_cap * 4; }
+};
+
+// ---- known items (ALSServingModel.java:75-76 knownItems, :189-258): per user row, the item rows the
+// user has interacted with.  The host keeps the authoritative sorted lists (set semantics of
+// addKnownItems); a mirror of every list lives in one device pool so that a /recommend query takes
+// its exclusion list from HBM instead of receiving it from the caller.
+struct KnownItems {
+  std::vector<std::vector<int32_t>> lists;  // [user row] sorted unique item rows
+  std::vector<int64_t> seg_off;             // [user row] start of the user's segment in the pool
+  std::vector<int32_t> seg_cap;             // [user row] capacity of that segment (0 = none yet)
+  int32_t* d_pool = nullptr;
+  int64_t pool_cap = 0, pool_used = 0, pool_garbage = 0;
+  int64_t total = 0;                        // sum of list sizes
 };
 
 // ---- per-query resources: a stream, device staging, scratch for the per-CTA candidate lists and
@@ -163,6 +181,7 @@ struct Model {
   float* d_hash_vectors = nullptr;  // [num_hashes x fpad]
   std::vector<float> h_hash_vectors;
   Store store[2];
+  KnownItems known;
 
   std::shared_mutex mu;  // queries shared, mutations exclusive
   cudaStream_t update_stream = nullptr;
@@ -197,6 +216,18 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
 int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n);
 int32_t store_get(Model* m, int which, int32_t row, float* out, int32_t* found);
 int32_t store_compact(Model* m, int which);
+
+// known.cu
+void known_free(KnownItems* k);
+int32_t known_add(Model* m, const int32_t* user_rows, const int64_t* begin, const int32_t* item_rows, int32_t n_users);
+int32_t known_retain(Model* m, const uint8_t* keep_users, int32_t n_user_rows, const uint8_t* keep_items,
+                     int32_t n_item_rows);
+int32_t known_counts(Model* m, int which, int32_t* out_counts, int32_t n_rows);
+// Writes the sorted exclusion SLOTS of `user_row` (padded with INT32_MAX) into ctx->d_excl on `stream`;
+// *n_excl = entries written.  Lists longer than the kernel's shared-memory sort fall back to a host
+// translation of the authoritative list.
+int32_t known_exclusions_device(Model* m, QueryCtx* ctx, int32_t user_row, int32_t* n_excl, cudaStream_t stream);
+int32_t ensure_excl(QueryCtx* c, int32_t n);
 
 // lsh.cu
 int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits);

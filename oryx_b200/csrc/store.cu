@@ -24,7 +24,7 @@ __global__ void scatter_rows_kernel(const float* __restrict__ in, int64_t in_str
                                     int fpad, const int32_t* __restrict__ dst_slot,
                                     const int32_t* __restrict__ rows, const int32_t* __restrict__ parts,
                                     int64_t n, float* __restrict__ vec, int32_t* __restrict__ slot_row,
-                                    int32_t* __restrict__ slot_part) {
+                                    int32_t* __restrict__ slot_part, int32_t* __restrict__ row_slot) {
   int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (w >= n) return;
@@ -36,12 +36,13 @@ __global__ void scatter_rows_kernel(const float* __restrict__ in, int64_t in_str
   if (lane == 0) {
     slot_row[slot] = rows[w];
     slot_part[slot] = parts ? parts[w] : 0;
+    if (row_slot) row_slot[rows[w]] = slot;
   }
 }
 
 __global__ void clear_slots_kernel(const int32_t* __restrict__ slots, int64_t n, int fpad,
                                    float* __restrict__ vec, int32_t* __restrict__ slot_row,
-                                   int32_t* __restrict__ slot_part) {
+                                   int32_t* __restrict__ slot_part, int32_t* __restrict__ row_slot) {
   int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (w >= n) return;
@@ -52,6 +53,8 @@ __global__ void clear_slots_kernel(const int32_t* __restrict__ slots, int64_t n,
   const float qnan = __int_as_float(0x7fc00000);
   for (int j = lane; j < fpad; j += 32) dst[j] = qnan;
   if (lane == 0) {
+    const int32_t row = slot_row[slot];
+    if (row_slot && row >= 0) row_slot[row] = -1;
     slot_row[slot] = -1;
     slot_part[slot] = -1;
   }
@@ -77,6 +80,12 @@ __global__ void block_part_kernel(const int32_t* __restrict__ slot_part, int64_t
 __global__ void fill_i32_kernel(int32_t* p, int64_t n, int32_t v) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
+}
+
+// row_slot[slot_row[i]] = i for every live slot (after compaction)
+__global__ void rebuild_row_slot_kernel(const int32_t* __restrict__ slot_row, int64_t n, int32_t* __restrict__ row_slot) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && slot_row[i] >= 0) row_slot[slot_row[i]] = (int32_t)i;
 }
 
 __global__ void iota_rows_kernel(int32_t* p, int64_t n, int32_t first) {
@@ -206,6 +215,25 @@ int32_t assign_slots(Model* m, Store* s, const int32_t* rows, int64_t n, int32_t
   if ((int64_t)max_row >= (int64_t)s->row2slot.size()) {
     s->row2slot.resize((size_t)max_row + 1 + (size_t)max_row / 4, -1);
   }
+  if (s->track_row_slot && (int64_t)s->row2slot.size() > s->row_slot_cap) {
+    const int64_t cap = (int64_t)s->row2slot.size();
+    int32_t* nrs = nullptr;
+    if (cudaMalloc(&nrs, (size_t)cap * sizeof(int32_t)) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("device allocation of the row->slot map (%lld rows) failed", (long long)cap);
+      return ORYX_E_NOMEM;
+    }
+    cudaStream_t st = m->update_stream;
+    if (s->row_slot_cap > 0)
+      ORYX_CUDA(cudaMemcpyAsync(nrs, s->d_row_slot, (size_t)s->row_slot_cap * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    const int64_t tail = cap - s->row_slot_cap;
+    fill_i32_kernel<<<(unsigned)((tail + 255) / 256), 256, 0, st>>>(nrs + s->row_slot_cap, tail, -1);
+    m->launches++;
+    ORYX_CUDA(cudaStreamSynchronize(st));
+    cudaFree(s->d_row_slot);
+    s->d_row_slot = nrs;
+    s->row_slot_cap = cap;
+  }
   // Count new slots needed first so the device buffers can grow before any kernel runs.
   int64_t fresh = 0;
   for (int64_t k = 0; k < n; k++) {
@@ -250,13 +278,16 @@ int32_t store_init(Model* m, int which, int64_t capacity_hint) {
   s->features = m->cfg.features;
   s->fpad = round_up(m->cfg.features, 4);
   s->hashed = (which == ORYX_Y) && m->num_hashes > 0;
+  s->track_row_slot = which == ORYX_Y;
   if (capacity_hint > 0) ORYX_TRY(grow(m, s, capacity_hint));
   return ORYX_OK;
 }
 
 void store_free(Store* s) {
   cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(s->d_block_part);
+  cudaFree(s->d_row_slot);
   s->d_vec = nullptr; s->d_slot_row = nullptr; s->d_slot_part = nullptr; s->d_block_part = nullptr;
+  s->d_row_slot = nullptr; s->row_slot_cap = 0;
   s->cap_slots = s->n_slots = s->live = 0;
   s->row2slot.clear(); s->free_slots.clear();
 }
@@ -292,7 +323,7 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
     int64_t blocks = (c * 32 + threads - 1) / threads;
     scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
         g.d_vec, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
-        s->d_slot_row, s->d_slot_part);
+        s->d_slot_row, s->d_slot_part, s->d_row_slot);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
     ORYX_CUDA(cudaStreamSynchronize(st));
@@ -332,7 +363,7 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
     int64_t blocks = (c * 32 + threads - 1) / threads;
     scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
         src, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
-        s->d_slot_row, s->d_slot_part);
+        s->d_slot_row, s->d_slot_part, s->d_row_slot);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
     ORYX_CUDA(cudaStreamSynchronize(st));
@@ -366,7 +397,7 @@ int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
   int threads = 256;
   int64_t blocks = ((int64_t)cnt * 32 + threads - 1) / threads;
   clear_slots_kernel<<<(unsigned)blocks, threads, 0, st>>>(g.d_i32, cnt, s->fpad, s->d_vec,
-                                                          s->d_slot_row, s->d_slot_part);
+                                                          s->d_slot_row, s->d_slot_part, s->d_row_slot);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
   if (s->hashed) ORYX_TRY(refresh_block_parts(m, s));
@@ -439,6 +470,11 @@ int32_t store_compact(Model* m, int which) {
     fill_i32_kernel<<<(unsigned)blocks, threads, 0, st>>>(np + live, tail, -1);
     m->launches += 2;
     ORYX_CUDA(cudaMemsetAsync(nv + live * s->fpad, 0, (size_t)tail * s->fpad * sizeof(float), st));
+  }
+  if (s->d_row_slot) {
+    fill_i32_kernel<<<(unsigned)((s->row_slot_cap + 255) / 256), 256, 0, st>>>(s->d_row_slot, s->row_slot_cap, -1);
+    if (live > 0) rebuild_row_slot_kernel<<<(unsigned)((live + 255) / 256), 256, 0, st>>>(nr, live, s->d_row_slot);
+    m->launches += 2;
   }
   ORYX_CUDA(cudaGetLastError());
   ORYX_CUDA(cudaStreamSynchronize(st));

@@ -170,7 +170,26 @@ ALSServingModel::~ALSServingModel() { oryx_model_destroy(h_); }
 
 int ALSServingModel::rowOf(const std::string& item) const {
   auto it = item_row_.find(item);
-  return it == item_row_.end() ? -1 : it->second;
+  return (it == item_row_.end() || !item_has_vec_[(size_t)it->second]) ? -1 : it->second;
+}
+
+int ALSServingModel::itemRowFor(const std::string& item) {
+  auto it = item_row_.find(item);
+  if (it != item_row_.end()) return it->second;
+  const int row = (int)row_item_.size();
+  row_item_.push_back(item);
+  item_has_vec_.push_back(0);
+  item_row_.emplace(item, row);
+  return row;
+}
+
+int ALSServingModel::userRowFor(const std::string& user) {
+  auto it = user_row_.find(user);
+  if (it != user_row_.end()) return it->second;
+  const int row = (int)row_user_.size();
+  row_user_.push_back(user);
+  user_row_.emplace(user, row);
+  return row;
 }
 
 std::unique_ptr<FloatVec> ALSServingModel::getUserVector(const std::string& user) const {
@@ -194,15 +213,29 @@ std::unique_ptr<FloatVec> ALSServingModel::getItemVector(const std::string& item
 
 void ALSServingModel::setUserVector(const std::string& user, const FloatVec& vector) {
   if ((int)vector.size() != features_) throw std::invalid_argument("vector.length != features");  // :154
-  std::lock_guard<std::mutex> lk(mu_);
-  auto it = X_.find(user);
-  if (it == X_.end()) {
-    X_.emplace(user, vector);
-    recent_users_.insert(user);  // FeatureVectors.java:74-77: ID was actually new
-  } else {
-    it->second = vector;
+  setUserVectors(&user, vector.data(), 1);
+}
+
+void ALSServingModel::setUserVectors(const std::string* users, const float* vecs, size_t n) {
+  if (n == 0) return;
+  const size_t f = (size_t)features_;
+  std::vector<int32_t> rows(n);
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (size_t i = 0; i < n; i++) {
+      rows[i] = userRowFor(users[i]);
+      auto it = X_.find(users[i]);
+      if (it == X_.end()) {
+        X_.emplace(users[i], FloatVec(vecs + i * f, vecs + (i + 1) * f));
+        recent_users_.insert(users[i]);  // FeatureVectors.java:74-77: ID was actually new
+      } else {
+        it->second.assign(vecs + i * f, vecs + (i + 1) * f);
+      }
+      if (!expected_users_.empty()) expected_users_.erase(users[i]);
+    }
   }
-  expected_users_.erase(user);
+  // the device copy of X serves oryx_recommend (query vector read from HBM)
+  check_status(oryx_items_upsert(h_, ORYX_X, rows.data(), vecs, (int32_t)n, nullptr));
 }
 
 void ALSServingModel::setItemVector(const std::string& item, const FloatVec& vector) {
@@ -220,12 +253,10 @@ void ALSServingModel::setItemVectors(const std::string* items, const float* vecs
   {
     std::lock_guard<std::mutex> lk(mu_);
     for (size_t i = 0; i < n; i++) {
-      int row = rowOf(items[i]);
-      if (row < 0) {
-        if (!free_rows_.empty()) { row = free_rows_.back(); free_rows_.pop_back(); }
-        else { row = (int)row_item_.size(); row_item_.emplace_back(); }
-        row_item_[row] = items[i];
-        item_row_[items[i]] = row;
+      const int row = itemRowFor(items[i]);
+      if (!item_has_vec_[(size_t)row]) {
+        item_has_vec_[(size_t)row] = 1;
+        n_item_vecs_++;
         recent_items_.insert(items[i]);  // FeatureVectors.java:74-77
       }
       rows[i] = row;
@@ -248,9 +279,80 @@ std::unordered_set<std::string> ALSServingModel::getKnownItems(const std::string
 }
 
 void ALSServingModel::addKnownItems(const std::string& user, const std::vector<std::string>& items) {
+  const int64_t begin[2] = {0, (int64_t)items.size()};
+  addKnownItems(&user, begin, items.data(), 1);
+}
+
+void ALSServingModel::addKnownItems(const std::string* users, const int64_t* begin, const std::string* items,
+                                    size_t nUsers) {
+  if (nUsers == 0) return;
+  std::vector<int32_t> userRows(nUsers), itemRows((size_t)(begin[nUsers] - begin[0]));
+  std::vector<int64_t> rel(nUsers + 1);
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (size_t i = 0; i < nUsers; i++) {
+      userRows[i] = userRowFor(users[i]);
+      rel[i] = begin[i] - begin[0];
+      auto& s = known_items_[users[i]];
+      for (int64_t j = begin[i]; j < begin[i + 1]; j++) {
+        s.insert(items[j]);
+        itemRows[(size_t)(j - begin[0])] = itemRowFor(items[j]);
+      }
+    }
+    rel[nUsers] = begin[nUsers] - begin[0];
+  }
+  static const int32_t none = 0;
+  check_status(oryx_known_items_add(h_, userRows.data(), rel.data(), itemRows.empty() ? &none : itemRows.data(),
+                                    (int32_t)nUsers));
+}
+
+std::unordered_map<std::string, int> ALSServingModel::getUserCounts() const {
+  std::vector<int32_t> counts;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    counts.resize(row_user_.size());
+  }
+  if (!counts.empty()) check_status(oryx_known_counts(h_, ORYX_X, counts.data(), (int32_t)counts.size()));
+  std::unordered_map<std::string, int> out;
   std::lock_guard<std::mutex> lk(mu_);
-  auto& s = known_items_[user];
-  s.insert(items.begin(), items.end());
+  // the reference's map has an entry per user with a known-items set, empty sets included
+  for (size_t r = 0; r < counts.size(); r++)
+    if (counts[r] > 0 || known_items_.count(row_user_[r])) out[row_user_[r]] = counts[r];
+  return out;
+}
+
+std::unordered_map<std::string, int> ALSServingModel::getItemCounts() const {
+  std::vector<int32_t> counts;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    counts.resize(row_item_.size());
+  }
+  if (!counts.empty()) check_status(oryx_known_counts(h_, ORYX_Y, counts.data(), (int32_t)counts.size()));
+  std::unordered_map<std::string, int> out;
+  std::lock_guard<std::mutex> lk(mu_);
+  for (size_t r = 0; r < counts.size(); r++)
+    if (counts[r] > 0) out[row_item_[r]] = counts[r];
+  return out;
+}
+
+std::unique_ptr<std::vector<IDValue>> ALSServingModel::recommend(const std::string& user, int howMany,
+                                                                 bool considerKnownItems) const {
+  int row;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = user_row_.find(user);
+    row = it == user_row_.end() ? -1 : it->second;
+  }
+  if (row < 0) return nullptr;
+  std::vector<int32_t> rows((size_t)howMany);
+  std::vector<double> scores((size_t)howMany);
+  int32_t n = 0, found = 0;
+  check_status(oryx_recommend(h_, row, howMany, considerKnownItems ? 1 : 0, rows.data(), scores.data(), &n, &found));
+  if (!found) return nullptr;
+  auto out = std::make_unique<std::vector<IDValue>>();
+  std::lock_guard<std::mutex> lk(mu_);
+  for (int i = 0; i < n; i++) out->emplace_back(row_item_[(size_t)rows[i]], scores[i]);
+  return out;
 }
 
 std::unique_ptr<std::vector<std::pair<std::string, FloatVec>>> ALSServingModel::getKnownItemVectorsForUser(
@@ -305,7 +407,7 @@ std::vector<IDValue> ALSServingModel::topN(const ScoreFunction& scoreFn, const R
   {
     std::lock_guard<std::mutex> lk(mu_);
     for (int r = 0; r < n_rows; r++) {
-      if (std::isnan(all[r]) || row_item_[r].empty() || excl_set.count(r)) continue;  // absent rows score NaN
+      if (std::isnan(all[r]) || !item_has_vec_[(size_t)r] || excl_set.count(r)) continue;  // absent rows score NaN
       const std::string& id = row_item_[r];
       if (rescorer->isFiltered && rescorer->isFiltered(id)) continue;
       double s = rescorer->rescore ? rescorer->rescore(id, all[r]) : all[r];
@@ -346,12 +448,19 @@ std::shared_ptr<Solver> ALSServingModel::getYTYSolver() {
 
 void ALSServingModel::retainRecentAndUserIDs(const std::vector<std::string>& users) {
   std::unordered_set<std::string> keep(users.begin(), users.end());
-  std::lock_guard<std::mutex> lk(mu_);
-  for (auto it = X_.begin(); it != X_.end();)
-    it = (keep.count(it->first) || recent_users_.count(it->first)) ? std::next(it) : X_.erase(it);
-  recent_users_.clear();
-  expected_users_.clear();
-  for (const auto& u : users) if (!X_.count(u)) expected_users_.insert(u);
+  std::vector<int32_t> drop;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (auto it = X_.begin(); it != X_.end();) {
+      if (keep.count(it->first) || recent_users_.count(it->first)) { ++it; continue; }
+      drop.push_back(user_row_.at(it->first));
+      it = X_.erase(it);
+    }
+    recent_users_.clear();
+    expected_users_.clear();
+    for (const auto& u : users) if (!X_.count(u)) expected_users_.insert(u);
+  }
+  if (!drop.empty()) check_status(oryx_items_remove(h_, ORYX_X, drop.data(), (int32_t)drop.size()));
 }
 
 void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& items) {
@@ -359,17 +468,18 @@ void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& ite
   std::vector<int32_t> drop;
   {
     std::lock_guard<std::mutex> lk(mu_);
-    for (auto it = item_row_.begin(); it != item_row_.end();) {
-      if (keep.count(it->first) || recent_items_.count(it->first)) { ++it; continue; }
-      drop.push_back(it->second);
-      row_item_[it->second].clear();
-      free_rows_.push_back(it->second);
-      item_partition_.erase(it->first);
-      it = item_row_.erase(it);
+    for (size_t r = 0; r < row_item_.size(); r++) {
+      if (!item_has_vec_[r]) continue;
+      const std::string& id = row_item_[r];
+      if (keep.count(id) || recent_items_.count(id)) continue;
+      drop.push_back((int32_t)r);
+      item_has_vec_[r] = 0;
+      n_item_vecs_--;
+      item_partition_.erase(id);
     }
     recent_items_.clear();
     expected_items_.clear();
-    for (const auto& i : items) if (!item_row_.count(i)) expected_items_.insert(i);
+    for (const auto& i : items) if (rowOf(i) < 0) expected_items_.insert(i);
     cached_yty_.reset();
   }
   if (!drop.empty()) check_status(oryx_items_remove(h_, ORYX_Y, drop.data(), (int32_t)drop.size()));
@@ -378,32 +488,45 @@ void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& ite
 void ALSServingModel::retainRecentAndKnownItems(const std::vector<std::string>& users,
                                                 const std::vector<std::string>& items) {
   std::unordered_set<std::string> keepUsers(users.begin(), users.end()), keepItems(items.begin(), items.end());
-  std::lock_guard<std::mutex> lk(mu_);
-  for (auto it = known_items_.begin(); it != known_items_.end();)
-    it = (keepUsers.count(it->first) || recent_users_.count(it->first)) ? std::next(it) : known_items_.erase(it);
-  for (auto& kv : known_items_) {
-    auto& set = kv.second;
-    for (auto it = set.begin(); it != set.end();)
-      it = (keepItems.count(*it) || recent_items_.count(*it)) ? std::next(it) : set.erase(it);
+  std::vector<uint8_t> userMask, itemMask;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (auto it = known_items_.begin(); it != known_items_.end();)
+      it = (keepUsers.count(it->first) || recent_users_.count(it->first)) ? std::next(it) : known_items_.erase(it);
+    for (auto& kv : known_items_) {
+      auto& set = kv.second;
+      for (auto it = set.begin(); it != set.end();)
+        it = (keepItems.count(*it) || recent_items_.count(*it)) ? std::next(it) : set.erase(it);
+    }
+    // the same predicate as row masks for the device copy
+    userMask.resize(row_user_.size());
+    for (size_t r = 0; r < row_user_.size(); r++)
+      userMask[r] = keepUsers.count(row_user_[r]) || recent_users_.count(row_user_[r]);
+    itemMask.resize(row_item_.size());
+    for (size_t r = 0; r < row_item_.size(); r++)
+      itemMask[r] = keepItems.count(row_item_[r]) || recent_items_.count(row_item_[r]);
   }
+  static const uint8_t none = 0;
+  check_status(oryx_known_items_retain(h_, userMask.empty() ? &none : userMask.data(), (int32_t)userMask.size(),
+                                       itemMask.empty() ? &none : itemMask.data(), (int32_t)itemMask.size()));
 }
 
 std::vector<std::string> ALSServingModel::getAllItemIDs() const {
   std::lock_guard<std::mutex> lk(mu_);
   std::vector<std::string> out;
-  out.reserve(item_row_.size());
-  for (const auto& kv : item_row_) out.push_back(kv.first);
+  out.reserve((size_t)n_item_vecs_);
+  for (size_t r = 0; r < row_item_.size(); r++) if (item_has_vec_[r]) out.push_back(row_item_[r]);
   return out;
 }
 
 int ALSServingModel::getNumUsers() const { std::lock_guard<std::mutex> lk(mu_); return (int)X_.size(); }
-int ALSServingModel::getNumItems() const { std::lock_guard<std::mutex> lk(mu_); return (int)item_row_.size(); }
+int ALSServingModel::getNumItems() const { std::lock_guard<std::mutex> lk(mu_); return n_item_vecs_; }
 
 float ALSServingModel::getFractionLoaded() const {
   std::lock_guard<std::mutex> lk(mu_);
   int expected = (int)expected_users_.size() + (int)expected_items_.size();
   if (expected == 0) return 1.0f;
-  float loaded = (float)X_.size() + (float)item_row_.size();
+  float loaded = (float)X_.size() + (float)n_item_vecs_;
   return loaded / (loaded + expected);
 }
 

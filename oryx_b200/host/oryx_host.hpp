@@ -123,12 +123,20 @@ class ALSServingModel {
   std::unique_ptr<FloatVec> getUserVector(const std::string& user) const;           // :138-140
   std::unique_ptr<FloatVec> getItemVector(const std::string& item) const;           // :142-151
   void setUserVector(const std::string& user, const FloatVec& vector);              // :153-159
+  void setUserVectors(const std::string* users, const float* vectorsRowMajor, size_t n);  // bulk form, one C ABI call
   void setItemVector(const std::string& item, const FloatVec& vector);              // :161-183
   // bulk form of setItemVector for model load (one C ABI call)
   void setItemVectors(const std::vector<std::string>& items, const std::vector<float>& vectorsRowMajor);
   void setItemVectors(const std::string* items, const float* vectorsRowMajor, size_t n);
   std::unordered_set<std::string> getKnownItems(const std::string& user) const;     // :189-201
   void addKnownItems(const std::string& user, const std::vector<std::string>& items);  // :241-258
+  // bulk form: user i gains items[begin[i] .. begin[i+1]); one C ABI call for the device copy
+  void addKnownItems(const std::string* users, const int64_t* begin, const std::string* items, size_t nUsers);
+  std::unordered_map<std::string, int> getUserCounts() const;                       // :212-225
+  std::unordered_map<std::string, int> getItemCounts() const;                       // :227-239
+  // Recommend.get without a rescorer (serving/als/Recommend.java:74-114): query vector and known items
+  // are taken from device memory (oryx_recommend).  nullptr when the user is unknown (404).
+  std::unique_ptr<std::vector<IDValue>> recommend(const std::string& user, int howMany, bool considerKnownItems) const;
   std::unique_ptr<std::vector<std::pair<std::string, FloatVec>>> getKnownItemVectorsForUser(const std::string& user) const;  // :264-287
 
   // :289-335.  allowed: IDs the predicate rejects (known items); extraPredicate / rescorer: arbitrary
@@ -150,7 +158,9 @@ class ALSServingModel {
   oryx_model* handle() const { return h_; }
 
  private:
-  int rowOf(const std::string& item) const;
+  int rowOf(const std::string& item) const;             // row of an item that HAS a vector, else -1
+  int itemRowFor(const std::string& item);              // row of any mentioned item id (created on demand)
+  int userRowFor(const std::string& user);
   int features_;
   bool implicit_;
   int device_;
@@ -158,9 +168,14 @@ class ALSServingModel {
   oryx_model* h_ = nullptr;
   mutable std::mutex mu_;
   std::unordered_map<std::string, FloatVec> X_;
+  // Rows are permanent per id (never re-used), so the device-resident known-item lists can refer to
+  // them; item_has_vec_ tells whether the row currently holds a vector.
   std::unordered_map<std::string, int> item_row_;
   std::vector<std::string> row_item_;
-  std::vector<int> free_rows_;
+  std::vector<uint8_t> item_has_vec_;
+  int n_item_vecs_ = 0;
+  std::unordered_map<std::string, int> user_row_;
+  std::vector<std::string> row_user_;
   std::unordered_map<std::string, int> item_partition_;
   std::unordered_map<std::string, std::unordered_set<std::string>> known_items_;
   std::unordered_set<std::string> expected_users_, expected_items_;

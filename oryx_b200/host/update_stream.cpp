@@ -939,12 +939,21 @@ void ALSServingModelManager::applyBatch(const FeatureBatch& b, char forceMatrix)
       model.setItemVectors(b.ids.data() + i, b.vec(i), j - i);  // vectors of a run are contiguous
       i = j;
     } else {
-      model.setUserVector(b.ids[i], FloatVec(b.vec(i), b.vec(i) + F));
-      if (b.hasOthers[i]) {
-        std::vector<std::string> known(b.others.begin() + b.otherBegin[i], b.others.begin() + b.otherBegin[i + 1]);
-        model.addKnownItems(b.ids[i], known);
+      size_t j = i;
+      while (j < n && (forceMatrix ? forceMatrix : b.matrix[j]) == 'X' && b.vecLen(j) == F) j++;
+      model.setUserVectors(b.ids.data() + i, b.vec(i), j - i);
+      // known items of the run in one call (only messages that carry a fourth element, :83-87)
+      std::vector<std::string> users;
+      std::vector<int64_t> begin{0};
+      std::vector<std::string> items;
+      for (size_t k = i; k < j; k++) {
+        if (!b.hasOthers[k]) continue;
+        users.push_back(b.ids[k]);
+        items.insert(items.end(), b.others.begin() + b.otherBegin[k], b.others.begin() + b.otherBegin[k + 1]);
+        begin.push_back((int64_t)items.size());
       }
-      i++;
+      if (!users.empty()) model.addKnownItems(users.data(), begin.data(), items.data(), users.size());
+      i = j;
     }
   }
 }

@@ -70,6 +70,11 @@ SIGNATURES = {
     "oryx_lsh_index_rows": [C.c_void_p, _f32p, C.c_int32, _i32p],
     "oryx_lsh_candidates": [C.c_void_p, _f32p, _i32p, _i32p],
     "oryx_topn": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _i32p, C.c_int32, _i32p, _f64p, _i32p],
+    "oryx_known_items_add": [C.c_void_p, _i32p, _i64p, _i32p, C.c_int32],
+    "oryx_known_items_get": [C.c_void_p, C.c_int32, _i32p, C.c_int32, _i32p],
+    "oryx_known_items_retain": [C.c_void_p, _u8p, C.c_int32, _u8p, C.c_int32],
+    "oryx_known_counts": [C.c_void_p, C.c_int32, _i32p, C.c_int32],
+    "oryx_recommend": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _i32p],
     "oryx_topn_batch": [C.c_void_p, C.c_int32, _f32p, C.c_int32, C.c_int32, _i32p, _i32p, _i32p, _f64p, _i32p],
     "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
     "oryx_scores_rows": [C.c_void_p, C.c_int32, _f32p, _i32p, C.c_int32, _f64p, _u8p],
@@ -222,6 +227,46 @@ class Model:
         _check(lib().oryx_topn(self._h, kind, _ptr(q, C.c_float), how_many, _ptr(ex, C.c_int32),
                                0 if ex is None else ex.size, _ptr(rows, C.c_int32),
                                _ptr(scores, C.c_double), C.byref(n)))
+        return rows[:n.value].copy(), scores[:n.value].copy()
+
+    # ---- known items on the device (ALSServingModel.java:189-258) and /recommend by user row
+    def known_items_add(self, user_rows, item_lists):
+        users = np.ascontiguousarray(user_rows, dtype=np.int32)
+        begin = np.zeros(users.size + 1, dtype=np.int64)
+        if users.size:
+            np.cumsum([len(l) for l in item_lists], out=begin[1:])
+        items = np.ascontiguousarray(np.concatenate([np.asarray(l, dtype=np.int32) for l in item_lists])
+                                     if users.size and begin[-1] else np.zeros(1, np.int32), dtype=np.int32)
+        _check(lib().oryx_known_items_add(self._h, _ptr(users, C.c_int32), _ptr(begin, C.c_int64),
+                                          _ptr(items, C.c_int32), users.size))
+
+    def known_items_get(self, user_row: int) -> np.ndarray:
+        n = C.c_int32()
+        lib().oryx_known_items_get(self._h, user_row, None, 0, C.byref(n))
+        out = np.zeros(max(n.value, 1), dtype=np.int32)
+        _check(lib().oryx_known_items_get(self._h, user_row, _ptr(out, C.c_int32), out.size, C.byref(n)))
+        return out[:n.value].copy()
+
+    def known_items_retain(self, keep_users=None, keep_items=None):
+        ku = None if keep_users is None else np.ascontiguousarray(keep_users, dtype=np.uint8)
+        ki = None if keep_items is None else np.ascontiguousarray(keep_items, dtype=np.uint8)
+        _check(lib().oryx_known_items_retain(self._h, _ptr(ku, C.c_uint8), 0 if ku is None else ku.size,
+                                             _ptr(ki, C.c_uint8), 0 if ki is None else ki.size))
+
+    def known_counts(self, which: int, n_rows: int) -> np.ndarray:
+        out = np.zeros(max(n_rows, 1), dtype=np.int32)
+        _check(lib().oryx_known_counts(self._h, which, _ptr(out, C.c_int32), n_rows))
+        return out[:n_rows]
+
+    def recommend(self, user_row: int, how_many: int, consider_known_items: bool = False):
+        """-> (rows, scores) or None when the user has no vector (the reference's 404)."""
+        rows = np.zeros(max(how_many, 1), dtype=np.int32)
+        scores = np.zeros(max(how_many, 1), dtype=np.float64)
+        n, found = C.c_int32(), C.c_int32()
+        _check(lib().oryx_recommend(self._h, user_row, how_many, int(consider_known_items), _ptr(rows, C.c_int32),
+                                    _ptr(scores, C.c_double), C.byref(n), C.byref(found)))
+        if not found.value:
+            return None
         return rows[:n.value].copy(), scores[:n.value].copy()
 
     def topn_batch(self, kind: int, queries, how_many: int, excluded_lists=None):

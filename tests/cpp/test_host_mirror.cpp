@@ -167,6 +167,27 @@ static void testServingGoldens() {
     CHECK(recs2.size() == 5 && recs2[0].first == "I1");
     CHECK_NEAR(0.51607955f, recs2[0].second, FLOAT_EPSILON);
   }
+  {  // the same /recommend goldens served from device-resident state (oryx_recommend): RecommendTest.java:31-37, 71-84
+    auto r0 = model.recommend("U0", 10, false);
+    CHECK(r0 && r0->size() == 6 && (*r0)[0].first == "I1");
+    if (r0 && !r0->empty()) CHECK_NEAR(0.4653969f, (*r0)[0].second, FLOAT_EPSILON);
+    auto r4 = model.recommend("U4", 10, false);
+    CHECK(r4 && r4->size() == 3 && (*r4)[0].first == "I2");
+    if (r4 && !r4->empty()) CHECK_NEAR(0.14134796f, (*r4)[0].second, FLOAT_EPSILON);
+    auto r4k = model.recommend("U4", 10, true);
+    CHECK(r4k && r4k->size() == 9 && (*r4k)[0].first == "I7");
+    if (r4k && !r4k->empty()) CHECK_NEAR(2.0047457f, (*r4k)[0].second, FLOAT_EPSILON);
+    CHECK(model.recommend("nobody", 10, false) == nullptr);
+    // identical to the path that ships the exclusion list with the call
+    auto viaTopN = recommend(model, "U0");
+    CHECK(r0 && viaTopN.size() == r0->size());
+    for (size_t i = 0; r0 && i < viaTopN.size(); i++) CHECK(viaTopN[i].first == (*r0)[i].first && viaTopN[i].second == (*r0)[i].second);
+    // T/MostActiveUsersTest / MostPopularItemsTest inputs: counts of the known-items matrix (TestALSModelFactory.java:80-96)
+    auto uc = model.getUserCounts();
+    auto ic = model.getItemCounts();
+    CHECK(uc["U0"] == 3 && uc["U1"] == 5 && uc["U4"] == 6 && uc["U5"] == 7);
+    CHECK(ic["I0"] == 2 && ic["I4"] == 4 && ic["I7"] == 6 && ic["I3"] == 2);
+  }
   {  // T/PopularRepresentativeItemsTest.java:30-36
     std::vector<std::string> items;
     FloatVec unit(2, 0.0f);
