@@ -36,6 +36,9 @@ FEATURES = 128
 HOW_MANY = 10
 LSH_CORES = 32          # LocalitySensitiveHash(1.0, features, 32 cores) -> 5 hashes, 5 bits differing
 N_QUERIES = 64          # distinct query vectors cycled through the timed steps
+# multi-GPU tuning knobs (defaults are what the measurements in DESIGN.md section 5 use)
+PIPELINE = os.environ.get("ORYX_BENCH_PIPELINE", "1") != "0"
+RESERVED_SMS = int(os.environ.get("ORYX_BENCH_RESERVED_SMS", "4"))
 SEED_Y, SEED_Q, SEED_H = 0x0B2000001, 0x0B2000003, 0x0B2000004
 METRIC = "als_recommend_top10_queries_per_sec_10M_items_x_128f"
 UNIT = "queries/s"
@@ -229,13 +232,17 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+        # The only collective on the path moves 128 bytes per rank: one NCCL channel (one CTA) is
+        # enough, and it has to fit next to a scan grid that fills the GPU.
+        os.environ.setdefault("NCCL_MAX_NCHANNELS", "1")
+        os.environ.setdefault("NCCL_MIN_NCHANNELS", "1")
         dist.init_process_group("nccl", device_id=dev)
 
     n_items, F = args.items, args.features
     H, bits = ob.lsh_plan(1.0, LSH_CORES)
     hv = np.random.default_rng(SEED_H).standard_normal((H, F), dtype=np.float32)
     model = ob.Model(F, implicit=True, hash_vectors=hv, max_bits_differing=bits, device=local_rank,
-                     capacity_hint=n_items, reserved_sms=1 if world > 1 else 0)
+                     capacity_hint=n_items, reserved_sms=RESERVED_SMS if world > 1 else 0)
 
     # ---- synthetic model, generated on the device shard-locally and bulk-loaded through the C ABI
     want_cpu = (rank == 0 and world == 1 and not args.no_cpu_baseline)
@@ -283,10 +290,15 @@ def run_ours(args):
     def step_device(i: int):
         """One query with inputs resident in HBM, enqueued on torch's current stream."""
         nonlocal launches_extra
-        if world > 1:
+        if world > 1 and PIPELINE:
             # scan on this stream; the one exchange step (a 128-byte record per rank over NCCL / NVLink)
             # and the merge follow on a side stream while the next query's scan already runs
             pipe.submit(ob.DOT, d_q[i % N_QUERIES].data_ptr())
+            launches_extra += 1
+        elif world > 1:
+            model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
+                              d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
+            exchange_merge()
             launches_extra += 1
         else:
             model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
