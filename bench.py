@@ -37,8 +37,9 @@ HOW_MANY = 10
 LSH_CORES = 32          # LocalitySensitiveHash(1.0, features, 32 cores) -> 5 hashes, 5 bits differing
 N_QUERIES = 64          # distinct query vectors cycled through the timed steps
 # multi-GPU tuning knobs (defaults are what the measurements in DESIGN.md section 5 use)
+EXCHANGE = os.environ.get("ORYX_BENCH_EXCHANGE", "p2p")   # "p2p": peer-memory exchange kernel; "nccl": all-gather + merge
 PIPELINE = os.environ.get("ORYX_BENCH_PIPELINE", "1") != "0"
-RESERVED_SMS = int(os.environ.get("ORYX_BENCH_RESERVED_SMS", "4"))
+RESERVED_SMS = int(os.environ.get("ORYX_BENCH_RESERVED_SMS", "1" if EXCHANGE == "p2p" else "4"))
 SEED_Y, SEED_Q, SEED_H = 0x0B2000001, 0x0B2000003, 0x0B2000004
 METRIC = "als_recommend_top10_queries_per_sec_10M_items_x_128f"
 UNIT = "queries/s"
@@ -271,9 +272,12 @@ def run_ours(args):
     d_rows = d_rec[HOW_MANY * 8: HOW_MANY * 12].view(torch.int32)
     d_n = d_rec[HOW_MANY * 12: HOW_MANY * 12 + 4].view(torch.int32)
     if world > 1:
-        from oryx_b200.sharded import PipelinedShardedTopN, ShardPlan, exchange_packed
+        from oryx_b200.sharded import P2PShardedTopN, PipelinedShardedTopN, ShardPlan, exchange_packed
         plan = ShardPlan(world, n_items)   # rank r owns global rows [r*n_items, (r+1)*n_items)
-        pipe = PipelinedShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
+        if EXCHANGE == "p2p":
+            pipe = P2PShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
+        else:
+            pipe = PipelinedShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
         g_rec = torch.zeros(world * rec_bytes, dtype=torch.uint8, device=dev)
         m_rows = torch.zeros(HOW_MANY, dtype=torch.int64, device=dev)
         m_scores = torch.zeros(HOW_MANY, dtype=torch.float64, device=dev)
@@ -290,11 +294,11 @@ def run_ours(args):
     def step_device(i: int):
         """One query with inputs resident in HBM, enqueued on torch's current stream."""
         nonlocal launches_extra
-        if world > 1 and PIPELINE:
+        if world > 1 and (PIPELINE or EXCHANGE == "p2p"):
             # scan on this stream; the one exchange step (a 128-byte record per rank over NCCL / NVLink)
             # and the merge follow on a side stream while the next query's scan already runs
             pipe.submit(ob.DOT, d_q[i % N_QUERIES].data_ptr())
-            launches_extra += 1
+            launches_extra += 0 if EXCHANGE == "p2p" else 1   # the NCCL path's merge kernel is launched from Python
         elif world > 1:
             model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
                               d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
@@ -363,13 +367,32 @@ def run_ours(args):
 
         def step_e2e(i):
             d_qe.copy_(h_q_pinned[i % N_QUERIES], non_blocking=True)
-            model.topn_device(ob.DOT, d_qe.data_ptr(), HOW_MANY, d_rows.data_ptr(), d_scores.data_ptr(),
-                              d_n.data_ptr(), stream.cuda_stream)
-            exchange_merge()
-            h_res_rows.copy_(m_rows, non_blocking=True)
-            h_res_scores.copy_(m_scores, non_blocking=True)
+            if EXCHANGE == "p2p":
+                pipe.submit(ob.DOT, d_qe.data_ptr())
+                h_res_rows.copy_(pipe.m_rows, non_blocking=True)
+                h_res_scores.copy_(pipe.m_scores, non_blocking=True)
+            else:
+                model.topn_device(ob.DOT, d_qe.data_ptr(), HOW_MANY, d_rows.data_ptr(), d_scores.data_ptr(),
+                                  d_n.data_ptr(), stream.cuda_stream)
+                exchange_merge()
+                h_res_rows.copy_(m_rows, non_blocking=True)
+                h_res_scores.copy_(m_scores, non_blocking=True)
             stream.synchronize()
         h2d, d2h = F * 4, HOW_MANY * 16
+
+        # the peer-memory exchange against the NCCL all-gather + merge on the same queries
+        exchange_check = None
+        if EXCHANGE == "p2p":
+            exchange_check = True
+            for i in range(4):
+                pipe.submit(ob.DOT, d_q[i].data_ptr())
+                model.topn_device(ob.DOT, d_q[i].data_ptr(), HOW_MANY, d_rows.data_ptr(), d_scores.data_ptr(),
+                                  d_n.data_ptr(), stream.cuda_stream)
+                exchange_merge()
+                stream.synchronize()
+                k = int(m_n.item())
+                exchange_check = exchange_check and int(pipe.m_n.item()) == k and \
+                    torch.equal(pipe.m_rows[:k], m_rows[:k]) and torch.equal(pipe.m_scores[:k], m_scores[:k])
     for i in range(3):
         step_e2e(i)
     barrier()
@@ -473,7 +496,10 @@ def run_ours(args):
                        "parallelism": f"row-sharded x{world}" if world > 1 else "1 GPU",
                        "l2_policy": f"inputs larger than L2 ({alg_bytes / 1e9:.2f} GB streamed per step vs 126 MB L2)",
                        "item_scores_per_sec": value * ITEMS_PER_GPU, "load_seconds": round(t_load, 2),
-                       "parity_vs_oracle_full_size": parity},
+                       "parity_vs_oracle_full_size": parity,
+                       "exchange": (("peer-memory kernel (oryx_topn_sharded_device)" if EXCHANGE == "p2p"
+                                     else "NCCL all-gather + merge kernel") if world > 1 else None),
+                       "exchange_matches_nccl_path": exchange_check if world > 1 else None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes,

@@ -25,7 +25,7 @@ void ctx_destroy(QueryCtx* c) {
   if (c->stream) cudaStreamDestroy(c->stream);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
-  cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter);
+  cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter); cudaFree(c->d_finish_seq);
   cudaFree(c->d_main_index); cudaFree(c->d_worklist); cudaFree(c->d_out_n);
   cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_n);
 }
@@ -43,6 +43,8 @@ static int32_t ctx_create(Model* m, QueryCtx* c) {
   ORYX_CUDA(cudaMalloc(&c->d_list_max, (size_t)2 * kMaxGrid * sizeof(uint32_t)));
   ORYX_CUDA(cudaMalloc(&c->d_counter, 32 * sizeof(unsigned int)));
   ORYX_CUDA(cudaMemset(c->d_counter, 0, 32 * sizeof(unsigned int)));
+  ORYX_CUDA(cudaMalloc(&c->d_finish_seq, sizeof(unsigned long long)));
+  ORYX_CUDA(cudaMemset(c->d_finish_seq, 0, sizeof(unsigned long long)));
   ORYX_CUDA(cudaMalloc(&c->d_main_index, sizeof(int32_t)));
   ORYX_CUDA(cudaMemset(c->d_main_index, 0, sizeof(int32_t)));
   // one packed result record: [count i32, pad][rows i32 x how_many, padded to 8][scores f64 x how_many]
@@ -84,6 +86,26 @@ void ctx_release(Model* m, QueryCtx* ctx) {
     m->pool_free.push_back(ctx);
   }
   m->pool_cv.notify_one();
+}
+
+int32_t ensure_max_dynamic_smem(const void* kernel, size_t bytes) {
+  struct Entry { int device; const void* kernel; size_t bytes; };
+  static std::mutex mu;
+  static std::vector<Entry> done;
+  int device = 0;
+  ORYX_CUDA(cudaGetDevice(&device));
+  std::lock_guard<std::mutex> lk(mu);
+  for (auto& e : done) {
+    if (e.device == device && e.kernel == kernel) {
+      if (e.bytes >= bytes) return ORYX_OK;
+      ORYX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+      e.bytes = bytes;
+      return ORYX_OK;
+    }
+  }
+  ORYX_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  done.push_back({device, kernel, bytes});
+  return ORYX_OK;
 }
 
 int32_t ensure_excl(QueryCtx* c, int32_t n) {
@@ -146,7 +168,6 @@ static int32_t run_topn_staged(Model* m, QueryCtx* c, int32_t kind, const float*
   std::memcpy(out_rows, h_rec + rows_off, (size_t)n * sizeof(int32_t));
   std::memcpy(out_scores, h_rec + scores_off, (size_t)n * sizeof(double));
   *out_n = n;
-  m->queries++;
   float ms = 0.f;
   if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);
   else cudaGetLastError();
@@ -177,6 +198,37 @@ static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query,
     }
   }
   return run_topn_staged(m, c, kind, c->d_query, n_excl_slots, how_many, out_rows, out_scores, out_n);
+}
+
+int32_t topn_device_impl(Model* m, int kind, const float* d_query, int how_many, int32_t* d_out_rows,
+                         double* d_out_scores, int32_t* d_out_n, cudaStream_t stream,
+                         const unsigned long long* gate, unsigned long long gate_value) {
+  // The asynchronous form uses one dedicated context (scratch + ticket counter): the caller orders
+  // these calls on `stream`, so they never overlap each other.
+  {
+    std::unique_lock<std::mutex> lk(m->pool_mu);
+    if (m->async_ctx == nullptr) {
+      auto c = std::make_unique<QueryCtx>();
+      int32_t rc = ctx_create(m, c.get());
+      if (rc != ORYX_OK) { ctx_destroy(c.get()); return rc; }
+      m->async_ctx = c.get();
+      m->pool_all.push_back(std::move(c));
+    }
+  }
+  QueryCtx* async_ctx = m->async_ctx;
+  TopnRequest rq{};
+  rq.kind = kind;
+  rq.d_query = d_query;
+  rq.how_many = how_many;
+  rq.d_excl = nullptr;
+  rq.n_excl = 0;
+  rq.d_out_rows = d_out_rows;
+  rq.d_out_scores = d_out_scores;
+  rq.d_out_n = d_out_n;
+  rq.gate = gate;
+  rq.gate_value = gate_value;
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  return scan_topn_launch(m, async_ctx, rq, stream);
 }
 
 }  // namespace oryx
@@ -258,6 +310,8 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     store_free(&m->store[0]);
     store_free(&m->store[1]);
     known_free(&m->known);
+    cudaFree(m->staging.d_vec); cudaFree(m->staging.d_i32); cudaFreeHost(m->staging.h_i32);
+    cudaFree(m->staging.d_known_dst); cudaFree(m->staging.d_known_val);
     cudaFree(m->d_hash_vectors);
     for (auto& b : m->batch.buf) cudaFree(b);
     cudaFree(m->d_debug_ts);
@@ -657,30 +711,8 @@ int32_t oryx_topn_device(oryx_model* mh, int32_t kind, const float* d_query, int
   ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
-  // The asynchronous form uses one dedicated context (scratch + ticket counter): the caller orders
-  // these calls on `stream`, so they never overlap each other.
-  {
-    std::unique_lock<std::mutex> lk(m->pool_mu);
-    if (m->async_ctx == nullptr) {
-      auto c = std::make_unique<QueryCtx>();
-      int32_t rc = ctx_create(m, c.get());
-      if (rc != ORYX_OK) { ctx_destroy(c.get()); return rc; }
-      m->async_ctx = c.get();
-      m->pool_all.push_back(std::move(c));
-    }
-  }
-  QueryCtx* async_ctx = m->async_ctx;
-  TopnRequest rq{};
-  rq.kind = kind;
-  rq.d_query = d_query;
-  rq.how_many = how_many;
-  rq.d_excl = nullptr;
-  rq.n_excl = 0;
-  rq.d_out_rows = d_out_rows;
-  rq.d_out_scores = d_out_scores;
-  rq.d_out_n = d_out_n;
-  std::shared_lock<std::shared_mutex> lk(m->mu);
-  return scan_topn_launch(m, async_ctx, rq, reinterpret_cast<cudaStream_t>(stream));
+  return topn_device_impl(m, kind, d_query, how_many, d_out_rows, d_out_scores, d_out_n,
+                          reinterpret_cast<cudaStream_t>(stream), nullptr, 0);
 }
 
 int32_t oryx_merge_topn_device(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int32_t n_lists,

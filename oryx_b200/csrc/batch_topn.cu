@@ -624,11 +624,7 @@ int32_t launch_score(const CUtensorMap& tq, const CUtensorMap& ty, int n_qtiles,
                      float* bmax, int64_t bmax_stride, int num_sms, cudaStream_t st) {
   constexpr int YB = (NCH <= 2) ? 2 : 1;
   const size_t smem = ScoreSmem::bytes(NCH, YB);
-  static bool configured = false;
-  if (!configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(batch_score_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_score_kernel<NCH>), smem));
   const int grid = std::min(num_sms, n_ytiles);
   batch_score_kernel<NCH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride);
   ORYX_CUDA(cudaGetLastError());
@@ -745,11 +741,7 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   ORYX_CUDA(cudaEventRecord(ev[3], st));
 
   const size_t rsmem = (((size_t)fpad * 4 + 15) & ~(size_t)15) + (size_t)k * 20 + 16;
-  static bool refine_configured = false;
-  if (!refine_configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(batch_refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    refine_configured = true;
-  }
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_refine_kernel), 64 * 1024));
   batch_refine_kernel<<<nq, kRefineThreads, rsmem, st>>>(
       s->d_vec, s->d_slot_row, n, fpad, F, (const float*)d_q.p, kind, k, how_many, (const int32_t*)d_cand.p,
       cand_cap, (const int32_t*)d_candn.p, excl_offsets ? (const int32_t*)d_eo.p : nullptr,

@@ -117,6 +117,14 @@ struct Store {
 // user has interacted with.  The host keeps the authoritative sorted lists (set semantics of
 // addKnownItems); a mirror of every list lives in one device pool so that a /recommend query takes
 // its exclusion list from HBM instead of receiving it from the caller.
+// Grow-only staging of the (single) updater thread of a model.
+struct UpdateStaging {
+  float* d_vec = nullptr; size_t vec_bytes = 0;
+  int32_t* d_i32 = nullptr; size_t i32_count = 0;  // [3 x chunk]: dst, rows, parts
+  int32_t* h_i32 = nullptr; size_t h_count = 0;    // pinned
+  int64_t* d_known_dst = nullptr; int32_t* d_known_val = nullptr; size_t known_cap = 0;
+};
+
 struct KnownItems {
   std::vector<std::vector<int32_t>> lists;  // [user row] sorted unique item rows
   std::vector<int64_t> seg_off;             // [user row] start of the user's segment in the pool
@@ -141,6 +149,10 @@ struct QueryCtx {
   unsigned int* d_counter = nullptr;  // [scratch_sets x 16] dynamic tile counters (64 B apart)
   int scratch_sets = 1;
   int flip = 0;
+  // Finishing kernels of one context complete in order: kernel number n releases its dependents
+  // (the scan of query n+1, which reuses the scratch set of query n-1) only after number n-1 is done.
+  unsigned long long* d_finish_seq = nullptr;
+  unsigned long long finish_seq = 0;
   int32_t* d_main_index = nullptr;
   // LSH-filtered scans: the candidate (or mixed) 256-slot blocks of the current query, built on the
   // device right after the query is hashed; [0] = count, [1..] = block ids.  Null in a context that
@@ -182,6 +194,7 @@ struct Model {
   std::vector<float> h_hash_vectors;
   Store store[2];
   KnownItems known;
+  UpdateStaging staging;
 
   std::shared_mutex mu;  // queries shared, mutations exclusive
   cudaStream_t update_stream = nullptr;
@@ -248,6 +261,9 @@ struct TopnRequest {
   int32_t* d_out_rows;
   double* d_out_scores;
   int32_t* d_out_n;
+  // optional: the finishing kernel holds its output writes until *gate >= gate_value (exchange.cu)
+  const unsigned long long* gate = nullptr;
+  unsigned long long gate_value = 0;
 };
 int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStream_t stream);
 int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_rows, double* d_out,
@@ -272,6 +288,15 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
 
 // gram.cu
 int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);
+
+// cudaFuncSetAttribute is per device: raises the kernel's dynamic shared-memory limit on the CURRENT
+// device if it has not been raised that far yet (api.cu).
+int32_t ensure_max_dynamic_smem(const void* kernel, size_t bytes);
+
+// oryx_topn_device with an optional output gate (see TopnRequest); api.cu
+int32_t topn_device_impl(Model* m, int kind, const float* d_query, int how_many, int32_t* d_out_rows,
+                         double* d_out_scores, int32_t* d_out_n, cudaStream_t stream,
+                         const unsigned long long* gate, unsigned long long gate_value);
 
 // pool
 int32_t ctx_acquire(Model* m, QueryCtx** out);

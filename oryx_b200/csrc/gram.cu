@@ -193,11 +193,7 @@ int32_t gram_fast_launch(Model* m, Store* s, double* d_out, cudaStream_t stream)
   rows_per_chunk = (rows_per_chunk + kFlushRows - 1) / kFlushRows * kFlushRows;
   chunks = (s->n_slots + rows_per_chunk - 1) / rows_per_chunk;
   const size_t smem = (size_t)kFastTile * kFastTile * 8 + (size_t)4 * kFastKC * kFastTile * 4;
-  static bool configured = false;
-  if (!configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(gram_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
-  }
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(gram_fast_kernel), smem));
   dim3 grid((unsigned)n_blocks, (unsigned)chunks);
   gram_fast_kernel<<<grid, 256, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
   m->launches++;

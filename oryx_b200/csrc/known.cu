@@ -76,22 +76,15 @@ __global__ void known_item_counts_kernel(const int32_t* __restrict__ pool, const
   }
 }
 
-struct KnownStaging {
-  int64_t* d_dst = nullptr;
-  int32_t* d_val = nullptr;
-  size_t cap = 0;
-};
-thread_local KnownStaging g_known_staging;  // the single updater thread
-
-int32_t staging_reserve(size_t n) {
-  KnownStaging& g = g_known_staging;
-  if (n <= g.cap) return ORYX_OK;
-  cudaFree(g.d_dst); cudaFree(g.d_val);
-  g.d_dst = nullptr; g.d_val = nullptr; g.cap = 0;
+int32_t staging_reserve(Model* m, size_t n) {
+  UpdateStaging& g = m->staging;
+  if (n <= g.known_cap) return ORYX_OK;
+  cudaFree(g.d_known_dst); cudaFree(g.d_known_val);
+  g.d_known_dst = nullptr; g.d_known_val = nullptr; g.known_cap = 0;
   size_t cap = std::max<size_t>(n, 1024);
-  ORYX_CUDA(cudaMalloc(&g.d_dst, cap * sizeof(int64_t)));
-  ORYX_CUDA(cudaMalloc(&g.d_val, cap * sizeof(int32_t)));
-  g.cap = cap;
+  ORYX_CUDA(cudaMalloc(&g.d_known_dst, cap * sizeof(int64_t)));
+  ORYX_CUDA(cudaMalloc(&g.d_known_val, cap * sizeof(int32_t)));
+  g.known_cap = cap;
   return ORYX_OK;
 }
 
@@ -123,13 +116,13 @@ int32_t segment_capacity(size_t size) {
 
 int32_t upload(Model* m, KnownItems* k, const std::vector<int64_t>& dst, const std::vector<int32_t>& val) {
   if (dst.empty()) return ORYX_OK;
-  ORYX_TRY(staging_reserve(dst.size()));
-  KnownStaging& g = g_known_staging;
+  ORYX_TRY(staging_reserve(m, dst.size()));
+  UpdateStaging& g = m->staging;
   cudaStream_t st = m->update_stream;
-  ORYX_CUDA(cudaMemcpyAsync(g.d_dst, dst.data(), dst.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-  ORYX_CUDA(cudaMemcpyAsync(g.d_val, val.data(), val.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  ORYX_CUDA(cudaMemcpyAsync(g.d_known_dst, dst.data(), dst.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  ORYX_CUDA(cudaMemcpyAsync(g.d_known_val, val.data(), val.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   const int threads = 256;
-  known_scatter_kernel<<<(unsigned)((dst.size() + threads - 1) / threads), threads, 0, st>>>(k->d_pool, g.d_dst, g.d_val,
+  known_scatter_kernel<<<(unsigned)((dst.size() + threads - 1) / threads), threads, 0, st>>>(k->d_pool, g.d_known_dst, g.d_known_val,
                                                                                            (int64_t)dst.size());
   m->launches++;
   ORYX_CUDA(cudaGetLastError());

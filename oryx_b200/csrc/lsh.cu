@@ -181,11 +181,7 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
     return ORYX_E_UNSUPPORTED;
   }
   size_t smem = hv_bytes + (size_t)tile_rows * (F + 1) * sizeof(float);
-  static thread_local size_t configured = 0;
-  if (smem > configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(lsh_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(lsh_hash_kernel), smem));
   int64_t tiles = (n + tile_rows - 1) / tile_rows;
   int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
   lsh_hash_kernel<<<grid, tile_rows, smem, stream>>>(d_rows, n, stride, F, m->d_hash_vectors,

@@ -119,11 +119,7 @@ int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_ro
     set_error("features=%d too large for the exact scoring kernel", s->features);
     return ORYX_E_UNSUPPORTED;
   }
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    ORYX_CUDA(cudaFuncSetAttribute(scores_all_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024) ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(scores_all_kernel), smem));
   int64_t tiles = (s->n_slots + tile - 1) / tile;
   int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
   scores_all_kernel<<<grid, tile, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, s->features,

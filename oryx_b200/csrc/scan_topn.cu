@@ -70,6 +70,14 @@ struct ScanParams {
   double* out_scores;
   int32_t* out_n;
   unsigned long long* debug_ts;  // optional [8] timestamps (ns): see oryx_debug_scan_timestamps
+  // Optional gate: the finishing kernel does not overwrite the output record before *gate >= gate_value
+  // (the sharded path's exchange kernel may still have to read the record of an earlier query).
+  const unsigned long long* gate;
+  unsigned long long gate_value;
+  // Optional in-order token of the context's finishing kernels: this is kernel number order_value;
+  // it releases its dependents only once *order >= order_value - 1 and stores order_value at its end.
+  unsigned long long* order;
+  unsigned long long order_value;
 };
 
 // Programmatic dependent launch: let the next kernel in the stream start / wait for the previous one.
@@ -578,7 +586,19 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
   uint32_t* s_max = reinterpret_cast<uint32_t*>(smem_raw + L.lmax);
 
   // The next query's scan does not depend on this kernel (it uses the other scratch set): let it
-  // start now.  This kernel itself was launched ahead of time and must wait for its own scan.
+  // start now -- but not before the PREVIOUS finishing kernel is done with that other set (a tiny
+  // scan can complete, and release this kernel, while its predecessor is still selecting).  This
+  // kernel itself was launched ahead of time and must wait for its own scan.
+  if (p.order) {
+    if (tid == 0) {
+      const unsigned long long t0 = global_ns();
+      unsigned long long v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p.order) : "memory");
+      } while (v + 1 < p.order_value && global_ns() - t0 < 20000000000ull);
+    }
+    __syncthreads();
+  }
   pdl_launch_dependents();
   for (int j = tid; j < fpad; j += T) s_q[j] = __ldg(p.q + j);
   pdl_wait_primary();
@@ -630,6 +650,16 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
   // made deterministic.  A NaN exact score (possible only if fp32 and fp64 disagree about a zero
   // norm) ranks last.
   const int n_out = min(nsel, p.how_many);
+  if (p.gate) {
+    if (tid == 0) {
+      const unsigned long long t0 = global_ns();
+      unsigned long long v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p.gate) : "memory");
+      } while (v < p.gate_value && global_ns() - t0 < 20000000000ull);
+    }
+    __syncthreads();
+  }
   for (int i = tid; i < nsel; i += T) {
     const double si = sel_exact[i];
     const int32_t ri = sel_row[i];
@@ -650,10 +680,15 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
       p.out_scores[rank] = si;
     }
   }
+  __syncthreads();
   if (tid == 0) {
     *p.out_n = n_out;
     *p.counter = 0u;  // the dynamic tile counter starts at zero for the next query on this context
     if (p.debug_ts) p.debug_ts[6] = global_ns();
+    if (p.order) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p.order), "l"(p.order_value) : "memory");
+    }
   }
 }
 
@@ -661,18 +696,22 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
 
 // cudaOccupancyMaxActiveBlocksPerMultiprocessor costs microseconds; remember it per (kernel, smem).
 int occupancy_cached(const void* kern, int threads, size_t smem, size_t max_dynamic_smem) {
+  struct Entry { int device; const void* kern; size_t smem; int per_sm; };
   static std::mutex mu;
-  static std::vector<std::pair<std::pair<const void*, size_t>, int>> cache;
+  static std::vector<Entry> cache;
+  int device = 0;
+  if (cudaGetDevice(&device) != cudaSuccess) { cudaGetLastError(); device = -1; }
   std::lock_guard<std::mutex> lk(mu);
-  for (auto& e : cache) if (e.first.first == kern && e.first.second == smem) return e.second;
+  for (auto& e : cache) if (e.device == device && e.kern == kern && e.smem == smem) return e.per_sm;
   int per_sm = 0;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_dynamic_smem) != cudaSuccess ||
+  // function attributes are per device: raise the limit on this one before asking about occupancy
+  if (ensure_max_dynamic_smem(kern, max_dynamic_smem) != ORYX_OK ||
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem) != cudaSuccess) {
     cudaGetLastError();
     per_sm = 1;
   }
   if (per_sm < 1) per_sm = 1;
-  cache.push_back({{kern, smem}, per_sm});
+  cache.push_back({device, kern, smem, per_sm});
   return per_sm;
 }
 
@@ -721,12 +760,7 @@ int32_t launch_finish(const ScanParams& p, int n_lists, int kind, cudaStream_t s
   const int fpad = p.f4 * 4;
   const int rescore_warps = std::max(1, std::min(kFinishThreads / 32, kRowStageFloats / fpad));
   const FinishLayout L = finish_layout(p.k, fpad, rescore_warps, n_lists);
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(topn_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-  });
-  ORYX_CUDA(attr_err);
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(topn_finish_kernel), 224 * 1024));
   if (L.total > 224 * 1024) {
     set_error("finishing kernel needs %zu bytes of shared memory (features=%d, how_many=%d)", L.total, p.features,
               p.how_many);
@@ -801,6 +835,10 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   p.out_scores = rq.d_out_scores;
   p.out_n = rq.d_out_n;
   p.debug_ts = m->d_debug_ts;
+  p.gate = rq.gate;
+  p.gate_value = rq.gate_value;
+  p.order = (ctx->scratch_sets == 2 && ctx->d_finish_seq) ? ctx->d_finish_seq : nullptr;
+  p.order_value = p.order ? ++ctx->finish_seq : 0;
   int grid = 0;
   int32_t rc;
   const int f4 = p.f4;

@@ -166,16 +166,11 @@ int32_t refresh_block_parts(Model* m, Store* s) {
   return ORYX_OK;
 }
 
-// Grow-only staging used by the (single) updater thread.
-struct Staging {
-  float* d_vec = nullptr; size_t vec_bytes = 0;
-  int32_t* d_i32 = nullptr; size_t i32_count = 0;  // [3 x chunk]: dst, rows, parts
-  int32_t* h_i32 = nullptr; size_t h_count = 0;    // pinned
-};
-thread_local Staging g_staging;  // one updater thread per store by contract
+// Grow-only staging used by the (single) updater thread of the model.
+using Staging = UpdateStaging;
 
-int32_t staging_reserve(int64_t rows, int features, bool need_vec) {
-  Staging& g = g_staging;
+int32_t staging_reserve(Model* m, int64_t rows, int features, bool need_vec) {
+  Staging& g = m->staging;
   size_t vb = need_vec ? (size_t)rows * features * sizeof(float) : 0;
   if (vb > g.vec_bytes) {
     cudaFree(g.d_vec);
@@ -300,8 +295,8 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
   const int F = s->features;
   for (int64_t off = 0; off < n; off += kChunkRows) {
     int64_t c = std::min<int64_t>(kChunkRows, n - off);
-    ORYX_TRY(staging_reserve(c, F, true));
-    Staging& g = g_staging;
+    ORYX_TRY(staging_reserve(m, c, F, true));
+    Staging& g = m->staging;
     int32_t* h_dst = g.h_i32;
     int32_t* h_rows = g.h_i32 + c;
     int32_t* h_parts = g.h_i32 + 2 * c;
@@ -347,8 +342,8 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
   const int64_t chunk = 1 << 20;
   for (int64_t off = 0; off < n; off += chunk) {
     int64_t c = std::min<int64_t>(chunk, n - off);
-    ORYX_TRY(staging_reserve(c, F, false));
-    Staging& g = g_staging;
+    ORYX_TRY(staging_reserve(m, c, F, false));
+    Staging& g = m->staging;
     int32_t* h_dst = g.h_i32;
     int32_t* d_dst = g.d_i32;
     int32_t* d_rows = g.d_i32 + c;
@@ -379,8 +374,8 @@ int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
   Store* s = &m->store[which];
   s->version++;
   cudaStream_t st = m->update_stream;
-  ORYX_TRY(staging_reserve(std::max(n, 1), s->features, false));
-  Staging& g = g_staging;
+  ORYX_TRY(staging_reserve(m, std::max(n, 1), s->features, false));
+  Staging& g = m->staging;
   int32_t cnt = 0;
   for (int32_t k = 0; k < n; k++) {
     int32_t r = rows[k];

@@ -82,6 +82,13 @@ SIGNATURES = {
     "oryx_topn_device_static": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_packed": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_exchange_create": [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)],
+    "oryx_exchange_handle": [C.c_void_p, C.c_char_p],
+    "oryx_exchange_connect": [C.c_void_p, C.c_char_p],
+    "oryx_exchange_connect_local": [C.POINTER(C.c_void_p), C.c_int32],
+    "oryx_exchange_destroy": [C.c_void_p],
+    "oryx_topn_sharded_device": [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
@@ -323,6 +330,47 @@ class Model:
         _check(lib().oryx_stats_get(self._h, C.byref(s)))
         return {"rows": list(s.rows), "slots": list(s.slots), "device_bytes": s.device_bytes,
                 "queries": s.queries, "kernel_launches": s.kernel_launches, "last_query_ms": s.last_query_ms}
+
+
+class Exchange:
+    """One rank's end of the peer-memory exchange of a row-sharded model (oryx_exchange_*)."""
+
+    HANDLE_BYTES = 64
+
+    def __init__(self, device: int, world: int, rank: int, max_how_many: int):
+        self._h = C.c_void_p()
+        self.world, self.rank = world, rank
+        _check(lib().oryx_exchange_create(device, world, rank, max_how_many, C.byref(self._h)))
+
+    def handle(self) -> bytes:
+        buf = C.create_string_buffer(self.HANDLE_BYTES)
+        _check(lib().oryx_exchange_handle(self._h, buf))
+        return buf.raw
+
+    def connect(self, handles):
+        """handles: list of `world` 64-byte handles in rank order (from the other processes)."""
+        _check(lib().oryx_exchange_connect(self._h, b"".join(handles)))
+
+    @staticmethod
+    def connect_local(exchanges):
+        arr = (C.c_void_p * len(exchanges))(*[x._h for x in exchanges])
+        _check(lib().oryx_exchange_connect_local(arr, len(exchanges)))
+
+    def topn(self, model: "Model", kind: int, d_query: int, how_many: int, row_stride: int, d_rows: int,
+             d_scores: int, d_n: int, stream: int):
+        _check(lib().oryx_topn_sharded_device(model._h, self._h, kind, d_query, how_many, row_stride, d_rows,
+                                              d_scores, d_n, stream))
+
+    def close(self):
+        if self._h:
+            lib().oryx_exchange_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def merge_topn_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, how_many: int, row_stride: int,

@@ -151,6 +151,38 @@ class PipelinedShardedTopN:
         return self.m_rows[b], self.m_scores[b], self.m_n[b]
 
 
+class P2PShardedTopN:
+    """Sharded queries whose exchange step is the library's peer-memory kernel (oryx_topn_sharded_device):
+    the finishing kernel's record is stored straight into every peer's inbox over NVLink and merged
+    there -- no NCCL call on the query path.  ``dist`` is used once, to hand the 64-byte inbox handles
+    to the other processes."""
+
+    def __init__(self, ob, model, dist, torch, plan: ShardPlan, how_many: int, device):
+        self.ob, self.model, self.torch, self.plan, self.hm = ob, model, torch, plan, how_many
+        index = device.index if hasattr(device, "index") else int(device)
+        self.x = ob.Exchange(index, plan.world, dist.get_rank(), how_many)
+        handles = [None] * plan.world
+        dist.all_gather_object(handles, self.x.handle())
+        self.x.connect(handles)
+        dist.barrier()  # nobody publishes before every inbox is mapped
+        z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
+        self.m_rows, self.m_scores, self.m_n = z(how_many, torch.int64), z(how_many, torch.float64), z(1, torch.int32)
+
+    def submit(self, kind: int, d_query_ptr: int, stream=None):
+        st = self.torch.cuda.current_stream() if stream is None else stream
+        self.x.topn(self.model, kind, d_query_ptr, self.hm, self.plan.rows_per_rank, self.m_rows.data_ptr(),
+                    self.m_scores.data_ptr(), self.m_n.data_ptr(), st.cuda_stream)
+
+    def drain(self):
+        pass  # everything is ordered on the submitting stream
+
+    def merged(self, i: int = 0):
+        return self.m_rows, self.m_scores, self.m_n
+
+    def close(self):
+        self.x.close()
+
+
 def allreduce_gram(dist, torch, gram_partial):
     """YtY = sum of per-shard Grams (ALSServingModel.java:362-368), fp64, in place."""
     dist.all_reduce(gram_partial, op=dist.ReduceOp.SUM)
