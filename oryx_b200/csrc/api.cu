@@ -616,13 +616,15 @@ int32_t oryx_topn_batch(oryx_model* mh, int32_t kind, const float* queries, int3
 }
 
 // Development aid (not in the public header): phase timings (ms) and flops of the last tensor-core batch.
-int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {
+int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {  // out5 holds 7 doubles
   Model* m = reinterpret_cast<Model*>(mh);
   out5[0] = m->last_batch.convert_ms;
   out5[1] = m->last_batch.score_ms;
   out5[2] = m->last_batch.threshold_ms;
   out5[3] = m->last_batch.refine_ms;
   out5[4] = m->last_batch.flops;
+  out5[5] = m->last_batch.cand_mean;
+  out5[6] = m->last_batch.cand_max;
   return ORYX_OK;
 }
 

@@ -180,7 +180,8 @@ struct ScoreSmem {
 template <int NCH>
 __global__ void __launch_bounds__(kScoreThreads, 1)
 batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_y,
-                   int n_qtiles, int n_ytiles, int64_t n_slots, float* __restrict__ bmax, int64_t bmax_stride) {
+                   int n_qtiles, int n_ytiles, int64_t n_slots, float* __restrict__ bmax, int64_t bmax_stride,
+                   float* __restrict__ tmax, int64_t tmax_stride) {
   constexpr int YB = (NCH <= 2) ? 2 : 1;  // double-buffer the resident Y tile when it fits
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -312,6 +313,9 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         float4* dst = reinterpret_cast<float4*>(bmax + q * bmax_stride + (int64_t)t * SUBS_PER_TILE);
         dst[0] = make_float4(mx[0], mx[1], mx[2], mx[3]);
         dst[1] = make_float4(mx[4], mx[5], mx[6], mx[7]);
+        // coarse level: the maximum of the whole 256-item tile (the threshold step reads this one)
+        tmax[q * tmax_stride + t] = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])),
+                                          fmaxf(fmaxf(mx[4], mx[5]), fmaxf(mx[6], mx[7])));
       }
     }
   }
@@ -327,29 +331,44 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 constexpr int kThrThreads = 256;
 constexpr int kTopPerThread = 4;     // 256 x 4 = 1024 >= largest k
 constexpr int kCollectCap = 4096;    // sub-blocks above the first cut, staged in shared memory
+constexpr int kTileCap = 2048;       // tiles above the first cut
 
 // One CTA per query.  cand[q][0..cand_cap) receives candidate sub-block ids, cand_n[q] their number
-// (or -1 when more than cand_cap sub-blocks qualified: the host re-runs that query unbatched).
+// (or -1 when too many qualified: the host re-runs that query unbatched).
+//
+// Two levels keep this step off the 4-bytes-per-sub-block array: the per-TILE maxima (256 items,
+// 1/8 of the data) decide which tiles can matter, and only those tiles' 8 sub-block maxima are read.
+//   Tc  = k-th largest tile maximum: at least k tiles, hence k items, have a bf16 score >= Tc, so the
+//         k-th best exact score is >= Tc - delta and every top-k item has a bf16 score >= Tc - 2 delta;
+//         it lives in a tile (and a sub-block) whose maximum is >= Tc - 2 delta.
+//   T'  = k-th largest SUB-BLOCK maximum (>= Tc); same argument, tighter: candidates are the sub-blocks
+//         with maximum >= T' - 2 delta.  Every sub-block >= T' - 2 delta sits in a tile >= Tc - 2 delta.
 __global__ void __launch_bounds__(kThrThreads)
-batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, int n_sub, int k,
-                       const float* __restrict__ qnorm, const unsigned int* __restrict__ max_norm_sq_bits,
-                       int32_t* __restrict__ cand, int cand_cap, int32_t* __restrict__ cand_n) {
+batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, const float* __restrict__ tmax,
+                       int64_t tmax_stride, int n_tiles, int k, const float* __restrict__ qnorm,
+                       const unsigned int* __restrict__ max_norm_sq_bits, int32_t* __restrict__ cand, int cand_cap,
+                       int32_t* __restrict__ cand_n, float* __restrict__ cut_out) {
   __shared__ float s_top[kThrThreads * kTopPerThread];
   __shared__ float s_val[kCollectCap];
   __shared__ int32_t s_id[kCollectCap];
-  __shared__ unsigned int s_count, s_out;
+  __shared__ int32_t s_tile[kTileCap];
+  __shared__ unsigned int s_count, s_out, s_ntile;
   __shared__ float s_lb, s_t;
   const int q = blockIdx.x, tid = threadIdx.x;
+  const float* trow = tmax + (int64_t)q * tmax_stride;
   const float* row = bmax + (int64_t)q * bmax_stride;
   // rigorous bound on |bf16 score - exact score| for this query (see file header)
   const float delta = 0.0078125f * 1.01f * qnorm[q] * sqrtf(__uint_as_float(*max_norm_sq_bits));
 
-  // pass A: every thread keeps the 4 largest values of its strided share
+  // pass A (tiles): every thread keeps the 4 largest values of its strided share
   float top[kTopPerThread];
 #pragma unroll
   for (int j = 0; j < kTopPerThread; j++) top[j] = -INFINITY;
-  for (int i = tid; i < n_sub; i += kThrThreads) {
-    float v = row[i];
+  // 128-bit loads, four of them in flight per thread (a dependent load per element would leave the
+  // pass latency-bound)
+  const float4* trow4 = reinterpret_cast<const float4*>(trow);
+  const int n4 = (n_tiles + 3) >> 2;
+  auto offer = [&](float v) {
     if (v > top[kTopPerThread - 1]) {
       top[kTopPerThread - 1] = v;
 #pragma unroll
@@ -357,35 +376,86 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, int 
         if (top[j] > top[j - 1]) { float t = top[j]; top[j] = top[j - 1]; top[j - 1] = t; }
       }
     }
+  };
+  for (int i0 = tid; i0 < n4; i0 += 4 * kThrThreads) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = i0 + u * kThrThreads;
+      v[u] = i < n4 ? __ldg(trow4 + i) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int base = (i0 + u * kThrThreads) * 4;
+      if (base + 0 < n_tiles) offer(v[u].x);
+      if (base + 1 < n_tiles) offer(v[u].y);
+      if (base + 2 < n_tiles) offer(v[u].z);
+      if (base + 3 < n_tiles) offer(v[u].w);
+    }
   }
 #pragma unroll
   for (int j = 0; j < kTopPerThread; j++) s_top[tid * kTopPerThread + j] = top[j];
-  if (tid == 0) { s_count = 0u; s_out = 0u; }
+  if (tid == 0) { s_count = 0u; s_out = 0u; s_ntile = 0u; s_lb = -INFINITY; }
   __syncthreads();
-  // lower bound of the k-th largest value: the k-th largest of these 1024 (rank count; ties by index)
+  // lower bound of Tc: the k-th largest of these 1024 values -- bitonic sort, descending (a rank
+  // count over 1024 x 1024 pairs per query cost more than everything else in this kernel)
   {
-    const int m = kThrThreads * kTopPerThread;
-    const int kk = min(k, m);
-    for (int e = tid; e < m; e += kThrThreads) {
-      const float v = s_top[e];
-      int rank = 0;
-      for (int j = 0; j < m; j++) {
-        const float u = s_top[j];
-        rank += (u > v || (u == v && j < e)) ? 1 : 0;
+    constexpr int m = kThrThreads * kTopPerThread;
+    for (int kk2 = 2; kk2 <= m; kk2 <<= 1) {
+      for (int j = kk2 >> 1; j > 0; j >>= 1) {
+        for (int i = tid; i < m; i += kThrThreads) {
+          const int ixj = i ^ j;
+          if (ixj > i) {
+            const float a = s_top[i], b = s_top[ixj];
+            const bool desc = (i & kk2) == 0;
+            if ((a < b) == desc) { s_top[i] = b; s_top[ixj] = a; }
+          }
+        }
+        __syncthreads();
       }
-      if (rank == kk - 1) s_lb = v;
+    }
+    if (tid == 0) s_lb = s_top[min(k, m) - 1];
+  }
+  __syncthreads();
+  const float lb = s_lb;  // -inf when fewer than k finite tile maxima exist: then everything is collected
+  const float cut1 = lb - 2.0f * delta;
+
+  // pass B (tiles): the tiles at or above the first cut ...
+  auto collect = [&](float v, int i) {
+    if (i < n_tiles && v >= cut1 && v > -INFINITY) {
+      unsigned pos = atomicAdd(&s_ntile, 1u);
+      if (pos < (unsigned)kTileCap) s_tile[pos] = i;
+    }
+  };
+  for (int i0 = tid; i0 < n4; i0 += 4 * kThrThreads) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = i0 + u * kThrThreads;
+      v[u] = i < n4 ? __ldg(trow4 + i) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int base = (i0 + u * kThrThreads) * 4;
+      collect(v[u].x, base + 0);
+      collect(v[u].y, base + 1);
+      collect(v[u].z, base + 2);
+      collect(v[u].w, base + 3);
     }
   }
   __syncthreads();
-  const float lb = s_lb;  // -inf when fewer than k finite values exist: then everything is collected
-  const float cut1 = lb - 2.0f * delta;
-
-  // pass B: collect every sub-block at or above the first cut
-  for (int i = tid; i < n_sub; i += kThrThreads) {
-    float v = row[i];
+  const int nt = (int)s_ntile;
+  if (nt > kTileCap) {
+    if (tid == 0) cand_n[q] = -1;
+    return;
+  }
+  // ... and their sub-blocks at or above it
+  for (int e = tid; e < nt * SUBS_PER_TILE; e += kThrThreads) {
+    const int sub = s_tile[e / SUBS_PER_TILE] * SUBS_PER_TILE + (e % SUBS_PER_TILE);
+    const float v = row[sub];
     if (v >= cut1 && v > -INFINITY) {
       unsigned pos = atomicAdd(&s_count, 1u);
-      if (pos < (unsigned)kCollectCap) { s_val[pos] = v; s_id[pos] = i; }
+      if (pos < (unsigned)kCollectCap) { s_val[pos] = v; s_id[pos] = sub; }
     }
   }
   __syncthreads();
@@ -419,7 +489,10 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, int 
     }
   }
   __syncthreads();
-  if (tid == 0) cand_n[q] = (int)s_out > cand_cap ? -1 : (int)s_out;
+  if (tid == 0) {
+    cand_n[q] = (int)s_out > cand_cap ? -1 : (int)s_out;
+    cut_out[q] = cut2;  // the refine step applies the same cut row by row
+  }
 }
 
 // ---------------------------------------------------------------- step 4: refine
@@ -436,20 +509,29 @@ __device__ __forceinline__ bool excluded_slot(const int32_t* excl, int n, int32_
   return false;
 }
 
-// One CTA per query: fp32 scores of every row of the candidate sub-blocks (one warp per sub-block),
-// the k best kept in a shared
-// candidate array, then the exact finishing pass.  Same selection rule and the same exact arithmetic
-// as scan_topn.cu, so results are identical to the single-query path.
+// One CTA per query, one warp per candidate sub-block, two stages:
+//   A. score the sub-block's 32 rows against the bf16 shadow of Y (the very rows the tensor cores saw,
+//      256 bytes each at 128 features; fp32 query, fp32 accumulate) and keep the rows whose score
+//      reaches the query's cut T' - 2 delta.  |q . bf16(y) - q . y| <= delta / 2, so every row with an
+//      exact score >= T' - delta -- every possible top-k member -- passes;
+//   B. the survivors (one or two per sub-block) are scored from the fp32 rows, the whole warp on one
+//      row, and offered to the shared top-k array.
+// Then the exact finishing pass: same selection rule and the same exact arithmetic as scan_topn.cu,
+// so results are identical to the single-query path.  Reading 8 KB of bf16 per sub-block instead of
+// 16 KB of fp32 nearly halves this step's traffic.
+template <int NCH>
 __global__ void __launch_bounds__(kRefineThreads)
-batch_refine_kernel(const float* __restrict__ y, const int32_t* __restrict__ slot_row, int64_t n_slots, int fpad,
+batch_refine_kernel(const float* __restrict__ y, const __nv_bfloat16* __restrict__ ybf, int kpad,
+                    const int32_t* __restrict__ slot_row, int64_t n_slots, int fpad,
                     int features, const float* __restrict__ queries, int kind, int k, int how_many,
                     const int32_t* __restrict__ cand, int cand_cap, const int32_t* __restrict__ cand_n,
+                    const float* __restrict__ cutv,
                     const int32_t* __restrict__ excl_offsets, const int32_t* __restrict__ excl_slots,
                     int32_t* __restrict__ out_rows, double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  // layout: q[fpad] f32 | arr[k] u64 | exact[k] f64 | rows[k] i32
+  // layout: q[kpad] f32 | arr[k] u64 | exact[k] f64 | rows[k] i32
   float* s_q = reinterpret_cast<float*>(smem_raw);
-  unsigned long long* arr = reinterpret_cast<unsigned long long*>(smem_raw + (((size_t)fpad * 4 + 15) & ~(size_t)15));
+  unsigned long long* arr = reinterpret_cast<unsigned long long*>(smem_raw + (((size_t)kpad * 4 + 15) & ~(size_t)15));
   double* s_exact = reinterpret_cast<double*>(arr + k);
   int32_t* s_rows = reinterpret_cast<int32_t*>(s_exact + k);
   __shared__ unsigned int s_thr_key;
@@ -459,77 +541,109 @@ batch_refine_kernel(const float* __restrict__ y, const int32_t* __restrict__ slo
     if (tid == 0) out_n[qi] = -1;
     return;
   }
-  for (int j = tid; j < fpad; j += kRefineThreads) s_q[j] = j < features ? queries[(size_t)qi * features + j] : 0.f;
+  for (int j = tid; j < kpad; j += kRefineThreads) s_q[j] = j < features ? queries[(size_t)qi * features + j] : 0.f;
   for (int i = tid; i < k; i += kRefineThreads) arr[i] = 0ull;
   if (tid == 0) s_thr_key = 0u;
   __syncthreads();
   const int32_t* excl = excl_offsets ? excl_slots + excl_offsets[qi] : nullptr;
   const int n_excl = excl_offsets ? excl_offsets[qi + 1] - excl_offsets[qi] : 0;
   const int32_t* my_cand = cand + (int64_t)qi * cand_cap;
+  const float cut = cutv[qi];
 
-  // one warp per candidate sub-block; 8 lanes share a row (coalesced 128-byte segments, as in the
-  // single-query scan), 4 rows per pass, 8 passes per sub-block
   const int gl = lane & 7, grp = lane >> 3;
   const int f4 = fpad >> 2;
   const float4* q4 = reinterpret_cast<const float4*>(s_q);
+  // offer one scored row (all lanes hold the same score/slot) to the shared top-k array
+  auto offer_row = [&](float score, int32_t slot) {
+    const uint32_t ky = float_key(score);
+    if (!(score == score) || ky <= *(volatile unsigned int*)&s_thr_key) return;
+    if (n_excl > 0 && excluded_slot(excl, n_excl, slot)) return;
+    // replace-the-minimum with a 64-bit CAS, whole warp searches (as in scan_topn.cu)
+    const unsigned long long x = ((unsigned long long)ky << 32) | (unsigned long long)(uint32_t)slot;
+    for (;;) {
+      unsigned long long best = ~0ull;
+      int best_idx = 0;
+      for (int i = lane; i < k; i += 32) {
+        unsigned long long v = *(const volatile unsigned long long*)(arr + i);
+        if (v < best) { best = v; best_idx = i; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
+        int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+        if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
+      }
+      if (ky <= (uint32_t)(best >> 32)) {
+        if (lane == 0) atomicMax(&s_thr_key, (uint32_t)(best >> 32));
+        break;
+      }
+      unsigned long long old = 0ull;
+      if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
+      old = __shfl_sync(0xffffffffu, old, 0);
+      if (old == best) break;
+    }
+  };
+  const int u4_per_row = kpad >> 3;  // 8 bf16 per 128-bit load; 8 lanes share a row: NCH loads per lane
   for (int c = warp; c < nc; c += kRefineThreads / 32) {
     const int64_t sub0 = (int64_t)my_cand[c] * SUB;
-#pragma unroll 2
-    for (int pass = 0; pass < SUB / 4; pass++) {
-      const int64_t slot = sub0 + pass * 4 + grp;
-      const bool in = slot < n_slots;
+    // ---- stage A: bf16 scores of the 32 rows, 4 passes (16 rows) of loads in flight at a time
+    unsigned pass_mask = 0u;  // bit (pass * 4 + grp) = row sub0 + pass*4 + grp reaches the cut
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+      uint4 a[4][NCH];
+#pragma unroll
+      for (int h = 0; h < 4; h++) {
+        const int64_t slot = sub0 + (half * 4 + h) * 4 + grp;
+        const uint4* r = reinterpret_cast<const uint4*>(ybf + slot * kpad);
+#pragma unroll
+        for (int u = 0; u < NCH; u++)
+          a[h][u] = slot < n_slots ? __ldg(r + gl + u * 8) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int h = 0; h < 4; h++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int u = 0; u < NCH; u++) {
+          const int j = gl + u * 8;  // 128-bit unit -> q elements 8j .. 8j+7
+          const float4 b0 = q4[2 * j], b1 = q4[2 * j + 1];
+          const uint4 v = a[h][u];
+          acc = fmaf(__uint_as_float(v.x << 16), b0.x, acc); acc = fmaf(__uint_as_float(v.x & 0xffff0000u), b0.y, acc);
+          acc = fmaf(__uint_as_float(v.y << 16), b0.z, acc); acc = fmaf(__uint_as_float(v.y & 0xffff0000u), b0.w, acc);
+          acc = fmaf(__uint_as_float(v.z << 16), b1.x, acc); acc = fmaf(__uint_as_float(v.z & 0xffff0000u), b1.y, acc);
+          acc = fmaf(__uint_as_float(v.w << 16), b1.z, acc); acc = fmaf(__uint_as_float(v.w & 0xffff0000u), b1.w, acc);
+        }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        const int64_t slot = sub0 + (half * 4 + h) * 4 + grp;
+        const bool keep = gl == 0 && slot < n_slots && acc >= cut;  // NaN (tombstone) compares false
+        const unsigned ball = __ballot_sync(0xffffffffu, keep);     // bits 0, 8, 16, 24 <-> grp 0..3
+        pass_mask |= (((ball >> 0) & 1u) | (((ball >> 8) & 1u) << 1) | (((ball >> 16) & 1u) << 2) |
+                      (((ball >> 24) & 1u) << 3))
+                     << ((half * 4 + h) * 4);
+      }
+    }
+    (void)u4_per_row;
+    // ---- stage B: fp32 score of each surviving row, the whole warp on one row
+    while (pass_mask != 0u) {
+      const int r = __ffs(pass_mask) - 1;
+      pass_mask &= pass_mask - 1;
+      const int64_t slot = sub0 + r;
+      const float4* r4 = reinterpret_cast<const float4*>(y + slot * fpad);
       float acc = 0.f, nrm = 0.f;
-      if (in) {
-        const float4* r4 = reinterpret_cast<const float4*>(y + slot * fpad);
-        for (int j = gl; j < f4; j += 8) {
-          const float4 a = __ldg(r4 + j);
-          const float4 b = q4[j];
-          acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
-          if (kind == ORYX_COSINE) {
-            nrm = fmaf(a.x, a.x, nrm); nrm = fmaf(a.y, a.y, nrm); nrm = fmaf(a.z, a.z, nrm); nrm = fmaf(a.w, a.w, nrm);
-          }
+      for (int j = lane; j < f4; j += 32) {
+        const float4 v = __ldg(r4 + j);
+        const float4 b = q4[j];
+        acc = fmaf(v.x, b.x, acc); acc = fmaf(v.y, b.y, acc); acc = fmaf(v.z, b.z, acc); acc = fmaf(v.w, b.w, acc);
+        if (kind == ORYX_COSINE) {
+          nrm = fmaf(v.x, v.x, nrm); nrm = fmaf(v.y, v.y, nrm); nrm = fmaf(v.z, v.z, nrm); nrm = fmaf(v.w, v.w, nrm);
         }
       }
 #pragma unroll
-      for (int o = 4; o > 0; o >>= 1) {
+      for (int o = 16; o > 0; o >>= 1) {
         acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (kind == ORYX_COSINE) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
       }
-      const float score = (kind == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc;
-      const uint32_t key = float_key(score);
-      bool hit = in && gl == 0 && score == score && key > *(volatile unsigned int*)&s_thr_key;
-      if (hit && n_excl > 0 && excluded_slot(excl, n_excl, (int32_t)slot)) hit = false;
-      unsigned ball = __ballot_sync(0xffffffffu, hit);
-      while (ball != 0u) {
-        const int src = __ffs(ball) - 1;
-        ball &= ball - 1;
-        const uint32_t ky = __shfl_sync(0xffffffffu, key, src);
-        const int32_t sl = __shfl_sync(0xffffffffu, (int32_t)slot, src);
-        // replace-the-minimum with a 64-bit CAS, whole warp searches (as in scan_topn.cu)
-        const unsigned long long x = ((unsigned long long)ky << 32) | (unsigned long long)(uint32_t)sl;
-        for (;;) {
-          unsigned long long best = ~0ull;
-          int best_idx = 0;
-          for (int i = lane; i < k; i += 32) {
-            unsigned long long v = *(const volatile unsigned long long*)(arr + i);
-            if (v < best) { best = v; best_idx = i; }
-          }
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            unsigned long long ov = __shfl_xor_sync(0xffffffffu, best, o);
-            int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
-            if (ov < best || (ov == best && oi < best_idx)) { best = ov; best_idx = oi; }
-          }
-          if (ky <= (uint32_t)(best >> 32)) {
-            if (lane == 0) atomicMax(&s_thr_key, (uint32_t)(best >> 32));
-            break;
-          }
-          unsigned long long old = 0ull;
-          if (lane == 0) old = atomicCAS(arr + best_idx, best, x);
-          old = __shfl_sync(0xffffffffu, old, 0);
-          if (old == best) break;
-        }
-      }
+      offer_row((kind == ORYX_COSINE) ? acc * rsqrtf(nrm) : acc, (int32_t)slot);
     }
   }
   __syncthreads();
@@ -621,12 +735,13 @@ int32_t make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t kpad, uin
 
 template <int NCH>
 int32_t launch_score(const CUtensorMap& tq, const CUtensorMap& ty, int n_qtiles, int n_ytiles, int64_t n_slots,
-                     float* bmax, int64_t bmax_stride, int num_sms, cudaStream_t st) {
+                     float* bmax, int64_t bmax_stride, float* tmax, int64_t tmax_stride, int num_sms, cudaStream_t st) {
   constexpr int YB = (NCH <= 2) ? 2 : 1;
   const size_t smem = ScoreSmem::bytes(NCH, YB);
   ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_score_kernel<NCH>), smem));
   const int grid = std::min(num_sms, n_ytiles);
-  batch_score_kernel<NCH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride);
+  batch_score_kernel<NCH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride, tmax,
+                                                             tmax_stride);
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }
@@ -674,20 +789,23 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   const int n_ytiles = (int)((n + BN - 1) / BN);
   const int n_sub = n_ytiles * SUBS_PER_TILE;
   const int64_t bmax_stride = n_sub;
+  const int64_t tmax_stride = (n_ytiles + 3) / 4 * 4;
   const int cand_cap = 4096;
 
   BatchScratch& bs = m->batch;
   std::lock_guard<std::mutex> batch_lock(bs.mu);
-  struct P { void* p = nullptr; } d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
+  struct P { void* p = nullptr; } d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_tmax, d_cut, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
   bool y_grew = false;
   ORYX_TRY(scratch(bs, 0, (size_t)n * kpad * 2, &d_ybf.p, &y_grew));
   ORYX_TRY(scratch(bs, 1, (size_t)nq_pad * kpad * 2, &d_qbf.p));
   ORYX_TRY(scratch(bs, 2, (size_t)nq * F * 4, &d_q.p));
   ORYX_TRY(scratch(bs, 3, (size_t)nq_pad * 4, &d_qnorm.p));
   ORYX_TRY(scratch(bs, 4, 4, &d_maxn.p));
-  ORYX_TRY(scratch(bs, 5, (size_t)nq_pad * bmax_stride * 4, &d_bmax.p));
+  ORYX_TRY(scratch(bs, 5, (size_t)nq_pad * (bmax_stride + tmax_stride) * 4, &d_bmax.p));
+  d_tmax.p = reinterpret_cast<float*>(d_bmax.p) + (size_t)nq_pad * bmax_stride;
   ORYX_TRY(scratch(bs, 6, (size_t)nq * cand_cap * 4, &d_cand.p));
-  ORYX_TRY(scratch(bs, 7, (size_t)nq * 4, &d_candn.p));
+  ORYX_TRY(scratch(bs, 7, (size_t)nq * 8, &d_candn.p));
+  d_cut.p = reinterpret_cast<int32_t*>(d_candn.p) + nq;
   ORYX_TRY(scratch(bs, 8, (size_t)nq * how_many * 4, &d_orows.p));
   ORYX_TRY(scratch(bs, 9, (size_t)nq * how_many * 8, &d_oscores.p));
   ORYX_TRY(scratch(bs, 10, (size_t)nq * 4, &d_on.p));
@@ -726,26 +844,39 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   ORYX_TRY(make_map(&ty, d_ybf.p, (uint64_t)n, (uint64_t)kpad, BN));
   int32_t rc;
   switch (nch) {
-    case 1: rc = launch_score<1>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
-    case 2: rc = launch_score<2>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
-    case 3: rc = launch_score<3>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
-    default: rc = launch_score<4>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, m->num_sms, st); break;
+    case 1: rc = launch_score<1>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
+    case 2: rc = launch_score<2>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
+    case 3: rc = launch_score<3>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
+    default: rc = launch_score<4>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
   }
   ORYX_TRY(rc);
   ORYX_CUDA(cudaEventRecord(ev[2], st));
 
-  batch_threshold_kernel<<<nq, kThrThreads, 0, st>>>((const float*)d_bmax.p, bmax_stride, n_sub, k,
-                                                    (const float*)d_qnorm.p, (const unsigned int*)d_maxn.p,
-                                                    (int32_t*)d_cand.p, cand_cap, (int32_t*)d_candn.p);
+  batch_threshold_kernel<<<nq, kThrThreads, 0, st>>>((const float*)d_bmax.p, bmax_stride, (const float*)d_tmax.p,
+                                                    tmax_stride, n_ytiles, k, (const float*)d_qnorm.p,
+                                                    (const unsigned int*)d_maxn.p, (int32_t*)d_cand.p, cand_cap,
+                                                    (int32_t*)d_candn.p, (float*)d_cut.p);
   ORYX_CUDA(cudaGetLastError());
   ORYX_CUDA(cudaEventRecord(ev[3], st));
 
-  const size_t rsmem = (((size_t)fpad * 4 + 15) & ~(size_t)15) + (size_t)k * 20 + 16;
-  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_refine_kernel), 64 * 1024));
-  batch_refine_kernel<<<nq, kRefineThreads, rsmem, st>>>(
-      s->d_vec, s->d_slot_row, n, fpad, F, (const float*)d_q.p, kind, k, how_many, (const int32_t*)d_cand.p,
-      cand_cap, (const int32_t*)d_candn.p, excl_offsets ? (const int32_t*)d_eo.p : nullptr,
-      excl_offsets ? (const int32_t*)d_es.p : nullptr, (int32_t*)d_orows.p, (double*)d_oscores.p, (int32_t*)d_on.p);
+  const size_t rsmem = (((size_t)kpad * 4 + 15) & ~(size_t)15) + (size_t)k * 20 + 16;
+  auto launch_refine = [&](auto kern) -> int32_t {
+    ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(kern), 64 * 1024));
+    kern<<<nq, kRefineThreads, rsmem, st>>>(
+        s->d_vec, (const __nv_bfloat16*)d_ybf.p, kpad, s->d_slot_row, n, fpad, F, (const float*)d_q.p, kind, k,
+        how_many, (const int32_t*)d_cand.p, cand_cap, (const int32_t*)d_candn.p, (const float*)d_cut.p,
+        excl_offsets ? (const int32_t*)d_eo.p : nullptr, excl_offsets ? (const int32_t*)d_es.p : nullptr,
+        (int32_t*)d_orows.p, (double*)d_oscores.p, (int32_t*)d_on.p);
+    return ORYX_OK;
+  };
+  int32_t rrc;
+  switch (nch) {  // 128-bit loads per lane per bf16 row (8 lanes share a row)
+    case 1: rrc = launch_refine(batch_refine_kernel<1>); break;
+    case 2: rrc = launch_refine(batch_refine_kernel<2>); break;
+    case 3: rrc = launch_refine(batch_refine_kernel<3>); break;
+    default: rrc = launch_refine(batch_refine_kernel<4>); break;
+  }
+  ORYX_TRY(rrc);
   ORYX_CUDA(cudaGetLastError());
   ORYX_CUDA(cudaEventRecord(ev[4], st));
   ORYX_CUDA(cudaMemcpyAsync(out_rows, d_orows.p, (size_t)nq * how_many * 4, cudaMemcpyDeviceToHost, st));
@@ -760,6 +891,15 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
     cudaEventElapsedTime(&ms, ev[2], ev[3]); timings->threshold_ms = ms;
     cudaEventElapsedTime(&ms, ev[3], ev[4]); timings->refine_ms = ms;
     timings->flops = 2.0 * (double)nq_pad * (double)n_ytiles * BN * (double)kpad;
+    std::vector<int32_t> cn((size_t)nq);
+    if (cudaMemcpy(cn.data(), d_candn.p, (size_t)nq * 4, cudaMemcpyDeviceToHost) == cudaSuccess) {
+      double sum = 0, mx = 0;
+      for (int32_t v : cn) { sum += std::max(v, 0); mx = std::max(mx, (double)v); }
+      timings->cand_mean = sum / std::max(nq, 1);
+      timings->cand_max = mx;
+    } else {
+      cudaGetLastError();
+    }
   }
   return ORYX_OK;
 }

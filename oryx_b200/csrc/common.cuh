@@ -172,6 +172,7 @@ struct QueryCtx {
 
 struct BatchTimings {
   double convert_ms = 0, score_ms = 0, threshold_ms = 0, refine_ms = 0, flops = 0;
+  double cand_mean = 0, cand_max = 0;  // candidate sub-blocks per query handed to the refine step
 };
 
 // Grow-only device scratch of the tensor-core batch path, kept across calls (one batch at a time).
