@@ -30,6 +30,24 @@ namespace {
 
 constexpr int kRowsPerCta = 64;  // interactions per CTA
 
+// One warp per interaction: copy the row living in `slots[i]` of a store (or zeros when the slot is
+// negative) into a packed [n x f] buffer.
+__global__ void gather_rows_kernel(const float* __restrict__ vec, int fpad, int f, const int32_t* __restrict__ slots,
+                                   int64_t n, float* __restrict__ out, uint8_t* __restrict__ has) {
+  const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  const int32_t slot = slots[w];
+  float* dst = out + w * f;
+  if (slot >= 0) {
+    const float* src = vec + (int64_t)slot * fpad;
+    for (int j = lane; j < f; j += 32) dst[j] = src[j];
+  } else {
+    for (int j = lane; j < f; j += 32) dst[j] = 0.f;
+  }
+  if (lane == 0 && has) has[w] = slot >= 0 ? 1 : 0;
+}
+
 // ALSUtils.java:37-59
 __device__ __forceinline__ double target_qui(bool implicit, double value, double current) {
   if (implicit) {
@@ -209,6 +227,90 @@ int32_t oryx_fold_in_batch(oryx_solver* sh, int32_t implicit, const float* xu, c
       set_error("fold-in batch failed: %s", cudaGetErrorString(e));
       rc = ORYX_E_CUDA;
     }
+  }
+  cleanup();
+  return rc;
+}
+
+int32_t oryx_fold_in_rows(oryx_solver* sh, oryx_model* mh, int32_t implicit, int32_t xu_which,
+                          const int32_t* xu_rows, const int32_t* yi_rows, const double* values, int64_t n,
+                          float* out, uint8_t* out_valid) {
+  ORYX_ARG(sh && mh && xu_rows && yi_rows && values && out && out_valid, "null argument");
+  ORYX_ARG(xu_which == ORYX_X || xu_which == ORYX_Y, "xu_which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  Solver* s = reinterpret_cast<Solver*>(sh);
+  Model* m = reinterpret_cast<Model*>(mh);
+  const int f = solver_n(s);
+  ORYX_ARG(f == m->cfg.features, "solver and model disagree on the number of features");
+  ORYX_ARG(solver_device(s) == m->device, "solver and model live on different devices");
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+  if (cudaSetDevice(m->device) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("cannot select CUDA device %d", m->device);
+    return ORYX_E_CUDA;
+  }
+  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  std::lock_guard<std::mutex> lk(solver_mutex(s));
+  std::shared_lock<std::shared_mutex> model_lock(m->mu);  // the stores must not move while rows are gathered
+  const Store* sx = &m->store[xu_which];
+  const Store* sy = &m->store[xu_which == ORYX_X ? ORYX_Y : ORYX_X];
+  cudaStream_t st = solver_stream(s);
+  const int64_t chunk = 1 << 18;
+  const int64_t c_max = std::min<int64_t>(chunk, n);
+  float *d_xu = nullptr, *d_yi = nullptr, *d_out = nullptr;
+  double* d_val = nullptr;
+  uint8_t *d_has = nullptr, *d_valid = nullptr;
+  int32_t* d_slots = nullptr;  // [2 x c_max]
+  int32_t* h_slots = nullptr;  // pinned
+  auto cleanup = [&]() {
+    cudaFree(d_xu); cudaFree(d_yi); cudaFree(d_out); cudaFree(d_val); cudaFree(d_has); cudaFree(d_valid);
+    cudaFree(d_slots); cudaFreeHost(h_slots);
+  };
+  if (cudaMalloc(&d_xu, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_yi, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_out, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_val, (size_t)c_max * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&d_has, (size_t)c_max) != cudaSuccess || cudaMalloc(&d_valid, (size_t)c_max) != cudaSuccess ||
+      cudaMalloc(&d_slots, (size_t)c_max * 2 * sizeof(int32_t)) != cudaSuccess ||
+      cudaMallocHost(&h_slots, (size_t)c_max * 2 * sizeof(int32_t)) != cudaSuccess) {
+    cudaGetLastError();
+    cleanup();
+    set_error("allocation failed for a fold-in batch of %lld", (long long)c_max);
+    return ORYX_E_NOMEM;
+  }
+  auto slot_of = [](const Store* store, int32_t row) -> int32_t {
+    return (row >= 0 && (size_t)row < store->row2slot.size()) ? store->row2slot[(size_t)row] : -1;
+  };
+  int32_t rc = ORYX_OK;
+  for (int64_t off = 0; off < n && rc == ORYX_OK; off += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - off);
+    for (int64_t i = 0; i < c; i++) {
+      h_slots[i] = slot_of(sx, xu_rows[off + i]);
+      h_slots[c_max + i] = slot_of(sy, yi_rows[off + i]);
+    }
+    cudaError_t e = cudaMemcpyAsync(d_slots, h_slots, (size_t)c_max * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+      const unsigned g = (unsigned)((c * 32 + 255) / 256);
+      gather_rows_kernel<<<g, 256, 0, st>>>(sx->d_vec, sx->fpad, f, d_slots, c, d_xu, d_has);
+      gather_rows_kernel<<<g, 256, 0, st>>>(sy->d_vec, sy->fpad, f, d_slots + c_max, c, d_yi, nullptr);
+      const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
+      fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, d_xu, d_has, d_yi, d_val, c, d_out, d_valid);
+      m->launches += 3;
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * f, d_out, (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_valid + off, d_valid, (size_t)c, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      set_error("fold-in batch failed: %s", cudaGetErrorString(e));
+      rc = ORYX_E_CUDA;
+      break;
+    }
+    // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81)
+    for (int64_t i = 0; i < c; i++) if (h_slots[c_max + i] < 0) out_valid[off + i] = 0;
   }
   cleanup();
   return rc;

@@ -636,25 +636,27 @@ std::vector<Update> ALSSpeedModel::buildUpdates(const std::vector<UserItemStreng
   auto yty = getYTYSolver();
   if (!xtx || !yty) return out;
   const size_t n = input.size(), f = (size_t)features_;
-  // gather the snapshot vectors of every interaction (:186-187), then two device batches:
+  // Every interaction reads the same model snapshot (:186-187); the vectors never leave the device:
   //   newXu = computeUpdatedXu(YTYsolver, value, Xu, Yi)   :192
   //   newYi = computeUpdatedXu(XTXsolver, value, Yi, Xu)   :194
-  std::vector<float> xu(n * f, 0.0f), yi(n * f, 0.0f);
+  std::vector<int32_t> xr(n), yr(n);
   std::vector<uint8_t> has_x(n, 0), has_y(n, 0);
   std::vector<double> values(n);
   for (size_t k = 0; k < n; k++) {
     values[k] = input[k].strength;
-    auto ix = x_.vec.find(input[k].user);
-    auto iy = y_.vec.find(input[k].item);
-    if (ix != x_.vec.end()) { has_x[k] = 1; std::copy(ix->second.begin(), ix->second.end(), xu.begin() + k * f); }
-    if (iy != y_.vec.end()) { has_y[k] = 1; std::copy(iy->second.begin(), iy->second.end(), yi.begin() + k * f); }
+    auto ix = x_.row.find(input[k].user);
+    auto iy = y_.row.find(input[k].item);
+    xr[k] = ix == x_.row.end() ? -1 : ix->second;
+    yr[k] = iy == y_.row.end() ? -1 : iy->second;
+    has_x[k] = xr[k] >= 0;
+    has_y[k] = yr[k] >= 0;
   }
   std::vector<float> new_x(n * f), new_y(n * f);
   std::vector<uint8_t> ok_x(n), ok_y(n);
-  check_status(oryx_fold_in_batch(yty->handle(), implicit_ ? 1 : 0, xu.data(), has_x.data(), yi.data(), values.data(),
-                                  (int64_t)n, new_x.data(), ok_x.data()));
-  check_status(oryx_fold_in_batch(xtx->handle(), implicit_ ? 1 : 0, yi.data(), has_y.data(), xu.data(), values.data(),
-                                  (int64_t)n, new_y.data(), ok_y.data()));
+  check_status(oryx_fold_in_rows(yty->handle(), h_, implicit_ ? 1 : 0, ORYX_X, xr.data(), yr.data(), values.data(),
+                                 (int64_t)n, new_x.data(), ok_x.data()));
+  check_status(oryx_fold_in_rows(xtx->handle(), h_, implicit_ ? 1 : 0, ORYX_Y, yr.data(), xr.data(), values.data(),
+                                 (int64_t)n, new_y.data(), ok_y.data()));
   for (size_t k = 0; k < n; k++) {
     // computeUpdatedXu returns null when its "Yi" argument is null (ALSUtils.java:79-81)
     if (ok_x[k] && has_y[k]) out.push_back(Update{'X', input[k].user, FloatVec(new_x.begin() + k * f, new_x.begin() + (k + 1) * f), input[k].item});

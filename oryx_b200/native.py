@@ -89,6 +89,7 @@ SIGNATURES = {
     "oryx_exchange_destroy": [C.c_void_p],
     "oryx_topn_sharded_device": [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_fold_in_rows": [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, _i32p, _i32p, _f64p, C.c_int64, _f32p, _u8p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
@@ -434,4 +435,17 @@ class Solver:
         _check(lib().oryx_fold_in_batch(self._h, int(implicit), _ptr(xu_a, C.c_float), _ptr(has, C.c_uint8),
                                         _ptr(yi, C.c_float), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),
                                         _ptr(valid, C.c_uint8)))
+        return out, valid
+
+    def fold_in_rows(self, model: "Model", implicit: bool, xu_which: int, xu_rows, yi_rows, values):
+        """computeUpdatedXu for n interactions whose vectors are rows of the model's device stores."""
+        xr = np.ascontiguousarray(xu_rows, dtype=np.int32)
+        yr = np.ascontiguousarray(yi_rows, dtype=np.int32)
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        n = xr.size
+        out = np.empty((n, self.n), dtype=np.float32)
+        valid = np.zeros(n, dtype=np.uint8)
+        _check(lib().oryx_fold_in_rows(self._h, model._h, int(implicit), xu_which, _ptr(xr, C.c_int32),
+                                       _ptr(yr, C.c_int32), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),
+                                       _ptr(valid, C.c_uint8)))
         return out, valid

@@ -436,3 +436,42 @@ def test_gram_large_store_fast_path(n, f):
         assert used == n - 2
         assert np.max(np.abs(g - exp)) <= 1e-8 * np.max(np.abs(exp))
         assert np.array_equal(g, g.T)
+
+
+def test_fold_in_rows_equals_host_buffer_path():
+    """oryx_fold_in_rows (Xu / Yi gathered from the device stores) gives bit-identical results to
+    oryx_fold_in_batch on the same vectors, including null Xu, null Yi and removed rows."""
+    rng = np.random.default_rng(0xB2000060)
+    f, nu, ni, n = 40, 500, 700, 3000
+    x = rng.standard_normal((nu, f), dtype=np.float32) * 0.3
+    y = rng.standard_normal((ni, f), dtype=np.float32) * 0.3
+    with ob.Model(f) as m:
+        m.upsert(ob.X, np.arange(nu, dtype=np.int32), x)
+        m.upsert(ob.Y, np.arange(ni, dtype=np.int32), y)
+        gone_x, gone_y = np.array([3, 77], np.int32), np.array([5, 600], np.int32)
+        m.remove(ob.X, gone_x)
+        m.remove(ob.Y, gone_y)
+        yty = ob.Solver(m.gram(ob.Y)[0])
+        xtx = ob.Solver(m.gram(ob.X)[0])
+        ur = rng.integers(-1, nu + 20, n).astype(np.int32)   # -1 and rows >= nu: unknown users
+        ir = rng.integers(0, ni + 20, n).astype(np.int32)    # rows >= ni: unknown items
+        ur[:4] = [3, 77, 10, 11]
+        ir[:4] = [1, 2, 5, 600]
+        vals = rng.choice([1.0, 2.5, -1.0, 0.0, 0.5], n)
+        has_x = ((ur >= 0) & (ur < nu) & ~np.isin(ur, gone_x)).astype(np.uint8)
+        has_y = ((ir < ni) & ~np.isin(ir, gone_y)).astype(np.uint8)
+        xu = np.where(has_x[:, None] == 1, x[np.clip(ur, 0, nu - 1)], 0).astype(np.float32)
+        yi = np.where(has_y[:, None] == 1, y[np.clip(ir, 0, ni - 1)], 0).astype(np.float32)
+        for implicit in (True, False):
+            # new user vectors: solver of Y, Xu from X rows, Yi from Y rows
+            want, wv = yty.fold_in_batch(implicit, xu, has_x, yi, vals)
+            got, gv = yty.fold_in_rows(m, implicit, ob.X, ur, ir, vals)
+            wv = wv & has_y
+            assert np.array_equal(gv, wv)
+            assert np.array_equal(got[gv == 1], want[wv == 1])
+            # new item vectors: solver of X, "Xu" from Y rows, "Yi" from X rows
+            want, wv = xtx.fold_in_batch(implicit, yi, has_y, xu, vals)
+            got, gv = xtx.fold_in_rows(m, implicit, ob.Y, ir, ur, vals)
+            wv = wv & has_x
+            assert np.array_equal(gv, wv)
+            assert np.array_equal(got[gv == 1], want[wv == 1])
