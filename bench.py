@@ -177,6 +177,33 @@ def cpu_leg(y_host: np.ndarray, queries: np.ndarray, threads: int, budget_s: flo
     return 1.0 / per_query, i, per_query
 
 
+def cpu_faithful_leg(y_host: np.ndarray, queries: np.ndarray, threads: int, scale_items: int, n_parts: int,
+                     hash_vectors: np.ndarray):
+    """The "faithful" arm (SURVEY.md 8d variant i): per-partition String-keyed hash maps of separately
+    allocated float[], String-set known-items predicate, one task per partition -- on a bounded sample
+    of the rows, time scaled linearly to `scale_items`."""
+    import oracle
+    rows = min(y_host.shape[0], 2_000_000)
+    sample = y_host[:rows]
+    part = oracle.lsh_index_rows(hash_vectors, sample) if n_parts > 1 else None
+    t0 = time.perf_counter()
+    fm = oracle.FaithfulModel(sample, part, n_parts)
+    build_s = time.perf_counter() - t0
+    rng = np.random.default_rng(0xB2000041)
+    times = []
+    for i in range(8):
+        known = rng.integers(0, rows, int(rng.poisson(20)))
+        t0 = time.perf_counter()
+        fm.topn(oracle.DOT, queries[i % len(queries)], HOW_MANY, known_rows=known, threads=threads)
+        times.append(time.perf_counter() - t0)
+    fm.close()
+    per_query = statistics.median(times[1:]) * (scale_items / rows)
+    return {"value": 1.0 / per_query, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{rows} rows in {n_parts} String-keyed partition maps (built in {build_s:.1f} s), Poisson(20) known "
+                      f"items as a String set, 7 queries, time scaled linearly to {scale_items} rows "
+                      "(oracle/oryx_oracle.c oro_faithful_topn)"}
+
+
 # ------------------------------------------------------------------------------------------ reference arm
 
 def run_reference(args):
@@ -483,6 +510,8 @@ def run_ours(args):
                         "unit": UNIT, "cores": threads, "kind": "port",
                         "sample": f"{sample_desc}; {n_q} queries, {per_q * 1000:.1f} ms each on {threads} threads "
                                   "(oracle/oryx_oracle.c oro_topn_mt: contiguous rows, TopNConsumer per slice)"}
+        # second arm: the reference's data layout and control flow too (slower; reported, not the headline)
+        cpu_baseline["faithful_layout"] = cpu_faithful_leg(y_sample, q_host, threads, n_items, 1 << H, hv)
 
     if rank == 0:
         line = {

@@ -62,6 +62,15 @@ def lib() -> C.CDLL:
                                     i32p, C.c_int, C.c_int, i64p, f64p]
         L.oro_topn_values.restype = C.c_int
         L.oro_topn_values.argtypes = [f64p, C.c_int64, C.c_int, i64p, f64p]
+        L.oro_faithful_create.restype = C.c_void_p
+        L.oro_faithful_create.argtypes = [C.c_int, C.c_int]
+        L.oro_faithful_put_rows.restype = None
+        L.oro_faithful_put_rows.argtypes = [C.c_void_p, i32p, C.c_char_p, f32p, C.c_int64]
+        L.oro_faithful_destroy.restype = None
+        L.oro_faithful_destroy.argtypes = [C.c_void_p]
+        L.oro_faithful_topn.restype = C.c_int
+        L.oro_faithful_topn.argtypes = [C.c_void_p, C.c_int, f32p, C.c_int, i32p, C.c_int, C.POINTER(C.c_char_p),
+                                        C.c_int, C.c_int, C.POINTER(C.c_int64), f64p]
         L.oro_topn_mt.restype = C.c_int
         L.oro_topn_mt.argtypes = [C.c_int, f32p, f32p, C.c_int64, C.c_int, i32p, C.c_int, C.c_int,
                                   C.c_int, i64p, f64p]
@@ -208,6 +217,43 @@ def topn_mt(kind: int, q, y, how_many: int, threads: int, excluded=None):
                           _p(excl_a, C.c_int32), 0 if excl_a is None else excl_a.size,
                           how_many, threads, _p(rows, C.c_int64), _p(scores, C.c_double))
     return rows[:k].copy(), scores[:k].copy()
+
+
+class FaithfulModel:
+    """The "faithful" arm of the CPU baseline (oryx_oracle.c, section "faithful CPU baseline"): one
+    String-keyed hash map of heap-allocated float[] per LSH partition, String-set known-items
+    predicate, one task per candidate partition on a thread pool -- the structure of
+    ALSServingModel.topN (ALSServingModel.java:289-335).  Item ids are ``"I<row>"``."""
+
+    def __init__(self, y, part=None, n_partitions: int = 1):
+        y = _f32(y)
+        self.n, self.f = y.shape
+        self.n_partitions = n_partitions
+        self._h = C.c_void_p(lib().oro_faithful_create(self.f, n_partitions))
+        part_a = None if part is None else np.ascontiguousarray(part, dtype=np.int32)
+        lib().oro_faithful_put_rows(self._h, _p(part_a, C.c_int32), b"I", _p(y, C.c_float), self.n)
+
+    def topn(self, kind: int, q, how_many: int, cand=None, known_rows=(), threads: int = 1):
+        q = _f32(q)
+        cand_a = np.ascontiguousarray(np.arange(self.n_partitions) if cand is None else cand, dtype=np.int32)
+        ids = [b"I%d" % int(r) for r in known_rows]
+        arr = (C.c_char_p * max(len(ids), 1))(*ids)
+        rows = np.zeros(max(how_many, 1), dtype=np.int64)
+        scores = np.zeros(max(how_many, 1), dtype=np.float64)
+        k = lib().oro_faithful_topn(self._h, kind, _p(q, C.c_float), how_many, _p(cand_a, C.c_int32), cand_a.size,
+                                    arr, len(ids), threads, _p(rows, C.c_int64), _p(scores, C.c_double))
+        return rows[:k].copy(), scores[:k].copy()
+
+    def close(self):
+        if self._h:
+            lib().oro_faithful_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def topn_values(scores, how_many: int):

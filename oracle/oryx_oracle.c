@@ -41,6 +41,7 @@
 #include <math.h>
 #include <pthread.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -677,5 +678,183 @@ int oro_topn_mt(int kind, const float* q, const float* y, int64_t n, int f,
   int n_out = n_all < (size_t)how_many ? (int)n_all : how_many;
   for (int i = 0; i < n_out; i++) { out_rows[i] = all[i].row; out_scores[i] = all[i].score; }
   free(all); free(tasks); free(tids);
+  return n_out;
+}
+
+/* ------------------------------------------------------------------ "faithful" CPU baseline
+ *
+ * The second arm of the timed CPU baseline (variant i): not only the
+ * reference's arithmetic but its data layout and control flow --
+ *   - one hash map per LSH partition, String id -> separately heap-allocated float[F]
+ *     (FV:36-46 ObjObjMap<String,float[]>; ASM:69,97-124 `FeatureVectors[] Y`);
+ *   - the allowed-predicate is a hash-set lookup on the String id for every item
+ *     (Recommend.java:92-99 `knownItems.contains(id)`; TNC:57-59);
+ *   - one task per candidate partition on a pool of `threads` workers, each with its own
+ *     TopNConsumer, results concatenated and sorted (ASM:295-334).
+ * Ids carry their cached hash, as a java.lang.String does.  Iteration is in table order, so ties
+ * between equal scores may resolve differently from the row-ordered arms (as in the reference,
+ * where Koloboke's iteration order decides).
+ */
+typedef struct { char* id; uint32_t hash; float* vec; int64_t row; } oro_fentry;
+typedef struct { oro_fentry* slots; size_t cap, n; } oro_fmap;
+typedef struct { int f, parts; oro_fmap* maps; } oro_faithful;
+
+static uint32_t str_hash(const char* s) { /* String.hashCode(): s[0]*31^(n-1) + ... */
+  uint32_t h = 0;
+  for (; *s; s++) h = 31u * h + (uint32_t)(unsigned char)*s;
+  return h;
+}
+static uint32_t mix_hash(uint32_t h) { h ^= h >> 16; h *= 0x9E3779B1u; return h ^ (h >> 15); }
+
+static void fmap_grow(oro_fmap* m) {
+  size_t ncap = m->cap ? m->cap * 2 : 64;
+  oro_fentry* ns = (oro_fentry*)calloc(ncap, sizeof(oro_fentry));
+  for (size_t i = 0; i < m->cap; i++) {
+    if (!m->slots[i].id) continue;
+    size_t p = mix_hash(m->slots[i].hash) & (ncap - 1);
+    while (ns[p].id) p = (p + 1) & (ncap - 1);
+    ns[p] = m->slots[i];
+  }
+  free(m->slots);
+  m->slots = ns;
+  m->cap = ncap;
+}
+
+void* oro_faithful_create(int features, int partitions) {
+  oro_faithful* h = (oro_faithful*)calloc(1, sizeof(oro_faithful));
+  h->f = features;
+  h->parts = partitions < 1 ? 1 : partitions;
+  h->maps = (oro_fmap*)calloc((size_t)h->parts, sizeof(oro_fmap));
+  return h;
+}
+
+/* setItemVector (ASM:161-183): new float[] per item, keyed by id, in the partition's map. */
+void oro_faithful_put(void* hh, int partition, const char* id, int64_t row, const float* vec) {
+  oro_faithful* h = (oro_faithful*)hh;
+  oro_fmap* m = &h->maps[partition];
+  if ((m->n + 1) * 2 > m->cap) fmap_grow(m);
+  uint32_t hs = str_hash(id);
+  size_t p = mix_hash(hs) & (m->cap - 1);
+  while (m->slots[p].id) {
+    if (m->slots[p].hash == hs && strcmp(m->slots[p].id, id) == 0) {
+      memcpy(m->slots[p].vec, vec, sizeof(float) * (size_t)h->f);
+      return;
+    }
+    p = (p + 1) & (m->cap - 1);
+  }
+  {
+    size_t len = strlen(id) + 1;
+    m->slots[p].id = (char*)malloc(len);
+    memcpy(m->slots[p].id, id, len);
+  }
+  m->slots[p].hash = hs;
+  m->slots[p].row = row;
+  m->slots[p].vec = (float*)malloc(sizeof(float) * (size_t)h->f);
+  memcpy(m->slots[p].vec, vec, sizeof(float) * (size_t)h->f);
+  m->n++;
+}
+
+/* Bulk load: rows [0, n) of y with ids "<prefix><row>" (LoadTestALSModelFactory.java:62-95 ids "I<j>"),
+ * partition part[row] (NULL: partition 0). */
+void oro_faithful_put_rows(void* hh, const int32_t* part, const char* prefix, const float* y, int64_t n) {
+  oro_faithful* h = (oro_faithful*)hh;
+  char id[64];
+  for (int64_t row = 0; row < n; row++) {
+    snprintf(id, sizeof(id), "%s%lld", prefix, (long long)row);
+    oro_faithful_put(hh, part ? part[row] : 0, id, row, y + row * (int64_t)h->f);
+  }
+}
+
+void oro_faithful_destroy(void* hh) {
+  oro_faithful* h = (oro_faithful*)hh;
+  if (!h) return;
+  for (int p = 0; p < h->parts; p++) {
+    for (size_t i = 0; i < h->maps[p].cap; i++) { free(h->maps[p].slots[i].id); free(h->maps[p].slots[i].vec); }
+    free(h->maps[p].slots);
+  }
+  free(h->maps);
+  free(h);
+}
+
+typedef struct { char** ids; uint32_t* hashes; size_t cap; } oro_strset;
+static int strset_contains(const oro_strset* s, const char* id, uint32_t hs) {
+  if (s->cap == 0) return 0;
+  size_t p = mix_hash(hs) & (s->cap - 1);
+  while (s->ids[p]) {
+    if (s->hashes[p] == hs && strcmp(s->ids[p], id) == 0) return 1;
+    p = (p + 1) & (s->cap - 1);
+  }
+  return 0;
+}
+
+typedef struct {
+  const oro_faithful* h; int kind; const float* q; int how_many;
+  const int32_t* cand; int n_cand; int next; pthread_mutex_t* mu;
+  const oro_strset* known;
+  oro_topn* per_task; /* one TopNConsumer per candidate partition */
+} oro_fjob;
+
+static void* faithful_worker(void* arg) {
+  oro_fjob* j = (oro_fjob*)arg;
+  for (;;) {
+    pthread_mutex_lock(j->mu);
+    int t = j->next < j->n_cand ? j->next++ : -1;
+    pthread_mutex_unlock(j->mu);
+    if (t < 0) return NULL;
+    const oro_fmap* m = &j->h->maps[j->cand[t]];
+    oro_topn* top = &j->per_task[t];
+    topn_init(top, j->how_many);
+    for (size_t i = 0; i < m->cap; i++) { /* FeatureVectors.forEach (FV:141-145) */
+      const oro_fentry* e = &m->slots[i];
+      if (!e->id) continue;
+      if (j->known && strset_contains(j->known, e->id, e->hash)) continue; /* TNC:57 */
+      double s = score_of(j->kind, j->q, e->vec, j->h->f);
+      topn_accept(top, e->row, s, e->row);
+    }
+  }
+}
+
+/* ASM:289-335 over the candidate partitions `cand`; known_ids is the user's known-items set. */
+int oro_faithful_topn(void* hh, int kind, const float* q, int how_many, const int32_t* cand, int n_cand,
+                      const char* const* known_ids, int n_known, int threads, int64_t* out_rows,
+                      double* out_scores) {
+  oro_faithful* h = (oro_faithful*)hh;
+  oro_strset known = {0};
+  if (n_known > 0) {
+    size_t cap = 16;
+    while (cap < (size_t)n_known * 2) cap <<= 1;
+    known.cap = cap;
+    known.ids = (char**)calloc(cap, sizeof(char*));
+    known.hashes = (uint32_t*)calloc(cap, sizeof(uint32_t));
+    for (int i = 0; i < n_known; i++) {
+      uint32_t hs = str_hash(known_ids[i]);
+      size_t p = mix_hash(hs) & (cap - 1);
+      while (known.ids[p]) p = (p + 1) & (cap - 1);
+      known.ids[p] = (char*)known_ids[i];
+      known.hashes[p] = hs;
+    }
+  }
+  if (threads < 1) threads = 1;
+  pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+  oro_fjob job;
+  job.h = h; job.kind = kind; job.q = q; job.how_many = how_many;
+  job.cand = cand; job.n_cand = n_cand; job.next = 0; job.mu = &mu;
+  job.known = n_known > 0 ? &known : NULL;
+  job.per_task = (oro_topn*)calloc((size_t)(n_cand > 0 ? n_cand : 1), sizeof(oro_topn));
+  pthread_t* tids = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)threads);
+  for (int i = 0; i < threads; i++) pthread_create(&tids[i], NULL, faithful_worker, &job);
+  for (int i = 0; i < threads; i++) pthread_join(tids[i], NULL);
+  size_t n_all = 0;
+  oro_pair* all = (oro_pair*)malloc(sizeof(oro_pair) * (size_t)(n_cand > 0 ? n_cand : 1) * (size_t)(how_many > 0 ? how_many : 1));
+  for (int t = 0; t < n_cand; t++) {
+    if (!job.per_task[t].heap) continue;
+    memcpy(all + n_all, job.per_task[t].heap, sizeof(oro_pair) * (size_t)job.per_task[t].size);
+    n_all += (size_t)job.per_task[t].size;
+    free(job.per_task[t].heap);
+  }
+  qsort(all, n_all, sizeof(oro_pair), cmp_desc);
+  int n_out = n_all < (size_t)how_many ? (int)n_all : how_many;
+  for (int i = 0; i < n_out; i++) { out_rows[i] = all[i].row; out_scores[i] = all[i].score; }
+  free(all); free(job.per_task); free(tids); free(known.ids); free(known.hashes);
   return n_out;
 }

@@ -139,3 +139,31 @@ def test_recommend_matches_oracle_with_device_resident_exclusions(lsh):
     assert ic.tolist() == want.tolist()
     assert m.known_counts(ob.X, n_users).tolist() == [len(s) for s in known]
     m.close()
+
+
+def test_config_c1_recommend_parity():
+    """BASELINE.json configs[0] -- the reference's own CPU-runnable case: 100 k users x 100 k items,
+    50 features, /recommend howMany=10, LSH sample-rate 1.0, Poisson(20) known items per user
+    (LoadTestALSModelFactory.java:38-51, 62-95).  Every sampled user's list must equal the oracle's,
+    scores bit for bit."""
+    n_users = n_items = 100_000
+    f, hm = 50, 10
+    y = random_model(n_items, f, 0xB2000080)
+    x = random_model(n_users, f, 0xB2000081)
+    hashes, bits = ob.lsh_plan(1.0, 8)  # sample-rate 1.0: every partition is a candidate
+    hv = random_hash_vectors(hashes, f, 0xB2000082)
+    m = ob.Model(f, hash_vectors=hv, max_bits_differing=bits)
+    m.upsert(ob.Y, np.arange(n_items, dtype=np.int32), y)
+    m.upsert(ob.X, np.arange(n_users, dtype=np.int32), x)
+    rng = np.random.default_rng(0xB2000083)
+    counts = rng.poisson(20, n_users)
+    flat = rng.integers(0, n_items, int(counts.sum())).astype(np.int32)
+    begin = np.concatenate([[0], np.cumsum(counts)])
+    m.known_items_add(np.arange(n_users), [flat[begin[u]:begin[u + 1]] for u in range(n_users)])
+    for u in rng.choice(n_users, 200, replace=False):
+        known = np.unique(flat[begin[u]:begin[u + 1]])
+        want_rows, want_scores = oracle.topn(ob.DOT, x[u], y, hm, excluded=known)
+        rows, scores = m.recommend(int(u), hm)
+        assert rows.tolist() == want_rows.tolist(), u
+        assert scores.tobytes() == want_scores.tobytes(), u
+    m.close()

@@ -190,3 +190,26 @@ def test_numpy_cross_check():
     assert list(rows) == list(order) and np.array_equal(scores, acc[order])
     r2, s2 = oracle.topn_mt(oracle.DOT, q, y, 10, threads=4)
     assert list(r2) == list(rows) and np.array_equal(s2, scores)
+
+
+def test_faithful_layout_arm_agrees_with_the_row_ordered_oracle():
+    """The "faithful" CPU-baseline arm (String-keyed partition maps, String-set predicate, task per
+    partition) returns what the plain restatement returns -- with and without LSH candidates."""
+    from als_harness import random_hash_vectors, random_model
+    y = random_model(30000, 24, 0xB2000070)
+    hv = random_hash_vectors(3, 24, 0xB2000071)
+    part = oracle.lsh_index_rows(hv, y)
+    fm = oracle.FaithfulModel(y, part, 8)
+    rng = np.random.default_rng(0xB2000072)
+    for i in range(6):
+        q = rng.standard_normal(24).astype(np.float32)
+        known = rng.integers(0, 30000, 25)
+        for kind in (oracle.DOT, oracle.COSINE):
+            r1, s1 = oracle.topn(kind, q, y, 10, excluded=np.unique(known))
+            r2, s2 = fm.topn(kind, q, 10, known_rows=known, threads=3)
+            assert r1.tolist() == r2.tolist() and s1.tobytes() == s2.tobytes()
+        cand = oracle.lsh_candidates(3, 1, oracle.lsh_index(hv, q))
+        r1, s1 = oracle.topn(oracle.DOT, q, y, 10, part=part, cand=cand)
+        r2, s2 = fm.topn(oracle.DOT, q, 10, cand=cand, threads=3)
+        assert r1.tolist() == r2.tolist() and s1.tobytes() == s2.tobytes()
+    fm.close()
