@@ -9,7 +9,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import torch.distributed as dist
 import oryx_b200 as ob
-from oryx_b200.sharded import ShardPlan, exchange_packed
+from oryx_b200.sharded import P2PShardedTopN, ShardPlan, exchange_packed
+
+EXCHANGE = os.environ.get("ORYX_BENCH_EXCHANGE", "p2p")  # "p2p": peer-memory exchange kernel; "nccl": all-gather + merge
 
 total = int(sys.argv[1]) if len(sys.argv) > 1 else 100_000_000
 F = int(sys.argv[2]) if len(sys.argv) > 2 else 256
@@ -23,7 +25,7 @@ lo, hi = plan.local_range(rank, total)
 n = hi - lo
 H, bits = ob.lsh_plan(0.3, 32)
 hv = np.random.default_rng(4).standard_normal((H, F), dtype=np.float32)
-m = ob.Model(F, hash_vectors=hv, max_bits_differing=bits, device=lr, capacity_hint=n)
+m = ob.Model(F, hash_vectors=hv, max_bits_differing=bits, device=lr, capacity_hint=n, reserved_sms=1 if world > 1 else 0)
 g = torch.Generator(device=dev); g.manual_seed(100 + rank)
 t0 = time.perf_counter()
 for off in range(0, n, 1_000_000):
@@ -40,8 +42,12 @@ m_rows = torch.zeros(HM, dtype=torch.int64, device=dev); m_scores = torch.zeros(
 NQ = 32
 d_q = torch.from_numpy(np.random.default_rng(9).standard_normal((NQ, F), dtype=np.float32)).to(dev)
 stream = torch.cuda.current_stream(dev)
+pipe = P2PShardedTopN(ob, m, dist, torch, plan, HM, dev) if (world > 1 and EXCHANGE == "p2p") else None
 
 def step(i):
+    if pipe is not None:
+        pipe.submit(ob.DOT, d_q[i % NQ].data_ptr())
+        return
     m.topn_device(ob.DOT, d_q[i % NQ].data_ptr(), HM, d_rec[HM * 8:].data_ptr(), d_rec.data_ptr(), d_rec[HM * 12:].data_ptr(), stream.cuda_stream)
     if world > 1:
         exchange_packed(dist, torch, plan, d_rec, g_rec)
@@ -61,13 +67,22 @@ def run(label):
     return ms / steps
 
 ms_uncompacted = run("uncompacted")
-t0 = time.perf_counter(); m.compact(ob.Y); t_compact = time.perf_counter() - t0
-ms_compacted = run("compacted")
+free_b, _ = torch.cuda.mem_get_info(dev)
+can_compact = free_b > n * F * 4 * 1.05   # compaction builds a second copy of the shard
+if world > 1:
+    t = torch.tensor([1 if can_compact else 0], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MIN); can_compact = bool(t.item())
+t_compact = 0.0
+if can_compact:
+    t0 = time.perf_counter(); m.compact(ob.Y); t_compact = time.perf_counter() - t0
+    ms_compacted = run("compacted")
+else:
+    ms_compacted = ms_uncompacted
 if rank == 0:
     frac = 37 / 256
     print(json.dumps({
         "config": f"{total} items x {F} f over {world} GPU(s), LSH sample-rate 0.3/32 cores ({H} hashes, {bits} bits -> 37 of 256 partitions), top-{HM}",
-        "items_per_gpu": n, "load_s_per_gpu": round(t_load, 1), "compact_s": round(t_compact, 1),
+        "exchange": ("peer-memory kernel" if pipe is not None else "NCCL all-gather + merge") if world > 1 else None,
+        "compacted": can_compact, "items_per_gpu": n, "load_s_per_gpu": round(t_load, 1), "compact_s": round(t_compact, 1),
         "ms_per_query_uncompacted": ms_uncompacted, "ms_per_query_compacted": ms_compacted,
         "qps": 1000.0 / ms_compacted, "nominal_item_scores_per_sec": total * 1000.0 / ms_compacted,
         "actual_item_scores_per_sec": frac * total * 1000.0 / ms_compacted,
