@@ -179,8 +179,15 @@ int ALSServingModel::itemRowFor(const std::string& item) {
   const int row = (int)row_item_.size();
   row_item_.push_back(item);
   item_has_vec_.push_back(0);
+  item_recent_.push_back(0);
+  item_part_.push_back(-1);
   item_row_.emplace(item, row);
   return row;
+}
+
+bool ALSServingModel::itemIsRecent(const std::string& item) const {
+  auto it = item_row_.find(item);
+  return it != item_row_.end() && item_recent_[(size_t)it->second];
 }
 
 int ALSServingModel::userRowFor(const std::string& user) {
@@ -257,7 +264,7 @@ void ALSServingModel::setItemVectors(const std::string* items, const float* vecs
       if (!item_has_vec_[(size_t)row]) {
         item_has_vec_[(size_t)row] = 1;
         n_item_vecs_++;
-        recent_items_.insert(items[i]);  // FeatureVectors.java:74-77
+        item_recent_[(size_t)row] = 1;  // FeatureVectors.java:74-77: ID was actually new
       }
       rows[i] = row;
     }
@@ -266,7 +273,7 @@ void ALSServingModel::setItemVectors(const std::string* items, const float* vecs
   check_status(oryx_items_upsert(h_, ORYX_Y, rows.data(), vecs, (int32_t)n, parts.data()));
   std::lock_guard<std::mutex> lk(mu_);
   for (size_t i = 0; i < n; i++) {
-    item_partition_[items[i]] = parts[i];
+    item_part_[(size_t)rows[i]] = parts[i];
     if (!expected_items_.empty()) expected_items_.erase(items[i]);
   }
   cached_yty_.reset();  // :182 cachedYTYSolver.set(null)
@@ -471,13 +478,13 @@ void ALSServingModel::retainRecentAndItemIDs(const std::vector<std::string>& ite
     for (size_t r = 0; r < row_item_.size(); r++) {
       if (!item_has_vec_[r]) continue;
       const std::string& id = row_item_[r];
-      if (keep.count(id) || recent_items_.count(id)) continue;
+      if (item_recent_[r] || keep.count(id)) continue;
       drop.push_back((int32_t)r);
       item_has_vec_[r] = 0;
       n_item_vecs_--;
-      item_partition_.erase(id);
+      item_part_[r] = -1;
     }
-    recent_items_.clear();
+    std::fill(item_recent_.begin(), item_recent_.end(), 0);
     expected_items_.clear();
     for (const auto& i : items) if (rowOf(i) < 0) expected_items_.insert(i);
     cached_yty_.reset();
@@ -496,7 +503,7 @@ void ALSServingModel::retainRecentAndKnownItems(const std::vector<std::string>& 
     for (auto& kv : known_items_) {
       auto& set = kv.second;
       for (auto it = set.begin(); it != set.end();)
-        it = (keepItems.count(*it) || recent_items_.count(*it)) ? std::next(it) : set.erase(it);
+        it = (keepItems.count(*it) || itemIsRecent(*it)) ? std::next(it) : set.erase(it);
     }
     // the same predicate as row masks for the device copy
     userMask.resize(row_user_.size());
@@ -504,7 +511,7 @@ void ALSServingModel::retainRecentAndKnownItems(const std::vector<std::string>& 
       userMask[r] = keepUsers.count(row_user_[r]) || recent_users_.count(row_user_[r]);
     itemMask.resize(row_item_.size());
     for (size_t r = 0; r < row_item_.size(); r++)
-      itemMask[r] = keepItems.count(row_item_[r]) || recent_items_.count(row_item_[r]);
+      itemMask[r] = item_recent_[r] || keepItems.count(row_item_[r]);
   }
   static const uint8_t none = 0;
   check_status(oryx_known_items_retain(h_, userMask.empty() ? &none : userMask.data(), (int32_t)userMask.size(),
@@ -537,8 +544,8 @@ int ALSServingModel::itemRow(const std::string& item) const {
 
 int ALSServingModel::partitionOf(const std::string& item) const {
   std::lock_guard<std::mutex> lk(mu_);
-  auto it = item_partition_.find(item);
-  return it == item_partition_.end() ? -1 : it->second;
+  auto it = item_row_.find(item);
+  return it == item_row_.end() ? -1 : item_part_[(size_t)it->second];
 }
 
 // ---------------------------------------------------------------- ALSSpeedModel

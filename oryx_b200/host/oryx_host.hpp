@@ -173,13 +173,15 @@ class ALSServingModel {
   std::unordered_map<std::string, int> item_row_;
   std::vector<std::string> row_item_;
   std::vector<uint8_t> item_has_vec_;
+  std::vector<uint8_t> item_recent_;   // by row: vector set since the last retainRecentAndItemIDs (FeatureVectors recentIDs)
+  std::vector<int32_t> item_part_;     // by row: LSH partition the device assigned
   int n_item_vecs_ = 0;
   std::unordered_map<std::string, int> user_row_;
   std::vector<std::string> row_user_;
-  std::unordered_map<std::string, int> item_partition_;
   std::unordered_map<std::string, std::unordered_set<std::string>> known_items_;
   std::unordered_set<std::string> expected_users_, expected_items_;
-  std::unordered_set<std::string> recent_users_, recent_items_;
+  std::unordered_set<std::string> recent_users_;
+  bool itemIsRecent(const std::string& item) const;
   std::shared_ptr<Solver> cached_yty_;
 };
 

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <fstream>
 #include <functional>
+#include <future>
 #include <limits>
 #include <sstream>
 #include <thread>
@@ -157,6 +158,77 @@ double tokenToDouble(const NumTok& t) {
   return std::strtod(tmp.c_str(), nullptr);
 }
 
+// One pass over a JSON number: grammar check and value together.  Clinger's fast path -- at most 19
+// significant digits collected into a 64-bit mantissa that fits 2^53, |decimal exponent| <= 22 -- gives
+// the correctly rounded binary64 with one multiplication or division by an exact power of ten; anything
+// else goes through from_chars on the token.  *integral tells "-0" (the Integer 0) from "-0.0".
+double readNumber(Cur& c, bool* integral) {
+  static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+  const char* const b = c.p;
+  const char* p = c.p;
+  const char* const e = c.e;
+  bool neg = false;
+  if (p < e && *p == '-') { neg = true; p++; }
+  if (p >= e) bad("truncated number");
+  uint64_t mant = 0;
+  int digits = 0;       // significant digits taken into mant
+  int dropped = 0;      // integer digits beyond the 19th (each scales by 10)
+  bool exact = true;    // false once a non-zero digit had to be dropped
+  int exp10 = 0;
+  *integral = true;
+  if (*p == '0') {
+    p++;
+    if (p < e && *p >= '0' && *p <= '9') bad("leading zeros not allowed");
+  } else if (*p >= '1' && *p <= '9') {
+    while (p < e && *p >= '0' && *p <= '9') {
+      if (digits < 19) { mant = mant * 10 + (uint64_t)(*p - '0'); digits++; }
+      else { dropped++; if (*p != '0') exact = false; }
+      p++;
+    }
+  } else {
+    bad("unexpected character in numeric value");
+  }
+  if (p < e && *p == '.') {
+    *integral = false;
+    p++;
+    if (p >= e || *p < '0' || *p > '9') bad("decimal point not followed by a digit");
+    while (p < e && *p >= '0' && *p <= '9') {
+      if (digits < 19) {
+        if (mant != 0 || *p != '0') { mant = mant * 10 + (uint64_t)(*p - '0'); digits++; }
+        exp10--;
+      } else if (*p != '0') {
+        exact = false;
+      }
+      p++;
+    }
+  }
+  exp10 += dropped;
+  if (p < e && (*p == 'e' || *p == 'E')) {
+    *integral = false;
+    p++;
+    bool eneg = false;
+    if (p < e && (*p == '+' || *p == '-')) { eneg = *p == '-'; p++; }
+    if (p >= e || *p < '0' || *p > '9') bad("exponent has no digits");
+    int ev = 0;
+    while (p < e && *p >= '0' && *p <= '9') {
+      if (ev < 100000) ev = ev * 10 + (*p - '0');
+      p++;
+    }
+    exp10 += eneg ? -ev : ev;
+  }
+  if (p < e && !(*p == ',' || *p == ']' || *p == '}' || *p == ' ' || *p == '\t' || *p == '\n' || *p == '\r'))
+    bad("unexpected character after numeric value");
+  c.p = p;
+  if (exact && mant <= (1ull << 53) && exp10 >= -22 && exp10 <= 22) {
+    double d = (double)mant;
+    d = exp10 < 0 ? d / kPow10[-exp10] : d * kPow10[exp10];
+    return neg ? -d : d;
+  }
+  NumTok t{b, p, *integral};
+  return tokenToDouble(t);
+}
+
 bool matchLiteral(Cur& c, const char* lit) {
   size_t n = std::strlen(lit);
   if ((size_t)(c.e - c.p) < n || std::memcmp(c.p, lit, n) != 0) return false;
@@ -260,9 +332,9 @@ void readFloatArray(Cur& c, std::vector<float>& out) {
     if (!c.more()) bad("unexpected end of input");
     char ch = *c.p;
     if (ch == '-' || (ch >= '0' && ch <= '9')) {
-      NumTok t = readNumberToken(c);
-      const double d = tokenToDouble(t);
-      out.push_back(t.integral && d == 0.0 ? 0.0f : (float)d);  // "-0" is the Integer 0, not -0.0
+      bool integral;
+      const double d = readNumber(c, &integral);
+      out.push_back(integral && d == 0.0 ? 0.0f : (float)d);  // "-0" is the Integer 0, not -0.0
     } else if (ch == '"') {
       readString(c, tmp);
       out.push_back(stringToFloat(tmp));
@@ -873,6 +945,12 @@ FeatureBatch parseFeatureMessages(const char* text, const int64_t* begin, int64_
   return mergeParts(parseParts(get, n, tagged, threads));
 }
 
+std::vector<FeatureBatch> parseFeatureMessageParts(const char* text, const int64_t* begin, int64_t n, bool tagged,
+                                                   int threads) {
+  auto get = [&](int64_t i) { return std::string_view(text + begin[i], (size_t)(begin[i + 1] - begin[i])); };
+  return parseParts(get, n, tagged, threads);
+}
+
 void parseFeatureMessage(std::string_view message, bool tagged, char* matrix, std::string* id,
                          std::vector<float>* vector, bool* hasOthers, std::vector<std::string>* others) {
   FeatureBatch b;
@@ -958,31 +1036,54 @@ void ALSServingModelManager::applyBatch(const FeatureBatch& b, char forceMatrix)
   }
 }
 
-void ALSServingModelManager::consumeUpdates(const char* text, const int64_t* begin, int64_t n) {
-  if (!model_) return;  // :73-75 no model to interpret with yet
-  for (int64_t lo = 0; lo < n; lo += maxBatchRows_) {
-    const int64_t hi = std::min(n, lo + maxBatchRows_);
-    auto get = [&](int64_t i) { return std::string_view(text + begin[lo + i], (size_t)(begin[lo + i + 1] - begin[lo + i])); };
-    auto parts = parseParts(get, hi - lo, /*tagged=*/true, parseThreads_);
-    for (auto& p : parts) {
-      applyBatch(p, 0);
-      if (p.firstBad >= 0) throw BadMessage("Bad message #" + std::to_string(lo + p.firstBad) + ": " + p.firstBadWhy);
+namespace {
+// Parses sub-batch i+1 on the worker threads while the caller applies sub-batch i (bookkeeping and the
+// device upsert are serial: one updater).
+template <typename Apply>
+void pipelinedParse(const char* text, const int64_t* begin, int64_t n, bool tagged, int threads, int64_t maxBatchRows,
+                    Apply apply) {
+  auto parseRange = [=](int64_t lo) {
+    const int64_t hi = std::min(n, lo + maxBatchRows);
+    return parseFeatureMessageParts(text, begin + lo, hi - lo, tagged, threads);
+  };
+  if (n <= 0) return;
+  std::future<std::vector<FeatureBatch>> next = std::async(std::launch::async, parseRange, (int64_t)0);
+  for (int64_t lo = 0; lo < n; lo += maxBatchRows) {
+    std::vector<FeatureBatch> parts = next.get();
+    if (lo + maxBatchRows < n) next = std::async(std::launch::async, parseRange, lo + maxBatchRows);
+    try {
+      apply(parts, lo);
+    } catch (...) {
+      if (next.valid()) next.wait();  // do not leave a parse running over the caller's buffers
+      throw;
     }
   }
+}
+}  // namespace
+
+void ALSServingModelManager::consumeUpdates(const char* text, const int64_t* begin, int64_t n) {
+  if (!model_) return;  // :73-75 no model to interpret with yet
+  pipelinedParse(text, begin, n, /*tagged=*/true, parseThreads_, maxBatchRows_,
+                 [&](std::vector<FeatureBatch>& parts, int64_t lo) {
+                   for (auto& p : parts) {
+                     applyBatch(p, 0);
+                     if (p.firstBad >= 0)
+                       throw BadMessage("Bad message #" + std::to_string(lo + p.firstBad) + ": " + p.firstBadWhy);
+                   }
+                 });
 }
 
 void ALSServingModelManager::loadFeatureLines(char matrix, const char* text, const int64_t* begin, int64_t n) {
   if (!model_) throw std::logic_error("no model: a MODEL message must come first");
   if (matrix != 'X' && matrix != 'Y') throw std::invalid_argument("matrix must be 'X' or 'Y'");
-  for (int64_t lo = 0; lo < n; lo += maxBatchRows_) {
-    const int64_t hi = std::min(n, lo + maxBatchRows_);
-    auto get = [&](int64_t i) { return std::string_view(text + begin[lo + i], (size_t)(begin[lo + i + 1] - begin[lo + i])); };
-    auto parts = parseParts(get, hi - lo, /*tagged=*/false, parseThreads_);
-    for (auto& p : parts) {
-      applyBatch(p, matrix);
-      if (p.firstBad >= 0) throw BadMessage("Bad line #" + std::to_string(lo + p.firstBad) + ": " + p.firstBadWhy);
-    }
-  }
+  pipelinedParse(text, begin, n, /*tagged=*/false, parseThreads_, maxBatchRows_,
+                 [&](std::vector<FeatureBatch>& parts, int64_t lo) {
+                   for (auto& p : parts) {
+                     applyBatch(p, matrix);
+                     if (p.firstBad >= 0)
+                       throw BadMessage("Bad line #" + std::to_string(lo + p.firstBad) + ": " + p.firstBadWhy);
+                   }
+                 });
 }
 
 namespace {

@@ -87,6 +87,10 @@ struct FeatureBatch {
 // Messages after the first malformed one are not reported (consume() stops there, as the reference's
 // loop does when readJSON throws).
 FeatureBatch parseFeatureMessages(const char* text, const int64_t* begin, int64_t n, bool tagged, int threads = 0);
+// The same without the final concatenation: one batch per parsing thread, in message order (what the
+// managers consume; avoids a serial copy of every vector).
+std::vector<FeatureBatch> parseFeatureMessageParts(const char* text, const int64_t* begin, int64_t n, bool tagged,
+                                                   int threads = 0);
 // One message; throws BadMessage.
 void parseFeatureMessage(std::string_view message, bool tagged, char* matrix, std::string* id,
                          std::vector<float>* vector, bool* hasOthers, std::vector<std::string>* others);

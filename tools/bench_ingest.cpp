@@ -57,8 +57,7 @@ int main(int argc, char** argv) {
   int64_t parsed_rows = 0;
   for (int64_t lo = 0; lo < rows; lo += 1 << 20) {
     const int64_t n = std::min<int64_t>(rows - lo, 1 << 20);
-    FeatureBatch b = parseFeatureMessages(text.data(), begin.data() + lo, n, true, threads);
-    parsed_rows += (int64_t)b.size();
+    for (auto& part : parseFeatureMessageParts(text.data(), begin.data() + lo, n, true, threads)) parsed_rows += (int64_t)part.size();
   }
   auto t1 = Clock::now();
 
