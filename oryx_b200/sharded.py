@@ -179,6 +179,11 @@ class P2PShardedTopN:
     def merged(self, i: int = 0):
         return self.m_rows, self.m_scores, self.m_n
 
+    def check(self):
+        """Synchronises and raises if the last exchange timed out waiting for a peer (count == -2)."""
+        if int(self.m_n.item()) == -2:
+            raise RuntimeError("a peer did not deliver its record within ORYX_EXCHANGE_TIMEOUT_MS")
+
     def close(self):
         self.x.close()
 
