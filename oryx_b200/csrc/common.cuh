@@ -247,7 +247,7 @@ int32_t ensure_excl(QueryCtx* c, int32_t n);
 int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits);
 // Hash n packed rows (row stride `stride` floats) on `stream`; writes int32 partition per row.
 int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int stride, int32_t* d_out,
-                             cudaStream_t stream);
+                             cudaStream_t stream, int32_t* d_zero_counter = nullptr, bool early_start = false);
 int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream);
 int32_t lsh_candidates_device(Model* m, const int32_t* d_main_index, int32_t* d_out, int32_t* d_out_n,
                               cudaStream_t stream);

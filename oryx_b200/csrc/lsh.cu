@@ -28,12 +28,14 @@ int64_t binom(int n, int k) {
 // => conflict-free).  Hashes are processed four at a time for ILP across the dependent DADD chains.
 __global__ void lsh_hash_kernel(const float* __restrict__ rows, int64_t n, int64_t stride, int features,
                                 const float* __restrict__ hash_vectors, int hv_stride, int num_hashes,
-                                int tile_rows, int32_t* __restrict__ out) {
+                                int tile_rows, int32_t* __restrict__ out, int32_t* __restrict__ zero_counter) {
   extern __shared__ float smem[];
   float* s_hv = smem;                                  // [num_hashes x features]
   float* s_rows = smem + (size_t)num_hashes * features;  // [tile_rows x (features+1)]
   const int ld = features + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  // a query's hashing kernel also resets the count of its work list (built by the next kernel)
+  if (zero_counter && blockIdx.x == 0 && threadIdx.x == 0) *zero_counter = 0;
 
   for (int e = threadIdx.x; e < num_hashes * features; e += blockDim.x) {
     int h = e / features, j = e - h * features;
@@ -164,12 +166,13 @@ int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits) {
 }
 
 int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int stride, int32_t* d_out,
-                             cudaStream_t stream) {
+                             cudaStream_t stream, int32_t* d_zero_counter, bool early_start) {
   if (n <= 0) return ORYX_OK;
   const int F = m->cfg.features;
   const int H = m->num_hashes;
   if (H == 0) {
     ORYX_CUDA(cudaMemsetAsync(d_out, 0, (size_t)n * sizeof(int32_t), stream));
+    if (d_zero_counter) ORYX_CUDA(cudaMemsetAsync(d_zero_counter, 0, sizeof(int32_t), stream));
     return ORYX_OK;
   }
   size_t hv_bytes = (size_t)H * F * sizeof(float);
@@ -184,17 +187,28 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
   ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(lsh_hash_kernel), smem));
   int64_t tiles = (n + tile_rows - 1) / tile_rows;
   int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
-  lsh_hash_kernel<<<grid, tile_rows, smem, stream>>>(d_rows, n, stride, F, m->d_hash_vectors,
-                                                    m->store[ORYX_Y].fpad, H, tile_rows, d_out);
+  // `early_start`: the kernel depends on nothing the stream's previous kernels write (a query vector
+  // and the hash vectors), so it may begin as soon as they release their programmatic dependents.
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)tile_rows);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = early_start ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  ORYX_CUDA(cudaLaunchKernelEx(&cfg, lsh_hash_kernel, d_rows, n, (int64_t)stride, F, (const float*)m->d_hash_vectors,
+                               m->store[ORYX_Y].fpad, H, tile_rows, d_out, d_zero_counter));
   m->launches++;
-  ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }
 
+// The count d_worklist[0] must already be zero (the query's hashing kernel resets it).
 int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream) {
   Store* s = &m->store[ORYX_Y];
   const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
-  ORYX_CUDA(cudaMemsetAsync(d_worklist, 0, sizeof(int32_t), stream));
   const int threads = 256;
   const int grid = (int)std::min<int64_t>((n_blocks + threads - 1) / threads, (int64_t)m->num_sms * 4);
   lsh_worklist_kernel<<<grid, threads, 0, stream>>>(s->d_block_part, n_blocks, d_main_index, m->max_bits, d_worklist);

@@ -205,6 +205,9 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
   constexpr int RPI = 32 / G;       // rows covered by one load instruction of a warp
   constexpr int RPT = RPI * U;      // rows per warp tile
 
+  // A scan released early must still see what its immediate predecessors wrote: the exclusion list
+  // (a device-resident known-items list is prepared by a kernel) and, below, the LSH index / work list.
+  if (LSH || p.n_excl > 0) pdl_wait_primary();
   const int32_t* excl = p.excl_in_smem ? s_excl_buf : p.excl;
   if (p.excl_in_smem) {
     for (int i = tid; i < p.n_excl; i += T) s_excl_buf[i] = __ldg(p.excl + i);
@@ -792,8 +795,8 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   }
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;  // LSH.java:160-162: all partitions otherwise
   if (lsh) {
-    ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream));
-    if (ctx->scratch_sets == 2) {  // a context that owns memory: list the candidate blocks
+    const bool owns = ctx->scratch_sets == 2;  // a context that owns memory: list the candidate blocks
+    if (owns) {
       const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
       if (ctx->worklist_cap < n_blocks + 1) {
         cudaFree(ctx->d_worklist);
@@ -803,8 +806,13 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
         ORYX_CUDA(cudaMalloc(&ctx->d_worklist, (size_t)cap * sizeof(int32_t)));
         ctx->worklist_cap = cap;
       }
-      ORYX_TRY(lsh_worklist_device(m, ctx->d_main_index, ctx->d_worklist, stream));
     }
+    // Hashing the query depends on nothing earlier in the stream, so it starts while the previous
+    // query's finishing kernel still runs; the previous scan (the only reader of main_index and of the
+    // work list) has completed by then, because the finishing kernel that releases us waits for it.
+    ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream,
+                                  owns ? ctx->d_worklist : nullptr, owns));
+    if (owns) ORYX_TRY(lsh_worklist_device(m, ctx->d_main_index, ctx->d_worklist, stream));
   }
   ScanParams p{};
   p.y = reinterpret_cast<const float4*>(s->d_vec);
@@ -824,9 +832,9 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   p.max_bits = m->max_bits;
   p.main_index = ctx->d_main_index;
   // Two scratch sets alternate so that this query's scan may start while the previous query's
-  // finishing kernel (which reads the other set) is still running.  An LSH-filtered query runs a
-  // hashing kernel first, which serialises behind the previous query anyway.
-  const bool overlap = ctx->scratch_sets == 2 && !lsh;
+  // finishing kernel (which reads the other set) is still running (an LSH-filtered scan waits, on the
+  // device, for the kernels that hash its query and list its candidate blocks).
+  const bool overlap = ctx->scratch_sets == 2;
   const int set = ctx->scratch_sets == 2 ? (ctx->flip ^= 1) : 0;
   p.cand = ctx->d_cand + (size_t)set * kMaxGrid * kMaxK;
   p.list_max = ctx->d_list_max + (size_t)set * kMaxGrid;
