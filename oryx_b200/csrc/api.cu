@@ -615,6 +615,68 @@ int32_t oryx_topn_batch(oryx_model* mh, int32_t kind, const float* queries, int3
   return rc;
 }
 
+int32_t oryx_recommend_batch(oryx_model* mh, const int32_t* user_rows, int32_t n_users, int32_t how_many,
+                             int32_t consider_known_items, int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  ORYX_ARG(mh && out_rows && out_scores && out_n, "null argument");
+  ORYX_ARG(n_users >= 0, "n_users must be >= 0");
+  if (n_users == 0) return ORYX_OK;
+  ORYX_ARG(user_rows, "null user_rows");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc = ORYX_OK;
+  {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    Store* x = &m->store[ORYX_X];
+    Store* y = &m->store[ORYX_Y];
+    std::vector<int32_t> qslots((size_t)n_users);
+    for (int32_t i = 0; i < n_users; i++) {
+      const int32_t r = user_rows[i];
+      qslots[(size_t)i] = (r >= 0 && (size_t)r < x->row2slot.size()) ? x->row2slot[(size_t)r] : -1;
+    }
+    bool batched = false;
+    if (batch_topn_supported(m, n_users)) {
+      // the allowed-predicate of every user as sorted slots, CSR per query, from the authoritative lists
+      std::vector<int32_t> eo, es;
+      if (!consider_known_items) {
+        eo.assign((size_t)n_users + 1, 0);
+        for (int32_t i = 0; i < n_users; i++) {
+          const int32_t r = user_rows[i];
+          const size_t begin = es.size();
+          if (r >= 0 && (size_t)r < m->known.lists.size()) {
+            for (int32_t item : m->known.lists[(size_t)r]) {
+              if ((size_t)item < y->row2slot.size() && y->row2slot[(size_t)item] >= 0) es.push_back(y->row2slot[(size_t)item]);
+            }
+          }
+          std::sort(es.begin() + (std::ptrdiff_t)begin, es.end());
+          eo[(size_t)i + 1] = (int32_t)es.size();
+        }
+        if (es.empty()) eo.clear();
+      }
+      rc = batch_topn_run(m, ORYX_DOT, nullptr, n_users, how_many, eo.empty() ? nullptr : eo.data(),
+                          es.empty() ? nullptr : es.data(), out_rows, out_scores, out_n, c->stream, &m->last_batch,
+                          qslots.data(), ORYX_X);
+      batched = rc == ORYX_OK;
+      if (rc == ORYX_E_NOMEM) rc = ORYX_OK;  // not enough scratch for the tensor-core path: answer one by one
+    }
+    for (int32_t i = 0; i < n_users && rc == ORYX_OK; i++) {
+      if (qslots[(size_t)i] < 0) { out_n[i] = -1; continue; }  // no such user (the reference's 404)
+      if (batched && out_n[i] >= 0) continue;                  // -1 marks a query the batched path handed back
+      const float* d_query = x->d_vec + (int64_t)qslots[(size_t)i] * x->fpad;
+      int32_t n_excl = 0;
+      if (!consider_known_items) rc = known_exclusions_device(m, c, user_rows[i], &n_excl, c->stream);
+      if (rc == ORYX_OK)
+        rc = run_topn_staged(m, c, ORYX_DOT, d_query, n_excl, how_many, out_rows + (size_t)i * how_many,
+                             out_scores + (size_t)i * how_many, out_n + i);
+    }
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
+  ctx_release(m, c);
+  return rc;
+}
+
 // Development aid (not in the public header): phase timings (ms) and flops of the last tensor-core batch.
 int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {  // out5 holds 7 doubles
   Model* m = reinterpret_cast<Model*>(mh);

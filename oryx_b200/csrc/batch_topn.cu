@@ -152,6 +152,16 @@ __global__ void convert_y_kernel(const float* __restrict__ y, int64_t n, int fpa
   if (lane == 0) atomicMax(max_norm_bits, __float_as_uint(local_max));
 }
 
+// One warp per query: the row in slots[i] of a store (zeros for a negative slot) -> packed [nq x f].
+__global__ void gather_queries_kernel(const float* __restrict__ vec, int fpad, int f, const int32_t* __restrict__ slots,
+                                      int nq, float* __restrict__ out) {
+  const int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int lane = threadIdx.x & 31;
+  if (w >= nq) return;
+  const int32_t slot = slots[w];
+  for (int j = lane; j < f; j += 32) out[(size_t)w * f + j] = slot >= 0 ? vec[(int64_t)slot * fpad + j] : 0.f;
+}
+
 // Q fp32 [nq x features] -> bf16 [nq_pad x kpad] (zero padded rows and columns), and ||q|| per row.
 __global__ void convert_q_kernel(const float* __restrict__ q, int nq, int nq_pad, int features, int kpad,
                                  __nv_bfloat16* __restrict__ out, float* __restrict__ qnorm) {
@@ -778,7 +788,7 @@ bool batch_topn_supported(Model* m, int nq) {
 // answer unbatched (candidate overflow; pathological score distributions only).
 int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
                        const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
-                       cudaStream_t st, BatchTimings* timings) {
+                       cudaStream_t st, BatchTimings* timings, const int32_t* query_slots, int query_store) {
   Store* s = &m->store[ORYX_Y];
   const int F = s->features, fpad = s->fpad;
   const int kpad = round_up(F, BK), nch = kpad / BK;
@@ -824,7 +834,18 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   for (auto& e : ev) ORYX_CUDA(cudaEventCreate(&e));
   struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 5; i++) cudaEventDestroy(e[i]); } } evg{ev};
 
-  ORYX_CUDA(cudaMemcpyAsync(d_q.p, queries, (size_t)nq * F * 4, cudaMemcpyHostToDevice, st));
+  if (query_slots) {
+    // the queries are rows of a device-resident store: gather them, nothing but slot numbers is uploaded
+    void* d_qs = nullptr;
+    ORYX_TRY(scratch(bs, 12, (size_t)nq * 4, &d_qs));
+    ORYX_CUDA(cudaMemcpyAsync(d_qs, query_slots, (size_t)nq * 4, cudaMemcpyHostToDevice, st));
+    const Store* qs = &m->store[query_store];
+    gather_queries_kernel<<<(unsigned)(((int64_t)nq * 32 + 255) / 256), 256, 0, st>>>(
+        qs->d_vec, qs->fpad, F, (const int32_t*)d_qs, nq, (float*)d_q.p);
+    ORYX_CUDA(cudaGetLastError());
+  } else {
+    ORYX_CUDA(cudaMemcpyAsync(d_q.p, queries, (size_t)nq * F * 4, cudaMemcpyHostToDevice, st));
+  }
   ORYX_CUDA(cudaEventRecord(ev[0], st));
   if (!y_fresh) {
     ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 4, st));

@@ -178,8 +178,8 @@ struct BatchTimings {
 // Grow-only device scratch of the tensor-core batch path, kept across calls (one batch at a time).
 struct BatchScratch {
   std::mutex mu;
-  void* buf[12] = {nullptr};
-  size_t bytes[12] = {0};
+  void* buf[14] = {nullptr};
+  size_t bytes[14] = {0};
   uint64_t y_version = ~0ull;  // store version the bf16 shadow of Y was converted from
   int y_normalized = -1;       // ... and whether it holds y/||y|| (cosine) or y (dot)
   int64_t y_rows = -1;
@@ -283,9 +283,12 @@ int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_
 
 // batch_topn.cu
 bool batch_topn_supported(Model* m, int nq);
+// `queries` is a HOST [nq x features] array -- or, when `query_slots` is given, ignored: query i is then
+// the row in slot query_slots[i] of store `query_store` (a negative slot gives a zero query).
 int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
                        const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
-                       cudaStream_t st, BatchTimings* timings);
+                       cudaStream_t st, BatchTimings* timings, const int32_t* query_slots = nullptr,
+                       int query_store = ORYX_X);
 
 // gram.cu
 int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);

@@ -75,6 +75,7 @@ SIGNATURES = {
     "oryx_known_items_retain": [C.c_void_p, _u8p, C.c_int32, _u8p, C.c_int32],
     "oryx_known_counts": [C.c_void_p, C.c_int32, _i32p, C.c_int32],
     "oryx_recommend": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _i32p],
+    "oryx_recommend_batch": [C.c_void_p, _i32p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p],
     "oryx_topn_batch": [C.c_void_p, C.c_int32, _f32p, C.c_int32, C.c_int32, _i32p, _i32p, _i32p, _f64p, _i32p],
     "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
     "oryx_scores_rows": [C.c_void_p, C.c_int32, _f32p, _i32p, C.c_int32, _f64p, _u8p],
@@ -276,6 +277,17 @@ class Model:
         if not found.value:
             return None
         return rows[:n.value].copy(), scores[:n.value].copy()
+
+    def recommend_batch(self, user_rows, how_many: int, consider_known_items: bool = False):
+        """-> (rows [n x how_many], scores [n x how_many], counts [n]); counts[i] == -1: no such user."""
+        users = np.ascontiguousarray(user_rows, dtype=np.int32)
+        n = users.size
+        rows = np.zeros((max(n, 1), how_many), dtype=np.int32)
+        scores = np.zeros((max(n, 1), how_many), dtype=np.float64)
+        cnt = np.zeros(max(n, 1), dtype=np.int32)
+        _check(lib().oryx_recommend_batch(self._h, _ptr(users, C.c_int32), n, how_many, int(consider_known_items),
+                                          _ptr(rows, C.c_int32), _ptr(scores, C.c_double), _ptr(cnt, C.c_int32)))
+        return rows[:n], scores[:n], cnt[:n]
 
     def topn_batch(self, kind: int, queries, how_many: int, excluded_lists=None):
         q = _f32(queries).reshape(-1, self.features)

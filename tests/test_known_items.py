@@ -167,3 +167,35 @@ def test_config_c1_recommend_parity():
         assert rows.tolist() == want_rows.tolist(), u
         assert scores.tobytes() == want_scores.tobytes(), u
     m.close()
+
+
+def test_recommend_batch_equals_one_at_a_time():
+    """oryx_recommend_batch (queries gathered from the device X store, scored on the tensor cores, each
+    against its own device-resident known items) returns exactly what oryx_recommend returns user by
+    user -- including users without a vector and users whose known items were removed from Y."""
+    n_items, n_users, f, hm = 70000, 400, 64, 20
+    y = random_model(n_items, f, 0xB20000A0)
+    x = random_model(n_users, f, 0xB20000A1)
+    m = ob.Model(f)
+    m.upsert(ob.Y, np.arange(n_items, dtype=np.int32), y)
+    m.upsert(ob.X, np.arange(n_users, dtype=np.int32), x)
+    rng = np.random.default_rng(0xB20000A2)
+    lists = []
+    for u in range(n_users):
+        top = np.argsort(-(y[:3000] @ x[u]))[: int(rng.integers(0, 15))]
+        lists.append(np.concatenate([top, rng.integers(0, n_items, int(rng.poisson(20)))]).astype(np.int32))
+    m.known_items_add(np.arange(n_users), lists)
+    m.remove(ob.Y, rng.choice(n_items, 500, replace=False).astype(np.int32))
+    m.remove(ob.X, np.array([5, 77], np.int32))
+    users = np.concatenate([rng.permutation(n_users)[:300], [n_users + 9, -1]]).astype(np.int32)
+    for consider in (False, True):
+        rows, scores, cnt = m.recommend_batch(users, hm, consider_known_items=consider)
+        for i, u in enumerate(users):
+            one = m.recommend(int(u), hm, consider_known_items=consider)
+            if one is None:
+                assert cnt[i] == -1, u
+                continue
+            assert cnt[i] == len(one[0])
+            assert rows[i, :cnt[i]].tolist() == one[0].tolist(), u
+            assert scores[i, :cnt[i]].tobytes() == one[1].tobytes(), u
+    m.close()
