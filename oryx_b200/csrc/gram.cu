@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(256) gram_exact_kernel(const float* __restrict
 // kernel improves with n: ~1e-8 relative at 7e4 rows, ~1e-9 at 1e7.  128 x 128 output block per CTA, 8 x 8 per thread.
 constexpr int kFastTile = 128;
 constexpr int kFastKC = 16;
+constexpr int kFastStage = kFastKC * 32 / 256;  // float4 of A (and of B) each thread stages per step
 constexpr int kFlushRows = 64;
 
 __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restrict__ vec,
@@ -112,20 +113,40 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
 
-  // each thread stages 2 float4 of A and 2 of B per step: row k = e / 32, float4 column = e % 32
-  auto stage = [&](int buf, int64_t r0) {
+  // each thread stages kFastStage float4 of A and of B per step: row k = e / 32, float4 column = e % 32.
+  // fetch() only issues the global loads (into registers; the tombstone test and the row load are
+  // independent, one latency instead of two), commit() stores them to shared memory after the math of
+  // the current step -- so the loads are in flight for a whole step instead of stalling it.
+  float4 fa[kFastStage], fb[kFastStage];
+  int32_t fr[kFastStage];
+  bool fin[kFastStage];
+  auto fetch = [&](int64_t r0) {
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
+    for (int h = 0; h < kFastStage; h++) {
       const int e = tid + h * 256;
       const int k = e >> 5, c4 = e & 31;
       const int64_t row = r0 + k;
-      const bool ok = row < row_end && __ldg(slot_row + row) >= 0;  // tombstones are NaN-filled: skip
+      fin[h] = row < row_end;
       const int ca = bi * kFastTile + c4 * 4, cb = bj * kFastTile + c4 * 4;
-      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-      if (ok && ca < fpad) a = __ldg(reinterpret_cast<const float4*>(vec + row * fpad + ca));
-      if (ok && cb < fpad) b = __ldg(reinterpret_cast<const float4*>(vec + row * fpad + cb));
-      *reinterpret_cast<float4*>(As + ((size_t)buf * kFastKC + k) * kFastTile + c4 * 4) = a;
-      *reinterpret_cast<float4*>(Bs + ((size_t)buf * kFastKC + k) * kFastTile + c4 * 4) = b;
+      fa[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+      fb[h] = fa[h];
+      fr[h] = -1;
+      if (fin[h]) {
+        fr[h] = __ldg(slot_row + row);
+        if (ca < fpad) fa[h] = __ldg(reinterpret_cast<const float4*>(vec + row * fpad + ca));
+        if (cb < fpad) fb[h] = __ldg(reinterpret_cast<const float4*>(vec + row * fpad + cb));
+      }
+    }
+  };
+  auto commit = [&](int buf) {
+#pragma unroll
+    for (int h = 0; h < kFastStage; h++) {
+      const int e = tid + h * 256;
+      const int k = e >> 5, c4 = e & 31;
+      const bool ok = fin[h] && fr[h] >= 0;  // tombstones are NaN-filled: contribute zeros
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(As + ((size_t)buf * kFastKC + k) * kFastTile + c4 * 4) = ok ? fa[h] : z;
+      *reinterpret_cast<float4*>(Bs + ((size_t)buf * kFastKC + k) * kFastTile + c4 * 4) = ok ? fb[h] : z;
     }
   };
   auto flush = [&]() {
@@ -141,10 +162,11 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
 
   __syncthreads();
   int buf = 0, since_flush = 0;
-  if (row_begin < row_end) stage(0, row_begin);
+  if (row_begin < row_end) { fetch(row_begin); commit(0); }
   __syncthreads();
   for (int64_t r0 = row_begin; r0 < row_end; r0 += kFastKC) {
-    if (r0 + kFastKC < row_end) stage(buf ^ 1, r0 + kFastKC);  // prefetch the next step into the other buffer
+    const bool more = r0 + kFastKC < row_end;
+    if (more) fetch(r0 + kFastKC);  // the next step's loads fly during this step's math
     const float* a_s = As + (size_t)buf * kFastKC * kFastTile;
     const float* b_s = Bs + (size_t)buf * kFastKC * kFastTile;
 #pragma unroll
@@ -161,6 +183,7 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
+    if (more) commit(buf ^ 1);
     since_flush += kFastKC;
     if (since_flush >= kFlushRows) { flush(); since_flush = 0; }
     __syncthreads();
