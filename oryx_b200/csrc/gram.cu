@@ -154,7 +154,10 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
     for (int i = 0; i < 8; i++)
 #pragma unroll
       for (int j = 0; j < 8; j++) {
-        double* d = acc64 + (size_t)((i < 4 ? 0 : 64) + ty * 4 + (i & 3)) * kFastTile + (j < 4 ? 0 : 64) + tx * 4 + (j & 3);
+        // accumulator (i, j) of thread tid lives at [(i*8+j)][tid]: a warp touches 32 consecutive
+        // doubles, conflict-free (a [row][col] layout made this read-modify-write a 4-way bank conflict
+        // and the largest user of shared-memory bandwidth in the kernel)
+        double* d = acc64 + (size_t)(i * 8 + j) * 256 + tid;
         *d += (double)acc[i][j];
         acc[i][j] = 0.f;
       }
@@ -192,7 +195,10 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   flush();
   __syncthreads();
   for (int e = tid; e < kFastTile * kFastTile; e += 256) {
-    const int i = e / kFastTile, j = e - i * kFastTile;
+    // e = (i*8+j)*256 + owner thread  ->  the tile coordinates that thread's accumulator (i, j) stands for
+    const int ij = e >> 8, owner = e & 255;
+    const int ai = ij >> 3, aj = ij & 7, otx = owner & 15, oty = owner >> 4;
+    const int i = (ai < 4 ? 0 : 64) + oty * 4 + (ai & 3), j = (aj < 4 ? 0 : 64) + otx * 4 + (aj & 3);
     const int r = bi * kFastTile + i, c = bj * kFastTile + j;
     if (r < features && c < features) {
       const double v = acc64[e];
