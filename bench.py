@@ -298,12 +298,18 @@ def run_ours(args):
     d_scores = d_rec[: HOW_MANY * 8].view(torch.float64)
     d_rows = d_rec[HOW_MANY * 8: HOW_MANY * 12].view(torch.int32)
     d_n = d_rec[HOW_MANY * 12: HOW_MANY * 12 + 4].view(torch.int32)
+    exchange = EXCHANGE
     if world > 1:
         from oryx_b200.sharded import P2PShardedTopN, PipelinedShardedTopN, ShardPlan, exchange_packed
         plan = ShardPlan(world, n_items)   # rank r owns global rows [r*n_items, (r+1)*n_items)
-        if EXCHANGE == "p2p":
-            pipe = P2PShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
-        else:
+        if exchange == "p2p":
+            try:
+                pipe = P2PShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
+            except RuntimeError as e:   # no peer access between these GPUs: every rank falls back together
+                if rank == 0:
+                    print(f"bench: {e}; using the NCCL exchange", file=sys.stderr)
+                exchange = "nccl"
+        if exchange != "p2p":
             pipe = PipelinedShardedTopN(ob, model, dist, torch, plan, HOW_MANY, dev)
         g_rec = torch.zeros(world * rec_bytes, dtype=torch.uint8, device=dev)
         m_rows = torch.zeros(HOW_MANY, dtype=torch.int64, device=dev)
@@ -321,11 +327,11 @@ def run_ours(args):
     def step_device(i: int):
         """One query with inputs resident in HBM, enqueued on torch's current stream."""
         nonlocal launches_extra
-        if world > 1 and (PIPELINE or EXCHANGE == "p2p"):
+        if world > 1 and (PIPELINE or exchange == "p2p"):
             # scan on this stream; the one exchange step (a 128-byte record per rank over NCCL / NVLink)
             # and the merge follow on a side stream while the next query's scan already runs
             pipe.submit(ob.DOT, d_q[i % N_QUERIES].data_ptr())
-            launches_extra += 0 if EXCHANGE == "p2p" else 1   # the NCCL path's merge kernel is launched from Python
+            launches_extra += 0 if exchange == "p2p" else 1   # the NCCL path's merge kernel is launched from Python
         elif world > 1:
             model.topn_device(ob.DOT, d_q[i % N_QUERIES].data_ptr(), HOW_MANY, d_rows.data_ptr(),
                               d_scores.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
@@ -394,7 +400,7 @@ def run_ours(args):
 
         def step_e2e(i):
             d_qe.copy_(h_q_pinned[i % N_QUERIES], non_blocking=True)
-            if EXCHANGE == "p2p":
+            if exchange == "p2p":
                 pipe.submit(ob.DOT, d_qe.data_ptr())
                 h_res_rows.copy_(pipe.m_rows, non_blocking=True)
                 h_res_scores.copy_(pipe.m_scores, non_blocking=True)
@@ -409,7 +415,7 @@ def run_ours(args):
 
         # the peer-memory exchange against the NCCL all-gather + merge on the same queries
         exchange_check = None
-        if EXCHANGE == "p2p":
+        if exchange == "p2p":
             exchange_check = True
             for i in range(4):
                 pipe.submit(ob.DOT, d_q[i].data_ptr())
@@ -526,7 +532,7 @@ def run_ours(args):
                        "l2_policy": f"inputs larger than L2 ({alg_bytes / 1e9:.2f} GB streamed per step vs 126 MB L2)",
                        "item_scores_per_sec": value * ITEMS_PER_GPU, "load_seconds": round(t_load, 2),
                        "parity_vs_oracle_full_size": parity,
-                       "exchange": (("peer-memory kernel (oryx_topn_sharded_device)" if EXCHANGE == "p2p"
+                       "exchange": (("peer-memory kernel (oryx_topn_sharded_device)" if exchange == "p2p"
                                      else "NCCL all-gather + merge kernel") if world > 1 else None),
                        "exchange_matches_nccl_path": exchange_check if world > 1 else None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -163,8 +163,17 @@ class P2PShardedTopN:
         self.x = ob.Exchange(index, plan.world, dist.get_rank(), how_many)
         handles = [None] * plan.world
         dist.all_gather_object(handles, self.x.handle())
-        self.x.connect(handles)
-        dist.barrier()  # nobody publishes before every inbox is mapped
+        failure = None
+        try:
+            self.x.connect(handles)
+        except Exception as e:  # noqa: BLE001 -- every rank must reach the vote below
+            failure = e
+        # nobody publishes before every inbox is mapped, and either all ranks use this path or none does
+        vote = torch.tensor([0 if failure else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(vote, op=dist.ReduceOp.MIN)
+        if int(vote.item()) == 0:
+            self.x.close()
+            raise RuntimeError(f"peer mapping of the exchange inboxes failed on at least one rank ({failure})")
         z = lambda n, dt: torch.zeros(n, dtype=dt, device=device)
         self.m_rows, self.m_scores, self.m_n = z(how_many, torch.int64), z(how_many, torch.float64), z(1, torch.int32)
 
