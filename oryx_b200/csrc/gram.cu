@@ -88,10 +88,11 @@ __global__ void __launch_bounds__(256) gram_exact_kernel(const float* __restrict
 // kernel improves with n: ~1e-8 relative at 7e4 rows, ~1e-9 at 1e7.  128 x 128 output block per CTA, 8 x 8 per thread.
 constexpr int kFastTile = 128;
 constexpr int kFastKC = 16;
-constexpr int kFastStage = kFastKC * 32 / 256;  // float4 of A (and of B) each thread stages per step
 constexpr int kFlushRows = 64;
 
-__global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restrict__ vec,
+// T threads: 256 (8 x 8 outputs per thread) or 512 (4 x 8; twice the warps to hide shared-memory latency).
+template <int T>
+__global__ void __launch_bounds__(T, 1) gram_fast_kernel(const float* __restrict__ vec,
                                                            const int32_t* __restrict__ slot_row, int64_t n_slots,
                                                            int fpad, int features, int nb, int64_t rows_per_chunk,
                                                            double* __restrict__ out) {
@@ -102,14 +103,17 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   int t = blockIdx.x, bi = 0;
   while (t >= nb - bi) { t -= nb - bi; bi++; }
   const int bj = bi + t;
+  constexpr int RH = T == 256 ? 2 : 1;  // 64-row halves of the tile a thread covers
+  constexpr int RI = 4 * RH;            // output rows per thread
+  constexpr int kFastStage = kFastKC * 32 / T;  // float4 of A (and of B) each thread stages per step
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int64_t row_begin = (int64_t)blockIdx.y * rows_per_chunk;
   const int64_t row_end = min(n_slots, row_begin + rows_per_chunk);
-  for (int e = tid; e < kFastTile * kFastTile; e += 256) acc64[e] = 0.0;
+  for (int e = tid; e < kFastTile * kFastTile; e += T) acc64[e] = 0.0;
 
-  float acc[8][8];
+  float acc[RI][8];
 #pragma unroll
-  for (int i = 0; i < 8; i++)
+  for (int i = 0; i < RI; i++)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
 
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   auto fetch = [&](int64_t r0) {
 #pragma unroll
     for (int h = 0; h < kFastStage; h++) {
-      const int e = tid + h * 256;
+      const int e = tid + h * T;
       const int k = e >> 5, c4 = e & 31;
       const int64_t row = r0 + k;
       fin[h] = row < row_end;
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   auto commit = [&](int buf) {
 #pragma unroll
     for (int h = 0; h < kFastStage; h++) {
-      const int e = tid + h * 256;
+      const int e = tid + h * T;
       const int k = e >> 5, c4 = e & 31;
       const bool ok = fin[h] && fr[h] >= 0;  // tombstones are NaN-filled: contribute zeros
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -151,13 +155,13 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   };
   auto flush = [&]() {
 #pragma unroll
-    for (int i = 0; i < 8; i++)
+    for (int i = 0; i < RI; i++)
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         // accumulator (i, j) of thread tid lives at [(i*8+j)][tid]: a warp touches 32 consecutive
         // doubles, conflict-free (a [row][col] layout made this read-modify-write a 4-way bank conflict
         // and the largest user of shared-memory bandwidth in the kernel)
-        double* d = acc64 + (size_t)(i * 8 + j) * 256 + tid;
+        double* d = acc64 + (size_t)(i * 8 + j) * T + tid;
         *d += (double)acc[i][j];
         acc[i][j] = 0.f;
       }
@@ -176,13 +180,13 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
     for (int k = 0; k < kFastKC; k++) {
       // lanes read consecutive float4 (16-byte stride): conflict-free; second half 64 columns on
       const float4 a0 = *reinterpret_cast<const float4*>(a_s + k * kFastTile + ty * 4);
-      const float4 a1 = *reinterpret_cast<const float4*>(a_s + k * kFastTile + 64 + ty * 4);
+      const float4 a1 = RH == 2 ? *reinterpret_cast<const float4*>(a_s + k * kFastTile + 64 + ty * 4) : a0;
       const float4 b0 = *reinterpret_cast<const float4*>(b_s + k * kFastTile + tx * 4);
       const float4 b1 = *reinterpret_cast<const float4*>(b_s + k * kFastTile + 64 + tx * 4);
       const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
       const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int i = 0; i < 8; i++)
+      for (int i = 0; i < RI; i++)
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
@@ -194,9 +198,9 @@ __global__ void __launch_bounds__(256, 1) gram_fast_kernel(const float* __restri
   }
   flush();
   __syncthreads();
-  for (int e = tid; e < kFastTile * kFastTile; e += 256) {
-    // e = (i*8+j)*256 + owner thread  ->  the tile coordinates that thread's accumulator (i, j) stands for
-    const int ij = e >> 8, owner = e & 255;
+  for (int e = tid; e < kFastTile * kFastTile; e += T) {
+    // e = (i*8+j)*T + owner thread  ->  the tile coordinates that thread's accumulator (i, j) stands for
+    const int ij = e / T, owner = e % T;
     const int ai = ij >> 3, aj = ij & 7, otx = owner & 15, oty = owner >> 4;
     const int i = (ai < 4 ? 0 : 64) + oty * 4 + (ai & 3), j = (aj < 4 ? 0 : 64) + otx * 4 + (aj & 3);
     const int r = bi * kFastTile + i, c = bj * kFastTile + j;
@@ -222,9 +226,10 @@ int32_t gram_fast_launch(Model* m, Store* s, double* d_out, cudaStream_t stream)
   rows_per_chunk = (rows_per_chunk + kFlushRows - 1) / kFlushRows * kFlushRows;
   chunks = (s->n_slots + rows_per_chunk - 1) / rows_per_chunk;
   const size_t smem = (size_t)kFastTile * kFastTile * 8 + (size_t)4 * kFastKC * kFastTile * 4;
-  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(gram_fast_kernel), smem));
+  constexpr int kThreads = 256;  // 512 threads (4 x 8 outputs each) measured slower: 30.8 ms vs 25.0 ms at 10 M x 256
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(gram_fast_kernel<kThreads>), smem));
   dim3 grid((unsigned)n_blocks, (unsigned)chunks);
-  gram_fast_kernel<<<grid, 256, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
+  gram_fast_kernel<kThreads><<<grid, kThreads, smem, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
