@@ -48,6 +48,29 @@ __global__ void gather_rows_kernel(const float* __restrict__ vec, int fpad, int 
   if (lane == 0 && has) has[w] = slot >= 0 ? 1 : 0;
 }
 
+// The same over a store that is sharded across the GPUs of one process: interaction i takes its row
+// from slot slots[i] of the shard owners[i]; bases[] are the shards' vector arrays, peers' ones read
+// over NVLink (peer access enabled by the caller).
+struct ShardBases {
+  const float* base[ORYX_MAX_WORLD];
+};
+__global__ void gather_rows_sharded_kernel(const __grid_constant__ ShardBases shards, int fpad, int f,
+                                           const int32_t* __restrict__ owners, const int32_t* __restrict__ slots,
+                                           int64_t n, float* __restrict__ out, uint8_t* __restrict__ has) {
+  const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  const int32_t slot = slots[w];
+  float* dst = out + w * f;
+  if (slot >= 0) {
+    const float* src = shards.base[owners[w]] + (int64_t)slot * fpad;
+    for (int j = lane; j < f; j += 32) dst[j] = src[j];
+  } else {
+    for (int j = lane; j < f; j += 32) dst[j] = 0.f;
+  }
+  if (lane == 0 && has) has[w] = slot >= 0 ? 1 : 0;
+}
+
 // ALSUtils.java:37-59
 __device__ __forceinline__ double target_qui(bool implicit, double value, double current) {
   if (implicit) {
@@ -311,6 +334,130 @@ int32_t oryx_fold_in_rows(oryx_solver* sh, oryx_model* mh, int32_t implicit, int
     }
     // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81)
     for (int64_t i = 0; i < c; i++) if (h_slots[c_max + i] < 0) out_valid[off + i] = 0;
+  }
+  cleanup();
+  return rc;
+}
+
+int32_t oryx_fold_in_rows_sharded(oryx_solver* sh, oryx_model* const* models, int32_t world, int64_t xu_row_stride,
+                                  int64_t yi_row_stride, int32_t implicit, int32_t xu_which, const int64_t* xu_rows,
+                                  const int64_t* yi_rows, const double* values, int64_t n, float* out,
+                                  uint8_t* out_valid) {
+  ORYX_ARG(sh && models && xu_rows && yi_rows && values && out && out_valid, "null argument");
+  ORYX_ARG(world >= 1 && world <= ORYX_MAX_WORLD, "world out of range [1, ORYX_MAX_WORLD]");
+  ORYX_ARG(xu_which == ORYX_X || xu_which == ORYX_Y, "xu_which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(xu_row_stride > 0 && yi_row_stride > 0, "row strides must be positive");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  Solver* s = reinterpret_cast<Solver*>(sh);
+  const int f = solver_n(s);
+  const int dev = solver_device(s);
+  for (int r = 0; r < world; r++) {
+    ORYX_ARG(models[r] != nullptr, "null model in the shard list");
+    ORYX_ARG(reinterpret_cast<Model*>(models[r])->cfg.features == f, "solver and shards disagree on the number of features");
+  }
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+  if (cudaSetDevice(dev) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("cannot select CUDA device %d", dev);
+    return ORYX_E_CUDA;
+  }
+  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  // the kernels run on the solver's GPU and read the other shards' rows over NVLink
+  for (int r = 0; r < world; r++) {
+    const int peer = reinterpret_cast<Model*>(models[r])->device;
+    if (peer == dev) continue;
+    int can = 0;
+    ORYX_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer));
+    if (!can) {
+      set_error("device %d cannot read device %d as a peer", dev, peer);
+      return ORYX_E_UNSUPPORTED;
+    }
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+      cudaGetLastError();
+      set_error("cudaDeviceEnablePeerAccess(%d -> %d): %s", dev, peer, cudaGetErrorString(e));
+      return ORYX_E_CUDA;
+    }
+    cudaGetLastError();
+  }
+  std::lock_guard<std::mutex> lk(solver_mutex(s));
+  // the stores must not move while rows are gathered: shared locks on every shard, in shard order
+  std::vector<std::shared_lock<std::shared_mutex>> locks;
+  locks.reserve((size_t)world);
+  for (int r = 0; r < world; r++) locks.emplace_back(reinterpret_cast<Model*>(models[r])->mu);
+  const int yi_which = xu_which == ORYX_X ? ORYX_Y : ORYX_X;
+  ShardBases bx{}, by{};
+  int fpad = 0;
+  for (int r = 0; r < world; r++) {
+    Model* m = reinterpret_cast<Model*>(models[r]);
+    bx.base[r] = m->store[xu_which].d_vec;
+    by.base[r] = m->store[yi_which].d_vec;
+    fpad = m->store[ORYX_Y].fpad;
+  }
+  cudaStream_t st = solver_stream(s);
+  const int64_t chunk = 1 << 18;
+  const int64_t c_max = std::min<int64_t>(chunk, n);
+  float *d_xu = nullptr, *d_yi = nullptr, *d_out = nullptr;
+  double* d_val = nullptr;
+  uint8_t *d_has = nullptr, *d_valid = nullptr;
+  int32_t* d_idx = nullptr;  // [4 x c_max]: xu owner, xu slot, yi owner, yi slot
+  int32_t* h_idx = nullptr;  // pinned
+  auto cleanup = [&]() {
+    cudaFree(d_xu); cudaFree(d_yi); cudaFree(d_out); cudaFree(d_val); cudaFree(d_has); cudaFree(d_valid);
+    cudaFree(d_idx); cudaFreeHost(h_idx);
+  };
+  if (cudaMalloc(&d_xu, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_yi, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_out, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&d_val, (size_t)c_max * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&d_has, (size_t)c_max) != cudaSuccess || cudaMalloc(&d_valid, (size_t)c_max) != cudaSuccess ||
+      cudaMalloc(&d_idx, (size_t)c_max * 4 * sizeof(int32_t)) != cudaSuccess ||
+      cudaMallocHost(&h_idx, (size_t)c_max * 4 * sizeof(int32_t)) != cudaSuccess) {
+    cudaGetLastError();
+    cleanup();
+    set_error("allocation failed for a fold-in batch of %lld", (long long)c_max);
+    return ORYX_E_NOMEM;
+  }
+  // global row -> (owning shard, slot in that shard's store); -1 slot when the row has no vector
+  auto locate = [&](int which, int64_t stride, int64_t row, int32_t* owner, int32_t* slot) {
+    *owner = 0;
+    *slot = -1;
+    if (row < 0) return;
+    const int64_t r = row / stride;
+    if (r >= world) return;
+    const Store* store = &reinterpret_cast<Model*>(models[r])->store[which];
+    const int64_t local = row - r * stride;
+    *owner = (int32_t)r;
+    if ((size_t)local < store->row2slot.size()) *slot = store->row2slot[(size_t)local];
+  };
+  int32_t rc = ORYX_OK;
+  for (int64_t off = 0; off < n && rc == ORYX_OK; off += chunk) {
+    const int64_t c = std::min<int64_t>(chunk, n - off);
+    for (int64_t i = 0; i < c; i++) {
+      locate(xu_which, xu_row_stride, xu_rows[off + i], &h_idx[i], &h_idx[c_max + i]);
+      locate(yi_which, yi_row_stride, yi_rows[off + i], &h_idx[2 * c_max + i], &h_idx[3 * c_max + i]);
+    }
+    cudaError_t e = cudaMemcpyAsync(d_idx, h_idx, (size_t)c_max * 4 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+      const unsigned g = (unsigned)((c * 32 + 255) / 256);
+      gather_rows_sharded_kernel<<<g, 256, 0, st>>>(bx, fpad, f, d_idx, d_idx + c_max, c, d_xu, d_has);
+      gather_rows_sharded_kernel<<<g, 256, 0, st>>>(by, fpad, f, d_idx + 2 * c_max, d_idx + 3 * c_max, c, d_yi, nullptr);
+      const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
+      fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, d_xu, d_has, d_yi, d_val, c, d_out, d_valid);
+      e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * f, d_out, (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_valid + off, d_valid, (size_t)c, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      set_error("sharded fold-in batch failed: %s", cudaGetErrorString(e));
+      rc = ORYX_E_CUDA;
+      break;
+    }
+    for (int64_t i = 0; i < c; i++) if (h_idx[3 * c_max + i] < 0) out_valid[off + i] = 0;  // Yi == null -> null
   }
   cleanup();
   return rc;

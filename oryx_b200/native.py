@@ -91,6 +91,8 @@ SIGNATURES = {
     "oryx_topn_sharded_device": [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_fold_in_rows": [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, _i32p, _i32p, _f64p, C.c_int64, _f32p, _u8p],
+    "oryx_fold_in_rows_sharded": [C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
+                                  _i64p, _i64p, _f64p, C.c_int64, _f32p, _u8p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
@@ -447,6 +449,21 @@ class Solver:
         _check(lib().oryx_fold_in_batch(self._h, int(implicit), _ptr(xu_a, C.c_float), _ptr(has, C.c_uint8),
                                         _ptr(yi, C.c_float), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),
                                         _ptr(valid, C.c_uint8)))
+        return out, valid
+
+    def fold_in_rows_sharded(self, models, xu_row_stride: int, yi_row_stride: int, implicit: bool, xu_which: int,
+                             xu_rows, yi_rows, values):
+        """fold_in_rows over stores sharded by rows across the GPUs of this process (global int64 rows)."""
+        xr = np.ascontiguousarray(xu_rows, dtype=np.int64)
+        yr = np.ascontiguousarray(yi_rows, dtype=np.int64)
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        n = xr.size
+        out = np.empty((n, self.n), dtype=np.float32)
+        valid = np.zeros(n, dtype=np.uint8)
+        arr = (C.c_void_p * len(models))(*[m._h for m in models])
+        _check(lib().oryx_fold_in_rows_sharded(self._h, arr, len(models), xu_row_stride, yi_row_stride, int(implicit),
+                                               xu_which, _ptr(xr, C.c_int64), _ptr(yr, C.c_int64),
+                                               _ptr(vals, C.c_double), n, _ptr(out, C.c_float), _ptr(valid, C.c_uint8)))
         return out, valid
 
     def fold_in_rows(self, model: "Model", implicit: bool, xu_which: int, xu_rows, yi_rows, values):

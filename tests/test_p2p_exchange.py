@@ -70,3 +70,51 @@ def test_exchange_two_gpus_matches_oracle(hm):
 @pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs four GPUs")
 def test_exchange_four_gpus_matches_oracle():
     _run(4, 20000, 48, 10, steps=40)
+
+
+def _sharded_fold_in(world):
+    """X and Y sharded by rows over `world` GPUs of this process: the sharded fold-in (rows of other
+    shards read over NVLink) must be bit-identical to the single-model one, and the sum of the shards'
+    Grams must be the Gram of the whole."""
+    f, nu, ni, n = 24, 900, 1200, 4000
+    rng = np.random.default_rng(0xB20000B0)
+    x = (rng.standard_normal((nu, f)) * 0.3).astype(np.float32)
+    y = (rng.standard_normal((ni, f)) * 0.3).astype(np.float32)
+    xs, ys = -(-nu // world), -(-ni // world)   # rows per shard
+    whole = ob.Model(f, device=0)
+    whole.upsert(ob.X, np.arange(nu, dtype=np.int32), x)
+    whole.upsert(ob.Y, np.arange(ni, dtype=np.int32), y)
+    shards = []
+    for r in range(world):
+        m = ob.Model(f, device=r)
+        lo, hi = r * xs, min(nu, (r + 1) * xs)
+        m.upsert(ob.X, np.arange(hi - lo, dtype=np.int32), x[lo:hi])
+        lo, hi = r * ys, min(ni, (r + 1) * ys)
+        m.upsert(ob.Y, np.arange(hi - lo, dtype=np.int32), y[lo:hi])
+        shards.append(m)
+    shards[-1].remove(ob.Y, np.array([3], np.int32))          # a hole in the last shard ...
+    whole.remove(ob.Y, np.array([(world - 1) * ys + 3], np.int32))  # ... and the same row in the whole
+    g_whole = whole.gram(ob.Y)[0]
+    g_sum = sum(m.gram(ob.Y)[0] for m in shards)
+    assert np.max(np.abs(g_sum - g_whole)) <= 1e-12 * np.max(np.abs(g_whole))
+    yty = ob.Solver(g_whole, device=0)
+    ur = rng.integers(-1, nu + 30, n).astype(np.int64)
+    ir = rng.integers(0, ni + 30, n).astype(np.int64)
+    ir[:3] = (world - 1) * ys + 3
+    vals = rng.choice([1.0, 2.0, -1.0, 0.5], n)
+    for implicit in (True, False):
+        want, wv = yty.fold_in_rows(whole, implicit, ob.X, ur.astype(np.int32), ir.astype(np.int32), vals)
+        got, gv = yty.fold_in_rows_sharded(shards, xs, ys, implicit, ob.X, ur, ir, vals)
+        assert np.array_equal(gv, wv)
+        assert np.array_equal(got[gv == 1], want[wv == 1])
+    for m in shards + [whole]:
+        m.close()
+
+
+def test_sharded_fold_in_world_1():
+    _sharded_fold_in(1)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_sharded_fold_in_two_gpus():
+    _sharded_fold_in(2)
