@@ -781,7 +781,11 @@ bool batch_topn_supported(Model* m, int nq) {
   Store* s = &m->store[ORYX_Y];
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;
   const int kpad = round_up(s->features, BK);
-  return !lsh && kpad <= 256 && nq >= 32 && s->n_slots >= 4096 && encode_tiled_fn() != nullptr;
+  // Below 32 queries the path only pays off while the bf16 shadow of Y is current (it then reads half the
+  // bytes of an fp32 scan even for a single query); building the shadow for a handful of queries does not.
+  const bool shadow_current = m->batch.y_version == s->version && m->batch.y_rows == s->n_slots;
+  return !lsh && kpad <= 256 && (nq >= 32 || (nq >= 1 && shadow_current)) && s->n_slots >= 4096 &&
+         encode_tiled_fn() != nullptr;
 }
 
 // queries: HOST [nq x features].  Outputs: HOST arrays.  out_n[i] == -1 marks a query the caller must
