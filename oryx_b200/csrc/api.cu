@@ -678,7 +678,7 @@ int32_t oryx_recommend_batch(oryx_model* mh, const int32_t* user_rows, int32_t n
 }
 
 // Development aid (not in the public header): phase timings (ms) and flops of the last tensor-core batch.
-int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {  // out5 holds 7 doubles
+int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {  // out5 holds 9 doubles
   Model* m = reinterpret_cast<Model*>(mh);
   out5[0] = m->last_batch.convert_ms;
   out5[1] = m->last_batch.score_ms;
@@ -687,6 +687,8 @@ int32_t oryx_debug_batch_timings(oryx_model* mh, double* out5) {  // out5 holds 
   out5[4] = m->last_batch.flops;
   out5[5] = m->last_batch.cand_mean;
   out5[6] = m->last_batch.cand_max;
+  out5[7] = m->last_batch.runs;
+  out5[8] = m->last_batch.shadow_rebuilds;
   return ORYX_OK;
 }
 

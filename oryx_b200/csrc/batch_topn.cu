@@ -152,6 +152,28 @@ __global__ void convert_y_kernel(const float* __restrict__ y, int64_t n, int fpa
   if (lane == 0) atomicMax(max_norm_bits, __float_as_uint(local_max));
 }
 
+// The same conversion for a list of slots that just changed (upsert / remove): keeps the shadow current
+// under a trickle of updates instead of rebuilding 2.6 GB per change.  max_norm_bits only ever grows,
+// which keeps the error bound valid (a removed row's norm may linger in it: looser, never wrong).
+__global__ void convert_rows_kernel(const float* __restrict__ y, const int32_t* __restrict__ slots, int64_t n_changed,
+                                    int64_t shadow_rows, int fpad, int features, int kpad, int normalize,
+                                    __nv_bfloat16* __restrict__ out, unsigned int* __restrict__ max_norm_bits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= n_changed) return;
+  const int64_t row = slots[w];
+  if (row < 0 || row >= shadow_rows) return;
+  const float* src = y + row * fpad;
+  __nv_bfloat16* dst = out + row * kpad;
+  float ss = 0.f;
+  for (int j = lane; j < features; j += 32) { float v = src[j]; ss = fmaf(v, v, ss); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const float scale = normalize ? rsqrtf(ss) : 1.0f;
+  for (int j = lane; j < kpad; j += 32) dst[j] = __float2bfloat16_rn(j < features ? src[j] * scale : 0.f);
+  if (lane == 0 && ss == ss) atomicMax(max_norm_bits, __float_as_uint(normalize ? 1.0002f : ss));
+}
+
 // One warp per query: the row in slots[i] of a store (zeros for a negative slot) -> packed [nq x f].
 __global__ void gather_queries_kernel(const float* __restrict__ vec, int fpad, int f, const int32_t* __restrict__ slots,
                                       int nq, float* __restrict__ out) {
@@ -777,6 +799,25 @@ int32_t scratch(BatchScratch& bs, int i, size_t bytes, void** out, bool* grew = 
 
 }  // namespace
 
+// Called by the store (under the model's exclusive lock) after the rows in d_slots[0..n) of Y changed.
+// Returns true when the shadow was current before the mutation and has been brought up to date.
+bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint64_t version_before, cudaStream_t st) {
+  BatchScratch& bs = m->batch;
+  Store* s = &m->store[ORYX_Y];
+  if (bs.buf[0] == nullptr || bs.buf[4] == nullptr || bs.y_version != version_before || bs.y_rows != s->n_slots ||
+      bs.y_normalized < 0)
+    return false;
+  if (n > 0) {
+    const int kpad = round_up(s->features, BK);
+    convert_rows_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(
+        s->d_vec, d_slots, n, bs.y_rows, s->fpad, s->features, kpad, bs.y_normalized, (__nv_bfloat16*)bs.buf[0],
+        (unsigned int*)bs.buf[4]);
+    m->launches++;
+    if (cudaGetLastError() != cudaSuccess) return false;
+  }
+  return true;
+}
+
 bool batch_topn_supported(Model* m, int nq) {
   Store* s = &m->store[ORYX_Y];
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;
@@ -858,6 +899,7 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
     bs.y_version = s->version;
     bs.y_normalized = normalized;
     bs.y_rows = n;
+    if (timings) timings->shadow_rebuilds += 1;
   }
   convert_q_kernel<<<(nq_pad + 7) / 8, 256, 0, st>>>((const float*)d_q.p, nq, nq_pad, F, kpad,
                                                     (__nv_bfloat16*)d_qbf.p, (float*)d_qnorm.p);
@@ -910,6 +952,7 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   ORYX_CUDA(cudaStreamSynchronize(st));
   m->launches += 5;
   if (timings) {
+    timings->runs += 1;
     float ms;
     cudaEventElapsedTime(&ms, ev[0], ev[1]); timings->convert_ms = ms;
     cudaEventElapsedTime(&ms, ev[1], ev[2]); timings->score_ms = ms;

@@ -173,6 +173,7 @@ struct QueryCtx {
 struct BatchTimings {
   double convert_ms = 0, score_ms = 0, threshold_ms = 0, refine_ms = 0, flops = 0;
   double cand_mean = 0, cand_max = 0;  // candidate sub-blocks per query handed to the refine step
+  double runs = 0, shadow_rebuilds = 0;  // batches answered by the tensor-core path / full conversions of Y
 };
 
 // Grow-only device scratch of the tensor-core batch path, kept across calls (one batch at a time).
@@ -283,6 +284,7 @@ int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_
 
 // batch_topn.cu
 bool batch_topn_supported(Model* m, int nq);
+bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint64_t version_before, cudaStream_t st);
 // `queries` is a HOST [nq x features] array -- or, when `query_slots` is given, ignored: query i is then
 // the row in slot query_slots[i] of store `query_store` (a negative slot gives a zero query).
 int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,

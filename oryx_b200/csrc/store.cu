@@ -290,7 +290,9 @@ void store_free(Store* s) {
 int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs, int32_t n,
                      int32_t* out_partitions) {
   Store* s = &m->store[which];
+  const uint64_t version_before = s->version;
   s->version++;
+  bool shadow_ok = which == ORYX_Y;  // keep the batch path's bf16 shadow current if it was (batch_topn.cu)
   cudaStream_t st = m->update_stream;
   const int F = s->features;
   for (int64_t off = 0; off < n; off += kChunkRows) {
@@ -321,6 +323,7 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
         s->d_slot_row, s->d_slot_part, s->d_row_slot);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
+    if (shadow_ok) shadow_ok = batch_shadow_rows_changed(m, d_dst, c, version_before, st);
     ORYX_CUDA(cudaStreamSynchronize(st));
     if (out_partitions) {
       if (s->hashed) std::memcpy(out_partitions + off, h_parts, (size_t)c * sizeof(int32_t));
@@ -331,12 +334,15 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
     ORYX_TRY(refresh_block_parts(m, s));
     ORYX_CUDA(cudaStreamSynchronize(st));
   }
+  if (shadow_ok) m->batch.y_version = s->version;
   return ORYX_OK;
 }
 
 int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float* d_vecs, int64_t n) {
   Store* s = &m->store[which];
+  const uint64_t version_before = s->version;
   s->version++;
+  bool shadow_ok = which == ORYX_Y;
   cudaStream_t st = m->update_stream;
   const int F = s->features;
   const int64_t chunk = 1 << 20;
@@ -361,17 +367,20 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
         s->d_slot_row, s->d_slot_part, s->d_row_slot);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
+    if (shadow_ok) shadow_ok = batch_shadow_rows_changed(m, d_dst, c, version_before, st);
     ORYX_CUDA(cudaStreamSynchronize(st));
   }
   if (s->hashed) {
     ORYX_TRY(refresh_block_parts(m, s));
     ORYX_CUDA(cudaStreamSynchronize(st));
   }
+  if (shadow_ok) m->batch.y_version = s->version;
   return ORYX_OK;
 }
 
 int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
   Store* s = &m->store[which];
+  const uint64_t version_before = s->version;
   s->version++;
   cudaStream_t st = m->update_stream;
   ORYX_TRY(staging_reserve(m, std::max(n, 1), s->features, false));
@@ -387,7 +396,10 @@ int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
     s->live--;
     g.h_i32[cnt++] = slot;
   }
-  if (cnt == 0) return ORYX_OK;
+  if (cnt == 0) {
+    if (which == ORYX_Y && m->batch.y_version == version_before) m->batch.y_version = s->version;  // nothing changed
+    return ORYX_OK;
+  }
   ORYX_CUDA(cudaMemcpyAsync(g.d_i32, g.h_i32, (size_t)cnt * sizeof(int32_t), cudaMemcpyHostToDevice, st));
   int threads = 256;
   int64_t blocks = ((int64_t)cnt * 32 + threads - 1) / threads;
@@ -395,8 +407,11 @@ int32_t store_remove(Model* m, int which, const int32_t* rows, int32_t n) {
                                                           s->d_slot_row, s->d_slot_part, s->d_row_slot);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
+  // tombstones are NaN rows in the shadow as well
+  const bool shadow_ok = which == ORYX_Y && batch_shadow_rows_changed(m, g.d_i32, cnt, version_before, st);
   if (s->hashed) ORYX_TRY(refresh_block_parts(m, s));
   ORYX_CUDA(cudaStreamSynchronize(st));
+  if (shadow_ok) m->batch.y_version = s->version;
   return ORYX_OK;
 }
 

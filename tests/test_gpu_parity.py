@@ -475,3 +475,57 @@ def test_fold_in_rows_equals_host_buffer_path():
             wv = wv & has_x
             assert np.array_equal(gv, wv)
             assert np.array_equal(got[gv == 1], want[wv == 1])
+
+
+def test_batch_shadow_follows_updates():
+    """The bf16 shadow of Y that the batched path scores against is kept current by upserts and
+    removals of existing rows (no full rebuild), small pages of queries ride on it, and the answers
+    stay identical to the single-query path."""
+    import ctypes as C
+    from oryx_b200 import native
+    L = native.lib()
+    L.oryx_debug_batch_timings.restype = C.c_int32
+    L.oryx_debug_batch_timings.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+
+    def counters(m):
+        t = (C.c_double * 9)()
+        L.oryx_debug_batch_timings(m._h, t)
+        return int(t[7]), int(t[8])   # batches answered by the tensor-core path, full conversions of Y
+
+    n, f, hm = 50000, 64, 10
+    rng = np.random.default_rng(0xB20000C0)
+    y = random_model(n, f, 0xB20000C1)
+    q = random_model(64, f, 0xB20000C2)
+    for kind in (ob.DOT, ob.COSINE):
+        with ob.Model(f) as m:
+            m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+            m.topn_batch(kind, q, hm)                      # builds the shadow
+            runs0, rebuilds0 = counters(m)
+            assert rebuilds0 == 1
+            y_now = y.copy()
+            for step in range(3):
+                rows = rng.choice(n, 300, replace=False).astype(np.int32)
+                y_now[rows] = random_model(300, f, 0xB20000C3 + step) * (3.0 if step == 1 else 1.0)  # larger norms too
+                m.upsert(ob.Y, rows, y_now[rows])
+                gone = rng.choice(n, 40, replace=False).astype(np.int32)
+                m.remove(ob.Y, gone)
+                back = gone[:20]
+                m.upsert(ob.Y, back, y_now[back])          # re-uses freed slots
+                dead = set(gone[20:].tolist())
+                page = q[step * 5: step * 5 + 5]           # a page of 5: only taken while the shadow is current
+                b_rows, b_scores, b_cnt = m.topn_batch(kind, page, hm)
+                for i in range(len(page)):
+                    r1, s1 = m.topn(kind, page[i], hm)
+                    assert b_cnt[i] == len(r1) and b_rows[i, :b_cnt[i]].tolist() == r1.tolist()
+                    assert b_scores[i, :b_cnt[i]].tobytes() == s1.tobytes()
+                    assert not (set(r1.tolist()) & dead)
+                y_now[list(dead)] = 0
+            runs1, rebuilds1 = counters(m)
+            assert runs1 == runs0 + 3 and rebuilds1 == rebuilds0   # the tensor-core path, without a rebuild
+            # growing the store invalidates the shadow: a small page then goes one by one, a large one rebuilds
+            # (more new rows than the 60 freed slots, so the slot array really grows)
+            m.upsert(ob.Y, np.arange(n, n + 200, dtype=np.int32), random_model(200, f, 0xB20000C9))
+            m.topn_batch(kind, q[:5], hm)
+            assert counters(m) == (runs1, rebuilds1)
+            m.topn_batch(kind, q, hm)
+            assert counters(m) == (runs1 + 1, rebuilds1 + 1)

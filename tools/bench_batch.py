@@ -30,9 +30,9 @@ for rep in range(3):
     t0 = time.perf_counter()
     rows, scores, cnt = m.topn_batch(KIND, q, how_many)
     wall = time.perf_counter() - t0
-    t = (C.c_double * 7)()
+    t = (C.c_double * 9)()
     L.oryx_debug_batch_timings(m._h, t)
-    conv, score, thr, ref, flops, cand_mean, cand_max = [float(x) for x in t]
+    conv, score, thr, ref, flops, cand_mean, cand_max = [float(x) for x in t][:7]
     res.append(dict(wall_ms=wall * 1e3, convert_ms=conv, score_ms=score, threshold_ms=thr, refine_ms=ref,
                     score_tflops=flops / (score * 1e-3) / 1e12, handed_back=int((cnt < 0).sum()),
                     candidate_subblocks_mean=cand_mean, candidate_subblocks_max=cand_max))
