@@ -296,6 +296,7 @@ int32_t oryx_model_create(const oryx_config* config, oryx_model** out) {
   }
   ORYX_TRY(store_init(m.get(), ORYX_X, 0));
   ORYX_TRY(store_init(m.get(), ORYX_Y, config->capacity_hint));
+  m->coalescer = coalescer_create();
   *out = reinterpret_cast<oryx_model*>(m.release());
   return ORYX_OK;
 }
@@ -310,6 +311,8 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     store_free(&m->store[0]);
     store_free(&m->store[1]);
     known_free(&m->known);
+    coalescer_destroy(m->coalescer);
+    m->coalescer = nullptr;
     cudaFree(m->staging.d_vec); cudaFree(m->staging.d_i32); cudaFreeHost(m->staging.h_i32);
     cudaFree(m->staging.d_known_dst); cudaFree(m->staging.d_known_val);
     cudaFree(m->d_hash_vectors);

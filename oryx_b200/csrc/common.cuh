@@ -186,6 +186,10 @@ struct BatchScratch {
   int64_t y_rows = -1;
 };
 
+struct Coalescer;  // coalesce.cu
+Coalescer* coalescer_create();
+void coalescer_destroy(Coalescer* c);
+
 struct Model {
   oryx_config cfg{};
   int device = 0;
@@ -211,6 +215,7 @@ struct Model {
   BatchTimings last_batch;  // phase timings of the most recent tensor-core batch (oryx_debug_batch_timings)
   unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
+  Coalescer* coalescer = nullptr;  // request combiner of oryx_topn_coalesced
 
   std::atomic<int64_t> queries{0};
   std::atomic<int64_t> launches{0};

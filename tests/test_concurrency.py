@@ -74,3 +74,44 @@ def test_many_readers_one_updater(lsh):
     final = np.stack([m.get(ob.Y, int(r)) for r in range(0, n, 97)])
     assert all(np.array_equal(v, y_old[r]) or np.array_equal(v, y_new[r]) for v, r in zip(final, range(0, n, 97)))
     m.close()
+
+
+def test_coalesced_callers_get_the_single_query_answers():
+    """oryx_topn_coalesced from 24 threads (mixed how_many, kinds and exclusion lists): every caller gets
+    exactly what oryx_topn returns for its own request, whether it rode in a page or ran alone."""
+    n, f = 60000, 48
+    y = random_model(n, f, 0xB20000D0)
+    queries = random_model(96, f, 0xB20000D1)
+    m = ob.Model(f)
+    m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+    m.topn_batch(ob.DOT, queries[:32], 10)   # the bf16 shadow exists: pages of any size take the batch path
+    rng = np.random.default_rng(0xB20000D2)
+    plan = []
+    for i in range(len(queries)):
+        kind = ob.DOT if i % 5 else ob.COSINE
+        hm = [10, 10, 10, 25][i % 4]
+        excl = rng.choice(n, int(rng.integers(0, 30)), replace=False).astype(np.int32) if i % 3 == 0 else None
+        plan.append((kind, hm, excl))
+    want = [m.topn(k, queries[i], hm, ex) for i, (k, hm, ex) in enumerate(plan)]
+    got, errors = [None] * len(queries), []
+
+    def caller(t):
+        try:
+            for i in range(t, len(queries), 24):
+                k, hm, ex = plan[i]
+                got[i] = m.topn_coalesced(k, queries[i], hm, ex)
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    for _ in range(3):   # a few rounds: different interleavings
+        threads = [threading.Thread(target=caller, args=(t,)) for t in range(24)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join(timeout=120)
+        assert not errors, errors[:3]
+        for i, (w, g) in enumerate(zip(want, got)):
+            assert g is not None and g[0].tolist() == w[0].tolist() and g[1].tobytes() == w[1].tobytes(), i
+    with pytest.raises(ob.OryxError):
+        m.topn_coalesced(ob.DOT, queries[0], 0)
+    m.close()
