@@ -524,6 +524,19 @@ def run_ours(args):
             "h2d_bytes_per_call_device_state": 0,
             "identical_results": bool(a[0].tolist() == b[0].tolist() and a[1].tobytes() == b[1].tobytes())}}
 
+    # 400 NATIVE request threads (the reference's Tomcat pool, ServingLayer.java:225) through the C ABI:
+    # a separate process with its own copy of the model (tools/bench_coalesce.cpp); skipped if not built
+    if extras is not None and not args.no_cpu_baseline:
+        exe = os.path.join(ROOT, "tools", "bench_coalesce")
+        if os.path.exists(exe):
+            model.close()
+            torch.cuda.empty_cache()
+            try:
+                out = subprocess.run([exe, str(n_items), str(F), "400", "100"], capture_output=True, text=True, timeout=600)
+                extras["native_request_threads"] = json.loads(out.stdout.strip().splitlines()[-1])
+            except Exception as e:  # noqa: BLE001 -- an extra, never fatal
+                extras["native_request_threads"] = {"error": repr(e)}
+
     # ---- numbers
     ms_per_step = ms_total / args.steps
     scans_per_query = world * (n_items / ITEMS_PER_GPU)   # units of "one 10M-item scan"
