@@ -397,8 +397,11 @@ std::vector<IDValue> ALSServingModel::topN(const ScoreFunction& scoreFn, const R
     std::vector<int32_t> rows((size_t)howMany);
     std::vector<double> scores((size_t)howMany);
     int32_t n = 0;
-    check_status(oryx_topn(h_, scoreFn.kind, scoreFn.target.data(), howMany, excl.empty() ? nullptr : excl.data(),
-                           (int32_t)excl.size(), rows.data(), scores.data(), &n));
+    // many request threads call this at once (ServingLayer.java:225): the combining entry point answers
+    // whoever is waiting with one batch pass, with oryx_topn's exact results
+    check_status(oryx_topn_coalesced(h_, scoreFn.kind, scoreFn.target.data(), howMany,
+                                     excl.empty() ? nullptr : excl.data(), (int32_t)excl.size(), rows.data(),
+                                     scores.data(), &n));
     std::lock_guard<std::mutex> lk(mu_);
     for (int i = 0; i < n; i++) out.emplace_back(row_item_[rows[i]], scores[i]);
     return out;
