@@ -76,6 +76,7 @@ SIGNATURES = {
     "oryx_known_counts": [C.c_void_p, C.c_int32, _i32p, C.c_int32],
     "oryx_recommend": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _i32p],
     "oryx_recommend_batch": [C.c_void_p, _i32p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p],
+    "oryx_recommend_coalesced": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, _i32p, _f64p, _i32p, _i32p],
     "oryx_topn_coalesced": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _i32p, C.c_int32, _i32p, _f64p, _i32p],
     "oryx_topn_batch": [C.c_void_p, C.c_int32, _f32p, C.c_int32, C.c_int32, _i32p, _i32p, _i32p, _f64p, _i32p],
     "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
@@ -291,6 +292,18 @@ class Model:
         _check(lib().oryx_topn_coalesced(self._h, kind, _ptr(q, C.c_float), how_many, _ptr(ex, C.c_int32),
                                          0 if ex is None else ex.size, _ptr(rows, C.c_int32),
                                          _ptr(scores, C.c_double), C.byref(n)))
+        return rows[:n.value].copy(), scores[:n.value].copy()
+
+    def recommend_coalesced(self, user_row: int, how_many: int, consider_known_items: bool = False):
+        """recommend() for many caller threads (answered together by one batch pass)."""
+        rows = np.zeros(max(how_many, 1), dtype=np.int32)
+        scores = np.zeros(max(how_many, 1), dtype=np.float64)
+        n, found = C.c_int32(), C.c_int32()
+        _check(lib().oryx_recommend_coalesced(self._h, user_row, how_many, int(consider_known_items),
+                                              _ptr(rows, C.c_int32), _ptr(scores, C.c_double), C.byref(n),
+                                              C.byref(found)))
+        if not found.value:
+            return None
         return rows[:n.value].copy(), scores[:n.value].copy()
 
     def recommend_batch(self, user_rows, how_many: int, consider_known_items: bool = False):

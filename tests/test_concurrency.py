@@ -115,3 +115,40 @@ def test_coalesced_callers_get_the_single_query_answers():
     with pytest.raises(ob.OryxError):
         m.topn_coalesced(ob.DOT, queries[0], 0)
     m.close()
+
+
+def test_coalesced_recommend_by_user_row():
+    """oryx_recommend_coalesced from 16 threads: each caller gets oryx_recommend's answer for its user,
+    unknown users included."""
+    n_items, n_users, f, hm = 50000, 200, 32, 10
+    y = random_model(n_items, f, 0xB20000F0)
+    x = random_model(n_users, f, 0xB20000F1)
+    m = ob.Model(f)
+    m.upsert(ob.Y, np.arange(n_items, dtype=np.int32), y)
+    m.upsert(ob.X, np.arange(n_users, dtype=np.int32), x)
+    rng = np.random.default_rng(0xB20000F2)
+    m.known_items_add(np.arange(n_users), [rng.integers(0, n_items, int(k)).astype(np.int32) for k in rng.poisson(20, n_users)])
+    m.topn_batch(ob.DOT, x[:32], hm)   # shadow on
+    users = list(range(0, n_users, 3)) + [n_users + 5]
+    want = {u: m.recommend(u, hm) for u in users}
+    got, errors = {}, []
+
+    def caller(t):
+        try:
+            for u in users[t::16]:
+                got[u] = m.recommend_coalesced(u, hm)
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=caller, args=(t,)) for t in range(16)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join(timeout=120)
+    assert not errors, errors[:3]
+    for u in users:
+        if want[u] is None:
+            assert got[u] is None
+        else:
+            assert got[u][0].tolist() == want[u][0].tolist() and got[u][1].tobytes() == want[u][1].tobytes(), u
+    m.close()
