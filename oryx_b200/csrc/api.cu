@@ -728,6 +728,50 @@ int32_t oryx_scores_all(oryx_model* mh, int32_t kind, const float* query, int32_
   return rc;
 }
 
+int32_t oryx_estimate_pairs(oryx_model* mh, const int32_t* user_rows, const int32_t* item_rows, int64_t n,
+                            int32_t wide_products, double* out_scores, uint8_t* out_found) {
+  ORYX_ARG(mh && out_scores, "null argument");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  ORYX_ARG(user_rows && item_rows, "null rows");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_DEVICE(m);
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t* d_slots = nullptr;
+  double* d_out = nullptr;
+  int32_t rc = ORYX_OK;
+  do {
+    std::shared_lock<std::shared_mutex> lk(m->mu);
+    const Store* sx = &m->store[ORYX_X];
+    const Store* sy = &m->store[ORYX_Y];
+    std::vector<int32_t> slots((size_t)n * 2);
+    for (int64_t i = 0; i < n; i++) {
+      const int32_t u = user_rows[i], it = item_rows[i];
+      slots[(size_t)i] = (u >= 0 && (size_t)u < sx->row2slot.size()) ? sx->row2slot[(size_t)u] : -1;
+      slots[(size_t)(n + i)] = (it >= 0 && (size_t)it < sy->row2slot.size()) ? sy->row2slot[(size_t)it] : -1;
+      if (out_found) out_found[i] = slots[(size_t)i] >= 0 && slots[(size_t)(n + i)] >= 0;
+    }
+    if (cudaMalloc(&d_slots, (size_t)n * 2 * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc(&d_out, (size_t)n * sizeof(double)) != cudaSuccess) {
+      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
+    }
+    if (cudaMemcpyAsync(d_slots, slots.data(), (size_t)n * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
+      set_error("H2D copy failed"); rc = ORYX_E_CUDA; break;
+    }
+    rc = pair_scores_launch(m, d_slots, d_slots + n, n, wide_products ? 1 : 0, d_out, c->stream);
+    if (rc != ORYX_OK) break;
+    if (cudaMemcpyAsync(out_scores, d_out, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+      set_error("estimate_pairs failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    }
+  } while (0);
+  cudaFree(d_slots); cudaFree(d_out);
+  ctx_release(m, c);
+  return rc;
+}
+
 int32_t oryx_scores_rows(oryx_model* mh, int32_t kind, const float* query, const int32_t* rows, int32_t n,
                          double* out_scores, uint8_t* found) {
   ORYX_ARG(mh && query && out_scores, "null argument");

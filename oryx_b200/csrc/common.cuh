@@ -279,6 +279,9 @@ int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_ro
 int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32_t* d_slots, int n,
                            double* d_out, cudaStream_t stream);
 
+int32_t pair_scores_launch(Model* m, const int32_t* d_x_slots, const int32_t* d_y_slots, int64_t n, int wide_products,
+                           double* d_out, cudaStream_t stream);
+
 int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists,
                           int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
                           int32_t* d_out_n, cudaStream_t stream);

@@ -63,6 +63,28 @@ __global__ void scores_rows_kernel(const float* __restrict__ y, int fpad, int fe
   out[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dmul_rn(__dsqrt_rn(qq), __dsqrt_rn(tot))) : dot;
 }
 
+// Many (user, item) pairs at once: one thread per pair, the exact sequential arithmetic.
+//   wide_products == 0: VectorMath.dot (Estimate.java:62-71): binary32 product, binary64 sum;
+//   wide_products == 1: MLlib's MatrixFactorizationModel.predict, which the batch layer's Evaluation uses
+//                       (features widened to double first, binary64 product and sum).
+__global__ void pair_scores_kernel(const float* __restrict__ x, const float* __restrict__ y, int fpad, int features,
+                                   const int32_t* __restrict__ x_slots, const int32_t* __restrict__ y_slots,
+                                   int64_t n, int wide_products, double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t xs = x_slots[i], ys = y_slots[i];
+  if (xs < 0 || ys < 0) { out[i] = 0.0; return; }
+  const float* xv = x + (int64_t)xs * fpad;
+  const float* yv = y + (int64_t)ys * fpad;
+  double acc = 0.0;
+  if (wide_products) {
+    for (int j = 0; j < features; j++) acc = __dadd_rn(acc, __dmul_rn((double)xv[j], (double)yv[j]));
+  } else {
+    for (int j = 0; j < features; j++) acc = exact_step(acc, xv[j], yv[j]);
+  }
+  out[i] = acc;
+}
+
 // Cross-shard merge (kernel K7, multi-GPU leg): rank-sort of n_lists*how_many exact (score,row) pairs
 // by (score desc, global row asc) in one CTA.
 __global__ void merge_topn_kernel(const unsigned char* __restrict__ scores_b, const unsigned char* __restrict__ rows_b,
@@ -134,6 +156,17 @@ int32_t scores_rows_launch(Model* m, int kind, const float* d_query, const int32
   Store* s = &m->store[ORYX_Y];
   scores_rows_kernel<<<(n + 127) / 128, 128, 0, stream>>>(s->d_vec, s->fpad, s->features, d_query, kind,
                                                          d_slots, n, d_out);
+  m->launches++;
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t pair_scores_launch(Model* m, const int32_t* d_x_slots, const int32_t* d_y_slots, int64_t n, int wide_products,
+                           double* d_out, cudaStream_t stream) {
+  const Store* sx = &m->store[ORYX_X];
+  const Store* sy = &m->store[ORYX_Y];
+  pair_scores_kernel<<<(unsigned)((n + 127) / 128), 128, 0, stream>>>(sx->d_vec, sy->d_vec, sy->fpad, sy->features,
+                                                                     d_x_slots, d_y_slots, n, wide_products, d_out);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;

@@ -675,5 +675,100 @@ std::vector<Update> ALSSpeedModel::buildUpdates(const std::vector<UserItemStreng
   return out;
 }
 
+// ---------------------------------------------------------------- Evaluation
+namespace Evaluation {
+
+namespace {
+// predict() for pairs; result[i] is meaningful where found[i]
+void predict(oryx_model* model, const std::vector<std::pair<int, int>>& pairs, std::vector<double>* scores,
+             std::vector<uint8_t>* found) {
+  std::vector<int32_t> users(pairs.size()), items(pairs.size());
+  for (size_t i = 0; i < pairs.size(); i++) { users[i] = pairs[i].first; items[i] = pairs[i].second; }
+  scores->assign(pairs.size(), 0.0);
+  found->assign(pairs.size(), 0);
+  if (pairs.empty()) return;
+  check_status(oryx_estimate_pairs(model, users.data(), items.data(), (int64_t)pairs.size(), /*wide_products=*/1,
+                                   scores->data(), found->data()));
+}
+}  // namespace
+
+double rmse(oryx_model* model, const std::vector<Rating>& testData) {
+  std::vector<std::pair<int, int>> pairs;
+  pairs.reserve(testData.size());
+  for (const auto& r : testData) pairs.emplace_back(r.user, r.product);
+  std::vector<double> pred;
+  std::vector<uint8_t> found;
+  predict(model, pairs, &pred, &found);
+  double sum = 0.0;
+  size_t n = 0;
+  for (size_t i = 0; i < testData.size(); i++) {
+    if (!found[i]) continue;  // no prediction: the join drops the pair (:57-62)
+    const double diff = pred[i] - testData[i].rating;
+    sum += diff * diff;
+    n++;
+  }
+  return n == 0 ? std::numeric_limits<double>::quiet_NaN() : std::sqrt(sum / (double)n);
+}
+
+std::vector<std::pair<int, int>> sampleNegatives(const std::vector<Rating>& positiveData, uint64_t seed) {
+  std::vector<int> allItemIDs;  // distinct items, first-appearance order (:93)
+  {
+    std::unordered_set<int> seen;
+    for (const auto& r : positiveData) if (seen.insert(r.product).second) allItemIDs.push_back(r.product);
+  }
+  std::unordered_map<int, std::unordered_set<int>> positives;
+  std::vector<int> userOrder;
+  for (const auto& r : positiveData) {
+    auto ins = positives.emplace(r.user, std::unordered_set<int>{});
+    if (ins.second) userOrder.push_back(r.user);
+    ins.first->second.insert(r.product);
+  }
+  std::mt19937_64 rng(seed);
+  const int numItems = (int)allItemIDs.size();
+  std::vector<std::pair<int, int>> negative;
+  for (int user : userOrder) {
+    const auto& pos = positives[user];
+    const size_t numPositive = pos.size();
+    size_t added = 0;
+    // "Sample about as many negative examples as positive" (:108-114)
+    for (int i = 0; i < numItems && added < numPositive; i++) {
+      const int item = allItemIDs[(size_t)(rng() % (uint64_t)numItems)];
+      if (!pos.count(item)) {
+        negative.emplace_back(user, item);
+        added++;
+      }
+    }
+  }
+  return negative;
+}
+
+double areaUnderCurve(oryx_model* model, const std::vector<Rating>& positiveData,
+                      const std::vector<std::pair<int, int>>& negativeUserProducts) {
+  std::vector<std::pair<int, int>> posPairs;
+  posPairs.reserve(positiveData.size());
+  for (const auto& r : positiveData) posPairs.emplace_back(r.user, r.product);
+  std::vector<double> ps, ns;
+  std::vector<uint8_t> pf, nf;
+  predict(model, posPairs, &ps, &pf);
+  predict(model, negativeUserProducts, &ns, &nf);
+  std::unordered_map<int, std::pair<std::vector<double>, std::vector<double>>> byUser;
+  for (size_t i = 0; i < posPairs.size(); i++) if (pf[i]) byUser[posPairs[i].first].first.push_back(ps[i]);
+  for (size_t i = 0; i < negativeUserProducts.size(); i++) if (nf[i]) byUser[negativeUserProducts[i].first].second.push_back(ns[i]);
+  double sum = 0.0;
+  size_t users = 0;
+  for (const auto& kv : byUser) {
+    const auto& pos = kv.second.first;
+    const auto& neg = kv.second.second;
+    if (pos.empty() || neg.empty()) continue;  // the join keeps users with both (:122)
+    long correct = 0, total = 0;
+    for (double p : pos) for (double q : neg) { if (p > q) correct++; total++; }
+    sum += total == 0 ? 0.0 : (double)correct / (double)total;
+    users++;
+  }
+  return users == 0 ? std::numeric_limits<double>::quiet_NaN() : sum / (double)users;
+}
+
+}  // namespace Evaluation
+
 }  // namespace host
 }  // namespace oryx

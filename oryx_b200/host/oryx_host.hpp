@@ -213,6 +213,7 @@ class ALSSpeedModel {
   void retainRecentAndItemIDs(const std::vector<std::string>& items);  // :107-114
   float getFractionLoaded() const;                                      // :127-141
   int getNumUsers() const { return (int)x_.row.size(); }
+  oryx_model* handle() const { return h_; }
   int getNumItems() const { return (int)y_.row.size(); }
   std::unique_ptr<FloatVec> getUserVector(const std::string& user) const;
   std::unique_ptr<FloatVec> getItemVector(const std::string& item) const;
@@ -239,6 +240,24 @@ class ALSSpeedModel {
   oryx_model* h_ = nullptr;
   Side x_, y_;
 };
+
+// Evaluation.java (app/oryx-app-mllib/.../batch/mllib/als/Evaluation.java) over a model whose X and Y
+// live on the device; users and products are the dense rows of those stores.  Predictions use MLlib's
+// arithmetic (binary64 products), through oryx_estimate_pairs; pairs whose user or product has no vector
+// yield no prediction, as with MatrixFactorizationModel.predict.
+struct Rating {
+  int user, product;
+  double rating;
+};
+namespace Evaluation {
+double rmse(oryx_model* model, const std::vector<Rating>& testData);  // :49-63
+// :95-120: for every user about as many random non-positive items as positive ones, drawn from the distinct
+// items of the data (the reference draws with its own RandomGenerator; here a seeded std::mt19937_64)
+std::vector<std::pair<int, int>> sampleNegatives(const std::vector<Rating>& positiveData, uint64_t seed);
+// :70-135 "mean AUC": per user, the share of (positive, negative) pairs ranked correctly
+double areaUnderCurve(oryx_model* model, const std::vector<Rating>& positiveData,
+                      const std::vector<std::pair<int, int>>& negativeUserProducts);
+}  // namespace Evaluation
 
 }  // namespace host
 }  // namespace oryx

@@ -80,6 +80,7 @@ SIGNATURES = {
     "oryx_topn_coalesced": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _i32p, C.c_int32, _i32p, _f64p, _i32p],
     "oryx_topn_batch": [C.c_void_p, C.c_int32, _f32p, C.c_int32, C.c_int32, _i32p, _i32p, _i32p, _f64p, _i32p],
     "oryx_scores_all": [C.c_void_p, C.c_int32, _f32p, C.c_int32, _f64p],
+    "oryx_estimate_pairs": [C.c_void_p, _i32p, _i32p, C.c_int64, C.c_int32, _f64p, _u8p],
     "oryx_scores_rows": [C.c_void_p, C.c_int32, _f32p, _i32p, C.c_int32, _f64p, _u8p],
     "oryx_topn_device": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_topn_device_static": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
@@ -348,6 +349,16 @@ class Model:
         _check(lib().oryx_scores_rows(self._h, kind, _ptr(q, C.c_float), _ptr(r, C.c_int32), r.size,
                                       _ptr(out, C.c_double), _ptr(found, C.c_uint8)))
         return out, found.astype(bool)
+
+    def estimate_pairs(self, user_rows, item_rows, wide_products: bool = False):
+        """dot(X[user], Y[item]) for many pairs -> (scores float64[n], found uint8[n])."""
+        u = np.ascontiguousarray(user_rows, dtype=np.int32)
+        it = np.ascontiguousarray(item_rows, dtype=np.int32)
+        out = np.zeros(max(u.size, 1), dtype=np.float64)
+        found = np.zeros(max(u.size, 1), dtype=np.uint8)
+        _check(lib().oryx_estimate_pairs(self._h, _ptr(u, C.c_int32), _ptr(it, C.c_int32), u.size, int(wide_products),
+                                         _ptr(out, C.c_double), _ptr(found, C.c_uint8)))
+        return out[:u.size], found[:u.size]
 
     def topn_device(self, kind: int, d_query: int, how_many: int, d_rows: int, d_scores: int, d_n: int, stream: int):
         _check(lib().oryx_topn_device(self._h, kind, C.c_void_p(d_query), how_many, C.c_void_p(d_rows),

@@ -523,6 +523,54 @@ static void testSpeedModelManager() {
   CHECK(q.size() == 1 && q[0].find("],[") == std::string::npos);  // no trailing known-ids element (:209-210)
 }
 
+// Evaluation.java:49-145 (batch layer's model evaluation) on device-resident X / Y
+static void testEvaluation() {
+  const int F = 6, NU = 40, NI = 60;
+  ALSSpeedModel model(F, true);
+  std::mt19937_64 rng(77);
+  std::normal_distribution<float> g(0.f, 1.f);
+  std::vector<FloatVec> X(NU, FloatVec(F)), Y(NI, FloatVec(F));
+  for (int u = 0; u < NU; u++) { for (auto& v : X[u]) v = g(rng); model.setUserVector("u" + std::to_string(u), X[u]); }
+  for (int i = 0; i < NI; i++) { for (auto& v : Y[i]) v = g(rng); model.setItemVector("i" + std::to_string(i), Y[i]); }
+  // rows were handed out in insertion order: user u -> row u, item i -> row i
+  auto predict = [&](int u, int i) { double s = 0; for (int j = 0; j < F; j++) s += (double)X[u][j] * (double)Y[i][j]; return s; };
+  std::vector<Rating> test;
+  double sum = 0;
+  for (int k = 0; k < 200; k++) {
+    int u = (int)(rng() % NU), i = (int)(rng() % NI);
+    double r = (double)(rng() % 5);
+    test.push_back({u, i, r});
+    double d = predict(u, i) - r;
+    sum += d * d;
+  }
+  test.push_back({NU + 3, 1, 4.0});  // unknown user: no prediction, dropped by the join
+  CHECK_NEAR(Evaluation::rmse(model.handle(), test), std::sqrt(sum / 200.0), 1e-12);
+  // AUC: positives = each user's 5 best items -> every sampled negative ranks below every positive... not
+  // necessarily (a negative can outrank the 5th best), so compare with a direct recomputation instead
+  std::vector<Rating> positives;
+  for (int u = 0; u < NU; u++) {
+    std::vector<std::pair<double, int>> s;
+    for (int i = 0; i < NI; i++) s.push_back({predict(u, i), i});
+    std::sort(s.rbegin(), s.rend());
+    for (int k = 0; k < 5; k++) positives.push_back({u, s[k].second, 1.0});
+  }
+  auto negatives = Evaluation::sampleNegatives(positives, 1234);
+  CHECK(!negatives.empty() && negatives.size() <= positives.size());
+  std::set<std::pair<int, int>> posSet;
+  for (auto& r : positives) posSet.insert({r.user, r.product});
+  for (auto& n : negatives) CHECK(!posSet.count(n));
+  double aucSum = 0; int aucUsers = 0;
+  for (int u = 0; u < NU; u++) {
+    long correct = 0, total = 0;
+    for (auto& r : positives) if (r.user == u)
+      for (auto& n : negatives) if (n.first == u) { if (predict(u, r.product) > predict(u, n.second)) correct++; total++; }
+    if (total) { aucSum += (double)correct / total; aucUsers++; }
+  }
+  const double auc = Evaluation::areaUnderCurve(model.handle(), positives, negatives);
+  CHECK_NEAR(auc, aucSum / aucUsers, 1e-12);
+  CHECK(auc > 0.9);  // positives are each user's best items
+}
+
 int main() {
   try {
     testSolverAndALSUtils();
@@ -531,6 +579,7 @@ int main() {
     testSpeedFoldIn();
     testServingModelManager();
     testSpeedModelManager();
+    testEvaluation();
   } catch (const std::exception& e) {
     std::printf("EXCEPTION: %s\n", e.what());
     return 2;

@@ -529,3 +529,37 @@ def test_batch_shadow_follows_updates():
             assert counters(m) == (runs1, rebuilds1)
             m.topn_batch(kind, q, hm)
             assert counters(m) == (runs1 + 1, rebuilds1 + 1)
+
+
+def test_estimate_pairs_exact():
+    """oryx_estimate_pairs: VectorMath.dot of (X row, Y row) pairs bit for bit (Estimate.java:62-71; golden
+    /estimate/U0/I0/I1/I2 of EstimateTest.java:29-34), and MLlib's binary64-product arithmetic."""
+    g = load_golden("als_fixed_model")
+    x = np.array(g["model"]["X"], np.float32)
+    y = np.array(g["model"]["Y"], np.float32)
+    with ob.Model(2) as m:
+        m.upsert(ob.X, np.arange(len(x), dtype=np.int32), x)
+        m.upsert(ob.Y, np.arange(len(y), dtype=np.int32), y)
+        s, f = m.estimate_pairs([0, 0, 0, 0, 99], [0, 1, 2, 77, 1])
+        assert f.tolist() == [1, 1, 1, 0, 0] and s[3] == 0.0 and s[4] == 0.0   # unknown item / user -> 0
+        for got, want in zip(s[:3], (0.38761318, 0.4653969, -0.0801478)):
+            assert abs(got - want) <= 1e-6
+    rng = np.random.default_rng(0xB2000100)
+    f_, nu, ni, n = 37, 300, 500, 5000
+    x = rng.standard_normal((nu, f_)).astype(np.float32)
+    y = rng.standard_normal((ni, f_)).astype(np.float32)
+    with ob.Model(f_) as m:
+        m.upsert(ob.X, np.arange(nu, dtype=np.int32), x)
+        m.upsert(ob.Y, np.arange(ni, dtype=np.int32), y)
+        u = rng.integers(0, nu, n)
+        it = rng.integers(0, ni, n)
+        s, f = m.estimate_pairs(u, it)
+        assert f.all()
+        for k in range(0, n, 97):
+            assert s[k] == oracle.dot(x[u[k]], y[it[k]])
+        w, _ = m.estimate_pairs(u, it, wide_products=True)
+        for k in range(0, n, 97):   # sequential binary64 products and sums
+            acc = 0.0
+            for a, b in zip(x[u[k]].astype(np.float64), y[it[k]].astype(np.float64)):
+                acc += a * b
+            assert w[k] == acc
