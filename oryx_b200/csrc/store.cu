@@ -8,6 +8,7 @@
 // so "moving" a row between partitions is an in-place update of that integer.  oryx_items_compact
 // re-orders slots so rows of one partition are contiguous, which only affects scan locality.
 #include <algorithm>
+#include <cstdlib>
 #include <numeric>
 
 #include "common.cuh"
@@ -108,6 +109,39 @@ __global__ void gather_slots_kernel(const int32_t* __restrict__ src, int64_t n, 
   if (lane == 0) {
     new_row[w] = old_row[s];
     new_part[w] = old_part[s];
+  }
+}
+
+// ---- in-place compaction (store_compact when a second copy of the store does not fit) ----
+// The permutation "slot src[i] moves to slot i" decomposes into paths and cycles; each is cut into
+// segments of at most kSegMoves moves.  pos[] lists the slots of every segment in move order
+// (pos[j] moves to pos[j+1]); seg_begin[k] .. seg_begin[k+1] are segment k's entries (moves + 1 of them).
+// Pass 1 saves the row in each segment's FIRST slot (the previous segment overwrites it); pass 2 walks
+// every segment backwards, so a slot is always read before the one write that lands in it, and the
+// segment's first row comes from the saved copy.  One warp per segment.
+constexpr int kSegMoves = 32;
+
+__global__ void compact_save_kernel(const float4* __restrict__ vec, int f4, const int32_t* __restrict__ pos,
+                                    const int64_t* __restrict__ seg_begin, int64_t n_seg, float4* __restrict__ saved) {
+  const int64_t k = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (k >= n_seg) return;
+  const int64_t first = pos[seg_begin[k]];
+  for (int j = lane; j < f4; j += 32) saved[k * f4 + j] = vec[first * f4 + j];
+}
+
+__global__ void compact_move_kernel(float4* __restrict__ vec, int f4, const int32_t* __restrict__ pos,
+                                    const int64_t* __restrict__ seg_begin, int64_t n_seg,
+                                    const float4* __restrict__ saved) {
+  const int64_t k = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (k >= n_seg) return;
+  const int64_t b = seg_begin[k], e = seg_begin[k + 1];  // entries b .. e-1, moves b->b+1 ... e-2->e-1
+  for (int64_t j = e - 2; j >= b; j--) {
+    const int64_t from = pos[j], to = pos[j + 1];
+    // each lane handles the same columns at every step: its read of `from` here precedes, in program
+    // order, its write to `from` at the next step
+    for (int c = lane; c < f4; c += 32) vec[to * f4 + c] = (j == b) ? saved[k * f4 + c] : vec[from * f4 + c];
   }
 }
 
@@ -427,6 +461,97 @@ int32_t store_get(Model* m, int which, int32_t row, float* out, int32_t* found) 
   return ORYX_OK;
 }
 
+namespace {
+
+// Moves the rows of `s` so that slot i holds what slot src[i] held (i < live), without a second copy of
+// the matrix: see compact_save_kernel / compact_move_kernel.  Extra device memory: one row per segment
+// (1/32 of the matrix) plus 4 bytes per slot.
+int32_t compact_rows_in_place(Model* m, Store* s, const std::vector<int32_t>& src, int64_t live,
+                              const std::vector<uint8_t>& is_live) {
+  const int64_t n = s->n_slots;
+  std::vector<int32_t> dst((size_t)n, -1);
+  for (int64_t i = 0; i < live; i++) dst[(size_t)src[(size_t)i]] = (int32_t)i;
+  std::vector<int32_t> pos;
+  std::vector<int64_t> seg_begin{0};
+  pos.reserve((size_t)(n + n / kSegMoves + 16));
+  int moves_in_seg = 0;
+  auto begin_chain = [&](int32_t p0) { pos.push_back(p0); moves_in_seg = 0; };
+  auto push = [&](int32_t p) {
+    pos.push_back(p);
+    if (++moves_in_seg == kSegMoves) {  // close the segment; the next one starts at the same slot
+      seg_begin.push_back((int64_t)pos.size());
+      pos.push_back(p);
+      moves_in_seg = 0;
+    }
+  };
+  auto end_chain = [&]() {
+    if (moves_in_seg > 0) seg_begin.push_back((int64_t)pos.size());
+    else pos.pop_back();  // a segment start without moves
+  };
+  std::vector<uint8_t> visited((size_t)n, 0);
+  // paths: start at a live slot beyond the compacted range, end in a hole of that range
+  for (int64_t start = live; start < n; start++) {
+    if (!is_live[(size_t)start]) continue;
+    begin_chain((int32_t)start);
+    int32_t cur = (int32_t)start;
+    for (;;) {
+      visited[(size_t)cur] = 1;
+      const int32_t d = dst[(size_t)cur];
+      push(d);
+      if (!is_live[(size_t)d]) break;  // a hole: the path ends, nothing has to leave d
+      cur = d;
+    }
+    end_chain();
+  }
+  // cycles among the live slots of the compacted range that no path went through
+  for (int64_t start = 0; start < live; start++) {
+    if (!is_live[(size_t)start] || visited[(size_t)start] || dst[(size_t)start] == (int32_t)start) continue;
+    begin_chain((int32_t)start);
+    int32_t cur = (int32_t)start;
+    do {
+      visited[(size_t)cur] = 1;
+      cur = dst[(size_t)cur];
+      push(cur);
+    } while (cur != (int32_t)start);
+    end_chain();
+  }
+  const int64_t n_seg = (int64_t)seg_begin.size() - 1;
+  if (n_seg == 0) return ORYX_OK;  // already in order
+  const int f4 = s->fpad / 4;
+  int32_t* d_pos = nullptr;
+  int64_t* d_seg = nullptr;
+  float4* d_saved = nullptr;
+  cudaError_t e = cudaMalloc(&d_pos, pos.size() * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d_seg, seg_begin.size() * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d_saved, (size_t)n_seg * s->fpad * sizeof(float));
+  if (e != cudaSuccess) {
+    cudaFree(d_pos); cudaFree(d_seg); cudaFree(d_saved);
+    cudaGetLastError();
+    set_error("in-place compaction needs %.1f MB of scratch: %s",
+              ((double)n_seg * s->fpad * 4 + pos.size() * 4.0) / 1e6, cudaGetErrorString(e));
+    return ORYX_E_NOMEM;
+  }
+  cudaStream_t st = m->update_stream;
+  int32_t rc = ORYX_OK;
+  do {
+    if (cudaMemcpyAsync(d_pos, pos.data(), pos.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemcpyAsync(d_seg, seg_begin.data(), seg_begin.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+      set_error("H2D copy failed: %s", cudaGetErrorString(cudaGetLastError())); rc = ORYX_E_CUDA; break;
+    }
+    const unsigned blocks = (unsigned)((n_seg * 32 + 255) / 256);
+    compact_save_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const float4*>(s->d_vec), f4, d_pos, d_seg, n_seg, d_saved);
+    compact_move_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(s->d_vec), f4, d_pos, d_seg, n_seg, d_saved);
+    m->launches += 2;
+    if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+      set_error("in-place compaction failed: %s", cudaGetErrorString(cudaGetLastError())); rc = ORYX_E_CUDA; break;
+    }
+  } while (0);
+  cudaFree(d_pos); cudaFree(d_seg); cudaFree(d_saved);
+  return rc;
+}
+
+}  // namespace
+
 int32_t store_compact(Model* m, int which) {
   Store* s = &m->store[which];
   s->version++;
@@ -454,15 +579,41 @@ int32_t store_compact(Model* m, int which) {
   }
   int64_t cap = std::max<int64_t>(s->cap_slots, 1024);
   float* nv = nullptr; int32_t *nr = nullptr, *np = nullptr, *d_src = nullptr;
-  cudaError_t e = cudaMalloc(&nv, (size_t)cap * s->fpad * sizeof(float));
+  const bool force_in_place = std::getenv("ORYX_COMPACT_IN_PLACE") != nullptr;  // tests
+  cudaError_t e = force_in_place ? cudaErrorMemoryAllocation : cudaMalloc(&nv, (size_t)cap * s->fpad * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&nr, (size_t)cap * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&np, (size_t)cap * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&d_src, (size_t)std::max<int64_t>(live, 1) * sizeof(int32_t));
   if (e != cudaSuccess) {
+    // No room for a second copy of the matrix (a shard that fills most of the GPU): permute it in place.
     cudaFree(nv); cudaFree(nr); cudaFree(np); cudaFree(d_src);
     cudaGetLastError();
-    set_error("compaction needs a second copy of the store: %s", cudaGetErrorString(e));
-    return ORYX_E_NOMEM;
+    std::vector<uint8_t> is_live((size_t)n);
+    for (int64_t i = 0; i < n; i++) is_live[(size_t)i] = rowid[(size_t)i] >= 0 && part[(size_t)i] >= 0 && part[(size_t)i] < n_parts;
+    ORYX_TRY(compact_rows_in_place(m, s, src, live, is_live));
+    // the small per-slot arrays are rebuilt on the host and uploaded into the existing allocations
+    std::vector<int32_t> new_row((size_t)n, -1), new_part((size_t)n, -1);
+    for (int64_t i = 0; i < live; i++) {
+      new_row[(size_t)i] = rowid[(size_t)src[(size_t)i]];
+      new_part[(size_t)i] = part[(size_t)src[(size_t)i]];
+    }
+    ORYX_CUDA(cudaMemcpyAsync(s->d_slot_row, new_row.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    ORYX_CUDA(cudaMemcpyAsync(s->d_slot_part, new_part.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (s->d_row_slot) {
+      fill_i32_kernel<<<(unsigned)((s->row_slot_cap + 255) / 256), 256, 0, st>>>(s->d_row_slot, s->row_slot_cap, -1);
+      if (live > 0) rebuild_row_slot_kernel<<<(unsigned)((live + 255) / 256), 256, 0, st>>>(s->d_slot_row, live, s->d_row_slot);
+      m->launches += 2;
+    }
+    ORYX_CUDA(cudaGetLastError());
+    ORYX_CUDA(cudaStreamSynchronize(st));
+    s->n_slots = live;
+    s->free_slots.clear();
+    for (int64_t i = 0; i < live; i++) s->row2slot[(size_t)rowid[(size_t)src[(size_t)i]]] = (int32_t)i;
+    if (s->hashed) {
+      ORYX_TRY(refresh_block_parts(m, s));
+      ORYX_CUDA(cudaStreamSynchronize(st));
+    }
+    return ORYX_OK;
   }
   int threads = 256;
   if (live > 0) {

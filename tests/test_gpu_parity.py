@@ -563,3 +563,53 @@ def test_estimate_pairs_exact():
             for a, b in zip(x[u[k]].astype(np.float64), y[it[k]].astype(np.float64)):
                 acc += a * b
             assert w[k] == acc
+
+
+@pytest.mark.parametrize("n,f", [(70000, 48), (5000, 130)])
+def test_compaction_in_place_equals_out_of_place(n, f, monkeypatch):
+    """oryx_items_compact when a second copy of the store does not fit (forced here): the rows are permuted
+    in place by segments of the permutation's paths and cycles.  Every row reads back unchanged, LSH
+    queries return what they returned before, and the slot order equals the out-of-place result."""
+    rng = np.random.default_rng(0xB2000110)
+    y = random_model(n, f, 0xB2000111)
+    h, bits = ob.lsh_plan(0.3, 16)
+    hv = random_hash_vectors(h, f, 0xB2000112)
+    queries = random_model(6, f, 0xB2000113)
+
+    def build():
+        m = ob.Model(f, hash_vectors=hv, max_bits_differing=bits)
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        gone = rng_local.choice(n, n // 10, replace=False).astype(np.int32)   # holes for the paths to end in
+        m.remove(ob.Y, gone)
+        back = gone[: n // 40]
+        m.upsert(ob.Y, back, y[back])                                        # re-used slots
+        return m, set(gone[n // 40:].tolist())
+
+    rng_local = np.random.default_rng(7)
+    m1, dead = build()
+    rng_local = np.random.default_rng(7)
+    m2, _ = build()
+    before = [m1.topn(ob.DOT, q, 10) for q in queries]
+    m1.compact(ob.Y)                                   # out of place
+    monkeypatch.setenv("ORYX_COMPACT_IN_PLACE", "1")
+    m2.compact(ob.Y)                                   # in place
+    monkeypatch.delenv("ORYX_COMPACT_IN_PLACE")
+    for q, (r0, s0) in zip(queries, before):
+        for m in (m1, m2):
+            r, s = m.topn(ob.DOT, q, 10)
+            assert r.tolist() == r0.tolist() and s.tobytes() == s0.tobytes()
+        assert np.array_equal(m1.scores_all(ob.DOT, q, n), m2.scores_all(ob.DOT, q, n), equal_nan=True)
+    for row in list(range(0, n, 211)) + [n - 1]:
+        v1, v2 = m1.get(ob.Y, row), m2.get(ob.Y, row)
+        if row in dead:
+            assert v1 is None and v2 is None
+        else:
+            assert np.array_equal(v1, y[row]) and np.array_equal(v2, y[row])
+    assert m1.stats()["slots"][1] == m2.stats()["slots"][1] == n - len(dead)
+    # the compacted store keeps working: updates, another (no-op) compaction in place
+    m2.upsert(ob.Y, np.array([1, 2, 3], np.int32), y[[4, 5, 6]])
+    monkeypatch.setenv("ORYX_COMPACT_IN_PLACE", "1")
+    m2.compact(ob.Y)
+    monkeypatch.delenv("ORYX_COMPACT_IN_PLACE")
+    assert np.array_equal(m2.get(ob.Y, 2), y[5])
+    m1.close(); m2.close()

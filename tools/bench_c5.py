@@ -68,21 +68,16 @@ def run(label):
 
 ms_uncompacted = run("uncompacted")
 free_b, _ = torch.cuda.mem_get_info(dev)
-can_compact = free_b > n * F * 4 * 1.05   # compaction builds a second copy of the shard
-if world > 1:
-    t = torch.tensor([1 if can_compact else 0], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MIN); can_compact = bool(t.item())
-t_compact = 0.0
-if can_compact:
-    t0 = time.perf_counter(); m.compact(ob.Y); t_compact = time.perf_counter() - t0
-    ms_compacted = run("compacted")
-else:
-    ms_compacted = ms_uncompacted
+in_place = free_b < n * F * 4 * 1.05   # no room for a second copy of the shard: oryx_items_compact permutes in place
+can_compact = True
+t0 = time.perf_counter(); m.compact(ob.Y); t_compact = time.perf_counter() - t0
+ms_compacted = run("compacted")
 if rank == 0:
     frac = 37 / 256
     print(json.dumps({
         "config": f"{total} items x {F} f over {world} GPU(s), LSH sample-rate 0.3/32 cores ({H} hashes, {bits} bits -> 37 of 256 partitions), top-{HM}",
         "exchange": ("peer-memory kernel" if pipe is not None else "NCCL all-gather + merge") if world > 1 else None,
-        "compacted": can_compact, "items_per_gpu": n, "load_s_per_gpu": round(t_load, 1), "compact_s": round(t_compact, 1),
+        "compacted": can_compact, "compaction_in_place": bool(in_place), "items_per_gpu": n, "load_s_per_gpu": round(t_load, 1), "compact_s": round(t_compact, 1),
         "ms_per_query_uncompacted": ms_uncompacted, "ms_per_query_compacted": ms_compacted,
         "qps": 1000.0 / ms_compacted, "nominal_item_scores_per_sec": total * 1000.0 / ms_compacted,
         "actual_item_scores_per_sec": frac * total * 1000.0 / ms_compacted,
