@@ -201,3 +201,32 @@ def allreduce_gram(dist, torch, gram_partial):
     """YtY = sum of per-shard Grams (ALSServingModel.java:362-368), fp64, in place."""
     dist.all_reduce(gram_partial, op=dist.ReduceOp.SUM)
     return gram_partial
+
+
+def merge_batch_topn(shard_results, row_stride: int, how_many: int):
+    """Merge of per-shard batched answers (the host half of a sharded oryx_topn_batch).
+
+    ``shard_results[r] = (rows [nq x how_many] int32 local rows, scores [nq x how_many] float64,
+    counts [nq] int32)`` as returned by ``Model.topn_batch`` on shard r.  Returns global rows (int64),
+    scores and counts with the ordering of ``merge_topn_kernel``: score descending, global row ascending.
+    The lists are tiny (world x how_many per query); the device does the scoring, not this.
+    """
+    import numpy as np
+    nq = shard_results[0][0].shape[0]
+    out_rows = np.zeros((nq, how_many), dtype=np.int64)
+    out_scores = np.zeros((nq, how_many), dtype=np.float64)
+    out_cnt = np.zeros(nq, dtype=np.int32)
+    for q in range(nq):
+        rows, scores = [], []
+        for r, (sr, ss, sc) in enumerate(shard_results):
+            k = int(sc[q])
+            if k < 0:
+                raise ValueError(f"shard {r} handed query {q} back unanswered")
+            rows.append(sr[q, :k].astype(np.int64) + r * row_stride)
+            scores.append(ss[q, :k])
+        rows, scores = np.concatenate(rows), np.concatenate(scores)
+        order = np.lexsort((rows, -scores))[:how_many]
+        out_cnt[q] = order.size
+        out_rows[q, :order.size] = rows[order]
+        out_scores[q, :order.size] = scores[order]
+    return out_rows, out_scores, out_cnt

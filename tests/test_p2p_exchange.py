@@ -118,3 +118,24 @@ def test_sharded_fold_in_world_1():
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_sharded_fold_in_two_gpus():
     _sharded_fold_in(2)
+
+
+def test_sharded_batch_merges_to_the_unsharded_answer():
+    """A page of queries over Y split in two shards (two models; both on GPU 0 if only one GPU is there):
+    each shard answers through the tensor-core batch path, the host merges -- equal to the oracle over
+    the concatenated rows."""
+    from oryx_b200.sharded import merge_batch_topn
+    n_per, f, hm = 40000, 64, 15
+    ys = [random_model(n_per, f, 0xB2000120 + r) for r in range(2)]
+    q = random_model(40, f, 0xB2000122)
+    res = []
+    for r in range(2):
+        dev = r if torch.cuda.device_count() > 1 else 0
+        with ob.Model(f, device=dev) as m:
+            m.upsert(ob.Y, np.arange(n_per, dtype=np.int32), ys[r])
+            res.append(m.topn_batch(ob.DOT, q, hm))
+    rows, scores, cnt = merge_batch_topn(res, n_per, hm)
+    y_all = np.concatenate(ys)
+    for i in range(len(q)):
+        wr, ws = oracle.topn(ob.DOT, q[i], y_all, hm)
+        assert cnt[i] == len(wr) and rows[i, :cnt[i]].tolist() == wr.tolist() and scores[i, :cnt[i]].tobytes() == ws.tobytes()

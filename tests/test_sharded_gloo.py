@@ -96,3 +96,17 @@ def test_shard_plan_routing():
     assert list(pos) == [2, 3] and list(loc) == [1, 2]
     assert list(plan.split_exclusions(1, [0, 4, 9])) == [1]
     assert plan.split_exclusions(2, []).size == 0
+
+
+def test_merge_batch_topn_orders_like_the_device_merge():
+    """Host merge of per-shard batched answers: score descending, global row ascending, ragged counts."""
+    from oryx_b200.sharded import merge_batch_topn
+    hm = 4
+    s0 = (np.array([[5, 1, 9, 0], [2, 0, 0, 0]], np.int32), np.array([[9.0, 7.0, 7.0, 1.0], [3.0, 0, 0, 0]]), np.array([4, 1], np.int32))
+    s1 = (np.array([[0, 3, 0, 0], [0, 0, 0, 0]], np.int32), np.array([[8.0, 7.0, 0, 0], [0, 0, 0, 0]]), np.array([2, 0], np.int32))
+    rows, scores, cnt = merge_batch_topn([s0, s1], row_stride=100, how_many=hm)
+    assert cnt.tolist() == [4, 1]
+    assert rows[0].tolist() == [5, 100, 1, 9] and scores[0].tolist() == [9.0, 8.0, 7.0, 7.0]  # ties: lower global row first
+    assert rows[1, 0] == 2 and scores[1, 0] == 3.0
+    with pytest.raises(ValueError):
+        merge_batch_topn([s0, (s1[0], s1[1], np.array([2, -1], np.int32))], 100, hm)
