@@ -319,20 +319,25 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
         mbar_wait(&t_full[acc], aph);
         tcgen05_fence_after();
         float mx[SUBS_PER_TILE];
+        // TMEM loads are software-pipelined: the load of sub-block j+1 is in flight while the 32 values of
+        // sub-block j are reduced (waiting for each load before touching it left the tensor pipe idle
+        // behind the epilogue)
+        uint32_t r[2][32];
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(w4 * 32) << 16) + (uint32_t)(acc * BN);
+        tmem_ld_32x32b_x32(taddr0, r[0]);
 #pragma unroll
         for (int j = 0; j < SUBS_PER_TILE; j++) {
-          uint32_t r[32];
-          const uint32_t taddr = tmem_base + ((uint32_t)(w4 * 32) << 16) + (uint32_t)(acc * BN + j * SUB);
-          tmem_ld_32x32b_x32(taddr, r);
           tmem_ld_wait();
+          if (j + 1 < SUBS_PER_TILE) tmem_ld_32x32b_x32(taddr0 + (uint32_t)((j + 1) * SUB), r[(j + 1) & 1]);
+          const uint32_t* rr = r[j & 1];
           float m = -INFINITY;
           if (!ragged) {
 #pragma unroll
-            for (int i = 0; i < 32; i++) m = fmaxf(m, __uint_as_float(r[i]));  // fmaxf drops NaN (tombstones)
+            for (int i = 0; i < 32; i++) m = fmaxf(m, __uint_as_float(rr[i]));  // fmaxf drops NaN (tombstones)
           } else {
 #pragma unroll
             for (int i = 0; i < 32; i++) {
-              const float v = __uint_as_float(r[i]);
+              const float v = __uint_as_float(rr[i]);
               if (col0 + j * SUB + i < n_slots) m = fmaxf(m, v);
             }
           }
