@@ -809,9 +809,11 @@ int32_t scratch(BatchScratch& bs, int i, size_t bytes, void** out, bool* grew = 
 bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint64_t version_before, cudaStream_t st) {
   BatchScratch& bs = m->batch;
   Store* s = &m->store[ORYX_Y];
-  if (bs.buf[0] == nullptr || bs.buf[4] == nullptr || bs.y_version != version_before || bs.y_rows != s->n_slots ||
-      bs.y_normalized < 0)
+  // the slot array may have grown inside its capacity: the new slots are in d_slots like any other change
+  if (bs.buf[0] == nullptr || bs.buf[4] == nullptr || bs.y_version != version_before || bs.y_rows > s->n_slots ||
+      s->n_slots > bs.y_cap_rows || bs.y_normalized < 0)
     return false;
+  bs.y_rows = s->n_slots;
   if (n > 0) {
     const int kpad = round_up(s->features, BK);
     convert_rows_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, st>>>(
@@ -856,7 +858,10 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   std::lock_guard<std::mutex> batch_lock(bs.mu);
   struct P { void* p = nullptr; } d_ybf, d_qbf, d_q, d_qnorm, d_maxn, d_bmax, d_tmax, d_cut, d_cand, d_candn, d_orows, d_oscores, d_on, d_eo, d_es;
   bool y_grew = false;
-  ORYX_TRY(scratch(bs, 0, (size_t)n * kpad * 2, &d_ybf.p, &y_grew));
+  // room for the store's whole slot capacity, so that the shadow can follow the store as it fills up
+  const int64_t shadow_rows_cap = std::max<int64_t>(n, s->cap_slots);
+  ORYX_TRY(scratch(bs, 0, (size_t)shadow_rows_cap * kpad * 2, &d_ybf.p, &y_grew));
+  bs.y_cap_rows = (int64_t)(bs.bytes[0] / ((size_t)kpad * 2));
   ORYX_TRY(scratch(bs, 1, (size_t)nq_pad * kpad * 2, &d_qbf.p));
   ORYX_TRY(scratch(bs, 2, (size_t)nq * F * 4, &d_q.p));
   ORYX_TRY(scratch(bs, 3, (size_t)nq_pad * 4, &d_qnorm.p));

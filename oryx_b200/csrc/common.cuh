@@ -183,7 +183,8 @@ struct BatchScratch {
   size_t bytes[14] = {0};
   uint64_t y_version = ~0ull;  // store version the bf16 shadow of Y was converted from
   int y_normalized = -1;       // ... and whether it holds y/||y|| (cosine) or y (dot)
-  int64_t y_rows = -1;
+  int64_t y_rows = -1;      // slots the shadow covers (== n_slots of the store while it is current)
+  int64_t y_cap_rows = 0;   // rows the shadow buffer has room for (the store's slot capacity when it was built)
 };
 
 struct Coalescer;  // coalesce.cu

@@ -529,6 +529,15 @@ def test_batch_shadow_follows_updates():
             assert counters(m) == (runs1, rebuilds1)
             m.topn_batch(kind, q, hm)
             assert counters(m) == (runs1 + 1, rebuilds1 + 1)
+            # the rebuilt shadow has room for the store's new slot capacity: further new rows are followed
+            extra = random_model(100, f, 0xB20000CA)
+            m.upsert(ob.Y, np.arange(n + 200, n + 300, dtype=np.int32), extra * 4.0)   # would win most queries
+            b_rows, b_scores, b_cnt = m.topn_batch(kind, q[:5], hm)
+            assert counters(m) == (runs1 + 2, rebuilds1 + 1)
+            for i in range(5):
+                r1, s1 = m.topn(kind, q[i], hm)
+                assert b_rows[i, :b_cnt[i]].tolist() == r1.tolist() and b_scores[i, :b_cnt[i]].tobytes() == s1.tobytes()
+            assert any(r >= n + 200 for r in b_rows[0, :b_cnt[0]].tolist()) or kind == ob.COSINE
 
 
 def test_estimate_pairs_exact():
