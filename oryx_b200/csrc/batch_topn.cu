@@ -825,6 +825,8 @@ bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint
   return true;
 }
 
+thread_local bool tl_batch_small_pages_ok = false;
+
 bool batch_topn_supported(Model* m, int nq) {
   Store* s = &m->store[ORYX_Y];
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;
@@ -832,7 +834,7 @@ bool batch_topn_supported(Model* m, int nq) {
   // Below 32 queries the path only pays off while the bf16 shadow of Y is current (it then reads half the
   // bytes of an fp32 scan even for a single query); building the shadow for a handful of queries does not.
   const bool shadow_current = m->batch.y_version == s->version && m->batch.y_rows == s->n_slots;
-  return !lsh && kpad <= 256 && (nq >= 32 || (nq >= 1 && shadow_current)) && s->n_slots >= 4096 &&
+  return !lsh && kpad <= 256 && (nq >= 32 || (nq >= 1 && (shadow_current || tl_batch_small_pages_ok))) && s->n_slots >= 4096 &&
          encode_tiled_fn() != nullptr;
 }
 

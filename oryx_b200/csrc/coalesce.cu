@@ -45,6 +45,8 @@ constexpr int kMaxPage = 1024;  // requests answered by one batch
 // Answers `page` (same kind and how_many) with one oryx_topn_batch call; fills status / outputs.
 void run_page(oryx_model* mh, const std::vector<CoalesceRequest*>& page) {
   Model* m = reinterpret_cast<Model*>(mh);
+  // pages keep coming: even a short one may (re)build the bf16 shadow rather than scan once per query
+  struct SmallPages { SmallPages() { tl_batch_small_pages_ok = true; } ~SmallPages() { tl_batch_small_pages_ok = false; } } small_pages;
   const int F = m->cfg.features;
   const int nq = (int)page.size();
   const int hm = page[0]->how_many;

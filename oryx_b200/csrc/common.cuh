@@ -293,6 +293,9 @@ int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_
 
 // batch_topn.cu
 bool batch_topn_supported(Model* m, int nq);
+// Set by a caller that will keep sending small pages (the request combiner): lets a page of fewer than 32
+// queries (re)build the bf16 shadow instead of falling back to one scan per query.
+extern thread_local bool tl_batch_small_pages_ok;
 bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint64_t version_before, cudaStream_t st);
 // `queries` is a HOST [nq x features] array -- or, when `query_slots` is given, ignored: query i is then
 // the row in slot query_slots[i] of store `query_store` (a negative slot gives a zero query).
