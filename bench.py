@@ -8,8 +8,9 @@ Workload (config[1] of BASELINE.json): one top-10 /recommend query (DotsFunction
 10 M item vectors x 128 features fp32 per GPU, LSH sample-rate 1.0 (the reference's sizing rule for
 32 cores: 5 hashes, all partitions candidates), synthetic N(0,1) model (LoadTestALSModelFactory's
 recipe).  One step = one query.  With N GPUs the model holds N x 10 M items sharded by rows (weak
-scaling); every query scans all shards, each GPU selects a local top-10, an NCCL all-gather over
-NVLink exchanges the N x 10 pairs and a merge kernel orders them.  `value` counts 10 M-item scans
+scaling); every query scans all shards, each GPU selects a local top-10, and one kernel stores the
+record into every peer's inbox over NVLink, waits for the others' and merges (ORYX_BENCH_EXCHANGE=nccl:
+an NCCL all-gather and a merge kernel instead).  `value` counts 10 M-item scans
 per second over the whole job (= queries/s at N=1).
 
 Prints ONE JSON line on rank 0.  See DESIGN.md section "Measurement" for the roofline arithmetic.
@@ -232,7 +233,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 products, f64 accumulate",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"single-query /recommend top-{HOW_MANY}, {n_items} items x {args.features} f per 10M-item scan, "
                                "CPU restatement of ALSServingModel.topN (oracle port; the Java reference has no JVM here)",
@@ -575,10 +576,11 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32 scan, f64 exact re-score of the top-18",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"single-query /recommend top-{HOW_MANY} (DotsFunction), {n_items} items x {F} f fp32 per GPU, "
                                    f"LSH sample-rate 1.0 ({H} hashes, all partitions candidates), BASELINE.json configs[1]",
+                       "arithmetic": "f32 scan of every item, f64 exact re-score (VectorMath.dot arithmetic) of the top-18",
                        "items_per_gpu": n_items, "features": F, "how_many": HOW_MANY, "queries_cycled": N_QUERIES,
                        "parallelism": f"row-sharded x{world}" if world > 1 else "1 GPU",
                        "l2_policy": f"inputs larger than L2 ({alg_bytes / 1e9:.2f} GB streamed per step vs 126 MB L2)",
