@@ -27,6 +27,7 @@ void ctx_destroy(QueryCtx* c) {
   if (c->ev1) cudaEventDestroy(c->ev1);
   cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter); cudaFree(c->d_finish_seq);
   cudaFree(c->d_main_index); cudaFree(c->d_worklist); cudaFree(c->d_out_n);
+  cudaFree(c->d_tmp[0]); cudaFree(c->d_tmp[1]);
   cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_n);
 }
 
@@ -119,6 +120,35 @@ int32_t ensure_excl(QueryCtx* c, int32_t n) {
   return ORYX_OK;
 }
 
+// Scratch slot `i` of a context, at least `bytes` large.  Buffers up to kTmpKeepBytes stay with the context
+// (the point lookups of /estimate and /similarityToItem reuse them request after request); a larger one
+// (oryx_scores_all over millions of rows) is released again by ctx_tmp_trim at the end of the call.
+constexpr size_t kTmpKeepBytes = (size_t)32 << 20;
+static int32_t ctx_tmp(QueryCtx* c, int i, size_t bytes, void** out) {
+  if (c->tmp_bytes[i] < bytes) {
+    cudaFree(c->d_tmp[i]);
+    c->d_tmp[i] = nullptr;
+    c->tmp_bytes[i] = 0;
+    if (cudaMalloc(&c->d_tmp[i], bytes) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("device allocation of %zu bytes failed", bytes);
+      return ORYX_E_NOMEM;
+    }
+    c->tmp_bytes[i] = bytes;
+  }
+  *out = c->d_tmp[i];
+  return ORYX_OK;
+}
+static void ctx_tmp_trim(QueryCtx* c) {
+  for (int i = 0; i < 2; i++) {
+    if (c->tmp_bytes[i] > kTmpKeepBytes) {
+      cudaFree(c->d_tmp[i]);
+      c->d_tmp[i] = nullptr;
+      c->tmp_bytes[i] = 0;
+    }
+  }
+}
+
 struct DeviceGuard {
   int prev = -1;
   bool ok = false;
@@ -200,6 +230,20 @@ static int32_t run_topn(Model* m, QueryCtx* c, int32_t kind, const float* query,
   return run_topn_staged(m, c, kind, c->d_query, n_excl_slots, how_many, out_rows, out_scores, out_n);
 }
 
+int32_t async_mark(Model* m, cudaStream_t stream) {
+  ORYX_CUDA(cudaEventRecord(m->async_done, stream));  // the event exists since oryx_model_create
+  m->async_pending.store(true, std::memory_order_release);
+  return ORYX_OK;
+}
+
+int32_t async_fence(Model* m) {
+  if (!m->async_pending.load(std::memory_order_acquire)) return ORYX_OK;
+  // exclusive lock held: no stream-ordered launch can be in progress, the event is the latest one
+  ORYX_CUDA(cudaStreamWaitEvent(m->update_stream, m->async_done, 0));
+  m->async_pending.store(false, std::memory_order_release);
+  return ORYX_OK;
+}
+
 int32_t topn_device_impl(Model* m, int kind, const float* d_query, int how_many, int32_t* d_out_rows,
                          double* d_out_scores, int32_t* d_out_n, cudaStream_t stream,
                          const unsigned long long* gate, unsigned long long gate_value) {
@@ -228,7 +272,8 @@ int32_t topn_device_impl(Model* m, int kind, const float* d_query, int how_many,
   rq.gate = gate;
   rq.gate_value = gate_value;
   std::shared_lock<std::shared_mutex> lk(m->mu);
-  return scan_topn_launch(m, async_ctx, rq, stream);
+  ORYX_TRY(scan_topn_launch(m, async_ctx, rq, stream));
+  return async_mark(m, stream);
 }
 
 }  // namespace oryx
@@ -285,6 +330,7 @@ int32_t oryx_model_create(const oryx_config* config, oryx_model** out) {
   }
   m->num_sms = prop.multiProcessorCount;
   ORYX_CUDA(cudaStreamCreateWithFlags(&m->update_stream, cudaStreamNonBlocking));
+  ORYX_CUDA(cudaEventCreateWithFlags(&m->async_done, cudaEventDisableTiming));
   const int F = config->features, fpad = round_up(F, 4);
   if (m->num_hashes > 0) {
     m->h_hash_vectors.assign((size_t)m->num_hashes * fpad, 0.0f);
@@ -316,8 +362,11 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     cudaFree(m->staging.d_vec); cudaFree(m->staging.d_i32); cudaFreeHost(m->staging.h_i32);
     cudaFree(m->staging.d_known_dst); cudaFree(m->staging.d_known_val);
     cudaFree(m->d_hash_vectors);
+    cudaFree(m->d_gram); cudaFree(m->d_gram_scratch);
     for (auto& b : m->batch.buf) cudaFree(b);
+    for (auto& e : m->batch.ev) if (e) cudaEventDestroy(e);
     cudaFree(m->d_debug_ts);
+    if (m->async_done) cudaEventDestroy(m->async_done);
     if (m->update_stream) cudaStreamDestroy(m->update_stream);
     cudaGetLastError();
   }
@@ -335,6 +384,7 @@ int32_t oryx_items_upsert(oryx_model* mh, int32_t which, const int32_t* rows, co
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return store_upsert(m, which, rows, vecs, n, out_partitions);
 }
 
@@ -348,6 +398,7 @@ int32_t oryx_items_upsert_device(oryx_model* mh, int32_t which, int32_t first_ro
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return store_upsert_device(m, which, first_row, d_vecs, n);
 }
 
@@ -360,6 +411,7 @@ int32_t oryx_items_remove(oryx_model* mh, int32_t which, const int32_t* rows, in
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return store_remove(m, which, rows, n);
 }
 
@@ -378,6 +430,7 @@ int32_t oryx_items_compact(oryx_model* mh, int32_t which) {
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return store_compact(m, which);
 }
 
@@ -395,13 +448,9 @@ int32_t oryx_lsh_index_rows(oryx_model* mh, const float* vecs, int32_t n, int32_
   ORYX_TRY(ctx_acquire(m, &c));
   int32_t rc = ORYX_OK;
   do {
-    if (cudaMalloc(&d_in, (size_t)n * F * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&d_out, (size_t)n * sizeof(int32_t)) != cudaSuccess) {
-      cudaGetLastError();
-      set_error("device allocation failed for %d vectors", n);
-      rc = ORYX_E_NOMEM;
+    if ((rc = ctx_tmp(c, 0, (size_t)n * F * sizeof(float), (void**)&d_in)) != ORYX_OK ||
+        (rc = ctx_tmp(c, 1, (size_t)n * sizeof(int32_t), (void**)&d_out)) != ORYX_OK)
       break;
-    }
     if (cudaMemcpyAsync(d_in, vecs, (size_t)n * F * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { rc = ORYX_E_CUDA; set_error("H2D copy failed"); break; }
     rc = lsh_hash_rows_device(m, d_in, n, F, d_out, c->stream);
     if (rc != ORYX_OK) break;
@@ -411,7 +460,7 @@ int32_t oryx_lsh_index_rows(oryx_model* mh, const float* vecs, int32_t n, int32_
       rc = ORYX_E_CUDA;
     }
   } while (0);
-  cudaFree(d_in); cudaFree(d_out);
+  ctx_tmp_trim(c);
   ctx_release(m, c);
   return rc;
 }
@@ -431,9 +480,7 @@ int32_t oryx_lsh_candidates(oryx_model* mh, const float* vec, int32_t* out, int3
   int32_t* d_out = nullptr;
   int32_t rc = ORYX_OK;
   do {
-    if (cudaMalloc(&d_out, (size_t)(total + 1) * sizeof(int32_t)) != cudaSuccess) {
-      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
-    }
+    if ((rc = ctx_tmp(c, 0, (size_t)(total + 1) * sizeof(int32_t), (void**)&d_out)) != ORYX_OK) break;
     std::memcpy(c->h_query, vec, (size_t)F * sizeof(float));
     for (int j = F; j < fpad; j++) c->h_query[j] = 0.f;
     if (cudaMemcpyAsync(c->d_query, c->h_query, (size_t)fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { rc = ORYX_E_CUDA; set_error("H2D copy failed"); break; }
@@ -452,7 +499,6 @@ int32_t oryx_lsh_candidates(oryx_model* mh, const float* vec, int32_t* out, int3
     std::memcpy(out, host.data(), (size_t)n * sizeof(int32_t));
     *out_n = n;
   } while (0);
-  cudaFree(d_out);
   ctx_release(m, c);
   return rc;
 }
@@ -490,6 +536,7 @@ int32_t oryx_known_items_add(oryx_model* mh, const int32_t* user_rows, const int
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return known_add(m, user_rows, begin, item_rows, n_users);
 }
 
@@ -517,6 +564,7 @@ int32_t oryx_known_items_retain(oryx_model* mh, const uint8_t* keep_users, int32
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return known_retain(m, keep_users, n_user_rows, keep_items, n_item_rows);
 }
 
@@ -530,6 +578,7 @@ int32_t oryx_known_counts(oryx_model* mh, int32_t which, int32_t* out_counts, in
   ORYX_DEVICE(m);
   // the count kernel runs on the update stream: exclusive, like any other use of that stream
   std::unique_lock<std::shared_mutex> lk(m->mu);
+  ORYX_TRY(async_fence(m));
   return known_counts(m, which, out_counts, n_rows);
 }
 
@@ -708,9 +757,7 @@ int32_t oryx_scores_all(oryx_model* mh, int32_t kind, const float* query, int32_
   double* d_out = nullptr;
   int32_t rc = ORYX_OK;
   do {
-    if (cudaMalloc(&d_out, (size_t)n_rows * sizeof(double)) != cudaSuccess) {
-      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
-    }
+    if ((rc = ctx_tmp(c, 0, (size_t)n_rows * sizeof(double), (void**)&d_out)) != ORYX_OK) break;
     std::memcpy(c->h_query, query, (size_t)s->features * sizeof(float));
     for (int j = s->features; j < s->fpad; j++) c->h_query[j] = 0.f;
     std::shared_lock<std::shared_mutex> lk(m->mu);
@@ -723,7 +770,7 @@ int32_t oryx_scores_all(oryx_model* mh, int32_t kind, const float* query, int32_
       rc = ORYX_E_CUDA;
     }
   } while (0);
-  cudaFree(d_out);
+  ctx_tmp_trim(c);
   ctx_release(m, c);
   return rc;
 }
@@ -752,10 +799,9 @@ int32_t oryx_estimate_pairs(oryx_model* mh, const int32_t* user_rows, const int3
       slots[(size_t)(n + i)] = (it >= 0 && (size_t)it < sy->row2slot.size()) ? sy->row2slot[(size_t)it] : -1;
       if (out_found) out_found[i] = slots[(size_t)i] >= 0 && slots[(size_t)(n + i)] >= 0;
     }
-    if (cudaMalloc(&d_slots, (size_t)n * 2 * sizeof(int32_t)) != cudaSuccess ||
-        cudaMalloc(&d_out, (size_t)n * sizeof(double)) != cudaSuccess) {
-      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
-    }
+    if ((rc = ctx_tmp(c, 0, (size_t)n * 2 * sizeof(int32_t), (void**)&d_slots)) != ORYX_OK ||
+        (rc = ctx_tmp(c, 1, (size_t)n * sizeof(double), (void**)&d_out)) != ORYX_OK)
+      break;
     if (cudaMemcpyAsync(d_slots, slots.data(), (size_t)n * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) {
       set_error("H2D copy failed"); rc = ORYX_E_CUDA; break;
     }
@@ -767,7 +813,7 @@ int32_t oryx_estimate_pairs(oryx_model* mh, const int32_t* user_rows, const int3
       rc = ORYX_E_CUDA;
     }
   } while (0);
-  cudaFree(d_slots); cudaFree(d_out);
+  ctx_tmp_trim(c);
   ctx_release(m, c);
   return rc;
 }
@@ -795,10 +841,9 @@ int32_t oryx_scores_rows(oryx_model* mh, int32_t kind, const float* query, const
       slots[i] = (r >= 0 && (size_t)r < s->row2slot.size()) ? s->row2slot[r] : -1;
       if (found) found[i] = slots[i] >= 0;
     }
-    if (cudaMalloc(&d_slots, (size_t)n * sizeof(int32_t)) != cudaSuccess ||
-        cudaMalloc(&d_out, (size_t)n * sizeof(double)) != cudaSuccess) {
-      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
-    }
+    if ((rc = ctx_tmp(c, 0, (size_t)n * sizeof(int32_t), (void**)&d_slots)) != ORYX_OK ||
+        (rc = ctx_tmp(c, 1, (size_t)n * sizeof(double), (void**)&d_out)) != ORYX_OK)
+      break;
     std::memcpy(c->h_query, query, (size_t)s->features * sizeof(float));
     for (int j = s->features; j < s->fpad; j++) c->h_query[j] = 0.f;
     if (cudaMemcpyAsync(c->d_query, c->h_query, (size_t)s->fpad * sizeof(float), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
@@ -813,7 +858,7 @@ int32_t oryx_scores_rows(oryx_model* mh, int32_t kind, const float* query, const
       rc = ORYX_E_CUDA;
     }
   } while (0);
-  cudaFree(d_slots); cudaFree(d_out);
+  ctx_tmp_trim(c);
   ctx_release(m, c);
   return rc;
 }

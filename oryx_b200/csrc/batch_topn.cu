@@ -382,7 +382,8 @@ constexpr int kTileCap = 2048;       // tiles above the first cut
 //         with maximum >= T' - 2 delta.  Every sub-block >= T' - 2 delta sits in a tile >= Tc - 2 delta.
 __global__ void __launch_bounds__(kThrThreads)
 batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, const float* __restrict__ tmax,
-                       int64_t tmax_stride, int n_tiles, int k, const float* __restrict__ qnorm,
+                       int64_t tmax_stride, int n_tiles, int k_base, const int32_t* __restrict__ excl_offsets,
+                       const float* __restrict__ qnorm,
                        const unsigned int* __restrict__ max_norm_sq_bits, int32_t* __restrict__ cand, int cand_cap,
                        int32_t* __restrict__ cand_n, float* __restrict__ cut_out) {
   __shared__ float s_top[kThrThreads * kTopPerThread];
@@ -392,6 +393,14 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, cons
   __shared__ unsigned int s_count, s_out, s_ntile;
   __shared__ float s_lb, s_t;
   const int q = blockIdx.x, tid = threadIdx.x;
+  // The maxima include rows the query excludes (exclusions are applied row by row in the refine step),
+  // so the rank that guarantees k ALLOWED rows at or above the cut is k + the number of excluded rows:
+  // of any k + n_excl sub-blocks, at most n_excl owe their maximum to an excluded row.
+  const int k = k_base + (excl_offsets ? excl_offsets[q + 1] - excl_offsets[q] : 0);
+  if (k > kThrThreads * kTopPerThread) {  // beyond what pass A can rank: the host answers this query unbatched
+    if (tid == 0) cand_n[q] = -1;
+    return;
+  }
   const float* trow = tmax + (int64_t)q * tmax_stride;
   const float* row = bmax + (int64_t)q * bmax_stride;
   // rigorous bound on |bf16 score - exact score| for this query (see file header)
@@ -827,6 +836,12 @@ bool batch_shadow_rows_changed(Model* m, const int32_t* d_slots, int64_t n, uint
 
 thread_local bool tl_batch_small_pages_ok = false;
 
+bool batch_topn_possible(Model* m) {
+  Store* s = &m->store[ORYX_Y];
+  const bool lsh = s->hashed && m->num_hashes != m->max_bits;
+  return !lsh && round_up(s->features, BK) <= 256 && s->n_slots >= 4096 && encode_tiled_fn() != nullptr;
+}
+
 bool batch_topn_supported(Model* m, int nq) {
   Store* s = &m->store[ORYX_Y];
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;
@@ -887,9 +902,9 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   // the bf16 shadow of Y (and the norm bound that goes with it) is reused while the store is unchanged
   const int normalized = kind == ORYX_COSINE ? 1 : 0;
   const bool y_fresh = !y_grew && bs.y_version == s->version && bs.y_normalized == normalized && bs.y_rows == n;
-  cudaEvent_t ev[5];
-  for (auto& e : ev) ORYX_CUDA(cudaEventCreate(&e));
-  struct EvGuard { cudaEvent_t* e; ~EvGuard() { for (int i = 0; i < 5; i++) cudaEventDestroy(e[i]); } } evg{ev};
+  cudaEvent_t* ev = bs.ev;  // under bs.mu
+  for (int i = 0; i < 5; i++)
+    if (ev[i] == nullptr) ORYX_CUDA(cudaEventCreate(&ev[i]));
 
   if (query_slots) {
     // the queries are rows of a device-resident store: gather them, nothing but slot numbers is uploaded
@@ -932,7 +947,8 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   ORYX_CUDA(cudaEventRecord(ev[2], st));
 
   batch_threshold_kernel<<<nq, kThrThreads, 0, st>>>((const float*)d_bmax.p, bmax_stride, (const float*)d_tmax.p,
-                                                    tmax_stride, n_ytiles, k, (const float*)d_qnorm.p,
+                                                    tmax_stride, n_ytiles, k, excl_offsets ? (const int32_t*)d_eo.p : nullptr,
+                                                    (const float*)d_qnorm.p,
                                                     (const unsigned int*)d_maxn.p, (int32_t*)d_cand.p, cand_cap,
                                                     (int32_t*)d_candn.p, (float*)d_cut.p);
   ORYX_CUDA(cudaGetLastError());

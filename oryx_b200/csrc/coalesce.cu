@@ -147,6 +147,15 @@ int32_t coalesce_submit(oryx_model* mh, Coalescer* c, CoalesceRequest* req) {
   return req->status;
 }
 
+// Queueing behind a leader only pays when the leader can answer the page in one tensor-core pass.  When
+// it cannot (LSH filtering on, more than 256 features, a small store) the page would be answered one
+// scan at a time on a single context -- slower than the same threads scanning side by side on the
+// context pool -- so those callers bypass the queue.
+static bool combining_pays(Model* m) {
+  std::shared_lock<std::shared_mutex> lk(m->mu);
+  return batch_topn_possible(m);
+}
+
 }  // namespace oryx
 
 using namespace oryx;
@@ -159,6 +168,8 @@ extern "C" int32_t oryx_topn_coalesced(oryx_model* mh, int32_t kind, const float
   ORYX_ARG(n_excluded >= 0 && (n_excluded == 0 || excluded_rows), "bad exclusion list");
   ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
   Model* m = reinterpret_cast<Model*>(mh);
+  if (!combining_pays(m))  // no page could ride on the tensor cores: concurrent callers use the context pool instead
+    return oryx_topn(mh, kind, query, how_many, excluded_rows, n_excluded, out_rows, out_scores, out_n);
   CoalesceRequest req;
   req.kind = kind;
   req.how_many = how_many;
@@ -180,6 +191,7 @@ extern "C" int32_t oryx_recommend_coalesced(oryx_model* mh, int32_t user_row, in
   *out_n = 0;
   *found = 0;
   if (user_row < 0) return ORYX_OK;  // no such user
+  if (!combining_pays(m)) return oryx_recommend(mh, user_row, how_many, consider_known_items, out_rows, out_scores, out_n, found);
   CoalesceRequest req;
   req.kind = ORYX_DOT;
   req.how_many = how_many;

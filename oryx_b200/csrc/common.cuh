@@ -162,6 +162,10 @@ struct QueryCtx {
   int32_t* d_out_rows = nullptr;  // [max_k]
   double* d_out_scores = nullptr; // [max_k]
   int32_t* d_out_n = nullptr;
+  // grow-only device scratch of the point-lookup entry points (/estimate, /similarityToItem, LSH index):
+  // kept with the context so those calls do not go through cudaMalloc / cudaFree per request
+  void* d_tmp[2] = {nullptr, nullptr};
+  size_t tmp_bytes[2] = {0, 0};
   // pinned host staging
   float* h_query = nullptr;
   int32_t* h_excl = nullptr;
@@ -181,11 +185,31 @@ struct BatchScratch {
   std::mutex mu;
   void* buf[14] = {nullptr};
   size_t bytes[14] = {0};
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // phase timing, created once
   uint64_t y_version = ~0ull;  // store version the bf16 shadow of Y was converted from
   int y_normalized = -1;       // ... and whether it holds y/||y|| (cosine) or y (dot)
   int64_t y_rows = -1;      // slots the shadow covers (== n_slots of the store while it is current)
   int64_t y_cap_rows = 0;   // rows the shadow buffer has room for (the store's slot capacity when it was built)
 };
+
+// Grow-only buffers, streams and events of one solver's fold-in pipeline (foldin.cu): allocated the first
+// time a batch of that size runs, kept until the solver is destroyed, so a steady stream of micro-batches
+// (ALSSpeedModelManager.buildUpdates every batch interval) never touches the device allocator.
+struct FoldScratch {
+  void* d[8] = {nullptr};
+  size_t d_bytes[8] = {0};
+  void* h[4] = {nullptr};  // pinned
+  size_t h_bytes[4] = {0};
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_done[2] = {nullptr, nullptr};    // chunk's kernel finished (compute stream)
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr};  // chunk's results are in pinned host memory (copy stream)
+  cudaEvent_t ev_k0[2] = {nullptr, nullptr}, ev_k1[2] = {nullptr, nullptr};  // around fold_in_kernel
+  // last call: device time of fold_in_kernel summed over chunks, of the gathers, wall time, sizes
+  double last_kernel_ms = 0, last_wall_ms = 0;
+  int64_t last_n = 0;
+  int last_chunks = 0;
+};
+void fold_scratch_free(FoldScratch* fs);
 
 struct Coalescer;  // coalesce.cu
 Coalescer* coalescer_create();
@@ -216,7 +240,20 @@ struct Model {
   BatchTimings last_batch;  // phase timings of the most recent tensor-core batch (oryx_debug_batch_timings)
   unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
+  // The stream-ordered entry points return with their kernels still queued on the CALLER's stream.  Each
+  // records this event behind its launches; every mutator makes update_stream wait for it before touching
+  // the store (async_fence), so an upsert / removal / compaction never runs under a queued scan.
+  cudaEvent_t async_done = nullptr;
+  std::atomic<bool> async_pending{false};
   Coalescer* coalescer = nullptr;  // request combiner of oryx_topn_coalesced
+
+  // YtY / XtX (gram.cu): one persistent F x F binary64 output buffer plus whatever scratch the kernel needs,
+  // allocated by the first oryx_gram call; one Gram at a time per model.
+  std::mutex gram_mu;
+  double* d_gram = nullptr;
+  void* d_gram_scratch = nullptr;
+  size_t gram_scratch_bytes = 0;
+  std::atomic<double> last_gram_ms{0.0};
 
   std::atomic<int64_t> queries{0};
   std::atomic<int64_t> launches{0};
@@ -293,6 +330,9 @@ int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_
 
 // batch_topn.cu
 bool batch_topn_supported(Model* m, int nq);
+// The conditions of batch_topn_supported that do not depend on the page: false means no page can ever ride
+// on the tensor-core path for this model as it stands (the request combiner then stays out of the way).
+bool batch_topn_possible(Model* m);
 // Set by a caller that will keep sending small pages (the request combiner): lets a page of fewer than 32
 // queries (re)build the bf16 shadow instead of falling back to one scan per query.
 extern thread_local bool tl_batch_small_pages_ok;
@@ -315,6 +355,11 @@ int32_t ensure_max_dynamic_smem(const void* kernel, size_t bytes);
 int32_t topn_device_impl(Model* m, int kind, const float* d_query, int how_many, int32_t* d_out_rows,
                          double* d_out_scores, int32_t* d_out_n, cudaStream_t stream,
                          const unsigned long long* gate, unsigned long long gate_value);
+
+// Called after a stream-ordered entry point queued its kernels on `stream` (still under the shared lock).
+int32_t async_mark(Model* m, cudaStream_t stream);
+// Called by every mutator right after it took the exclusive lock.
+int32_t async_fence(Model* m);
 
 // pool
 int32_t ctx_acquire(Model* m, QueryCtx** out);

@@ -102,6 +102,18 @@ __global__ void __launch_bounds__(kExchangeThreads, 1) exchange_merge_kernel(con
     }
   }
   __syncthreads();
+  if (s_timeout) {
+    // The previous exchange of this rank never finished.  Publishing now would be out of order and could
+    // overwrite a parity slot a slow peer has not merged yet: fail this call cleanly instead (the peers
+    // time out on their side); the host must re-create the exchange before using it again.
+    if (!local_in_smem && tid == 0) st_release_sys(p.done + 1, p.seq);
+    if (tid == 0) {
+      *p.out_n = -2;
+      __threadfence();
+      st_release_sys(p.done, p.seq);
+    }
+    return;
+  }
 
   // 1. publish: one warp per peer copies the payload, then the flag
   const size_t slot_off = ((size_t)p.parity * p.world + p.rank) * p.rec_bytes;

@@ -13,6 +13,7 @@
 // The per-interaction solve is done as one binary64 GEMM against the inverse that solver.cu
 // derives from the same QR factors; everything else is the reference's operation sequence.
 #include <algorithm>
+#include <chrono>
 
 #include "common.cuh"
 
@@ -24,6 +25,7 @@ int solver_n(const Solver* s);
 int solver_device(const Solver* s);
 cudaStream_t solver_stream(const Solver* s);
 std::mutex& solver_mutex(Solver* s);
+FoldScratch* solver_fold_scratch(Solver* s);
 int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);
 
 namespace {
@@ -94,6 +96,7 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
                                                       const float* __restrict__ xu,
                                                       const uint8_t* __restrict__ has_xu,
                                                       const float* __restrict__ yi,
+                                                      const uint8_t* __restrict__ has_yi,
                                                       const double* __restrict__ values, int64_t n,
                                                       float* __restrict__ out, uint8_t* __restrict__ out_valid) {
   __shared__ double s_dq[kRowsPerCta];
@@ -117,7 +120,8 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
         for (int j = 0; j < f; j++) qui = exact_step(qui, x[j], y[j]);
       }
       double target = target_qui(implicit != 0, values[k], has ? qui : 0.5);
-      if (target == target) {  // not NaN
+      // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81) or the target is NaN (:90-92)
+      if (target == target && (has_yi == nullptr || has_yi[k])) {
         valid = 1;
         dq = target - qui;
       }
@@ -186,7 +190,166 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
   }
 }
 
+
+constexpr int64_t kFoldChunk = 1 << 17;  // interactions per pipeline stage
+
+int32_t fold_buf(FoldScratch* fs, int i, size_t bytes, void** out) {
+  if (fs->d_bytes[i] < bytes) {
+    cudaFree(fs->d[i]);
+    fs->d[i] = nullptr;
+    fs->d_bytes[i] = 0;
+    if (cudaMalloc(&fs->d[i], bytes) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("device allocation of %zu bytes failed (fold-in scratch)", bytes);
+      return ORYX_E_NOMEM;
+    }
+    fs->d_bytes[i] = bytes;
+  }
+  *out = fs->d[i];
+  return ORYX_OK;
+}
+int32_t fold_pinned(FoldScratch* fs, int i, size_t bytes, void** out) {
+  if (fs->h_bytes[i] < bytes) {
+    cudaFreeHost(fs->h[i]);
+    fs->h[i] = nullptr;
+    fs->h_bytes[i] = 0;
+    if (cudaMallocHost(&fs->h[i], bytes) != cudaSuccess) {
+      cudaGetLastError();
+      set_error("pinned allocation of %zu bytes failed (fold-in staging)", bytes);
+      return ORYX_E_NOMEM;
+    }
+    fs->h_bytes[i] = bytes;
+  }
+  *out = fs->h[i];
+  return ORYX_OK;
+}
+
+struct FoldBuffers {
+  float *d_xu, *d_yi, *d_out[2];
+  double* d_val;
+  uint8_t *d_has_xu, *d_has_yi, *d_valid[2];
+  int32_t* d_idx;          // [4 x c_max]
+  float* h_out[2];         // pinned
+  uint8_t* h_valid[2];     // pinned
+  int32_t* h_idx[2];       // pinned, [4 x c_max] each
+  int64_t c_max;
+};
+
+int32_t fold_prepare(FoldScratch* fs, int f, int64_t n, bool need_idx, FoldBuffers* b) {
+  const int64_t c_max = std::min<int64_t>(kFoldChunk, n);
+  b->c_max = c_max;
+  void* p = nullptr;
+  ORYX_TRY(fold_buf(fs, 0, (size_t)c_max * f * 4, &p)); b->d_xu = (float*)p;
+  ORYX_TRY(fold_buf(fs, 1, (size_t)c_max * f * 4, &p)); b->d_yi = (float*)p;
+  ORYX_TRY(fold_buf(fs, 2, (size_t)c_max * f * 4, &p)); b->d_out[0] = (float*)p;
+  ORYX_TRY(fold_buf(fs, 3, (size_t)c_max * f * 4, &p)); b->d_out[1] = (float*)p;
+  ORYX_TRY(fold_buf(fs, 4, (size_t)c_max * 8, &p)); b->d_val = (double*)p;
+  ORYX_TRY(fold_buf(fs, 5, (size_t)c_max * 2, &p)); b->d_has_xu = (uint8_t*)p; b->d_has_yi = b->d_has_xu + c_max;
+  ORYX_TRY(fold_buf(fs, 6, (size_t)c_max * 2, &p)); b->d_valid[0] = (uint8_t*)p; b->d_valid[1] = b->d_valid[0] + c_max;
+  b->d_idx = nullptr;
+  b->h_idx[0] = b->h_idx[1] = nullptr;
+  if (need_idx) {
+    ORYX_TRY(fold_buf(fs, 7, (size_t)c_max * 16, &p)); b->d_idx = (int32_t*)p;
+    ORYX_TRY(fold_pinned(fs, 3, (size_t)c_max * 32, &p)); b->h_idx[0] = (int32_t*)p; b->h_idx[1] = b->h_idx[0] + 4 * c_max;
+  }
+  ORYX_TRY(fold_pinned(fs, 0, (size_t)c_max * f * 4, &p)); b->h_out[0] = (float*)p;
+  ORYX_TRY(fold_pinned(fs, 1, (size_t)c_max * f * 4, &p)); b->h_out[1] = (float*)p;
+  ORYX_TRY(fold_pinned(fs, 2, (size_t)c_max * 2, &p)); b->h_valid[0] = (uint8_t*)p; b->h_valid[1] = b->h_valid[0] + c_max;
+  if (fs->copy_stream == nullptr) ORYX_CUDA(cudaStreamCreateWithFlags(&fs->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; i++) {
+    if (!fs->ev_done[i]) ORYX_CUDA(cudaEventCreateWithFlags(&fs->ev_done[i], cudaEventDisableTiming));
+    if (!fs->ev_copied[i]) ORYX_CUDA(cudaEventCreateWithFlags(&fs->ev_copied[i], cudaEventDisableTiming));
+    if (!fs->ev_k0[i]) ORYX_CUDA(cudaEventCreate(&fs->ev_k0[i]));
+    if (!fs->ev_k1[i]) ORYX_CUDA(cudaEventCreate(&fs->ev_k1[i]));
+  }
+  return ORYX_OK;
+}
+
+// The pipeline shared by the three entry points.  stage(off, c, parity) puts chunk [off, off + c) of the
+// inputs into b.d_xu / d_has_xu / d_yi / d_has_yi / d_val on `st` (host-to-device copies or gathers from
+// the device stores).  Results leave through two pinned buffers on a second stream, so the copy-out of
+// one chunk and the host's slot translation for the next overlap the kernel of the chunk in between.
+template <class Stage>
+int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int64_t n, bool use_has_yi, float* out,
+                      uint8_t* out_valid, Stage stage) {
+  FoldScratch* fs = solver_fold_scratch(s);
+  cudaStream_t st = solver_stream(s);
+  const auto wall0 = std::chrono::steady_clock::now();
+  double kernel_ms = 0;
+  int chunks = 0;
+  auto finalize = [&](int64_t off, int64_t c, int par) -> cudaError_t {
+    cudaError_t e = cudaEventSynchronize(fs->ev_copied[par]);
+    if (e != cudaSuccess) return e;
+    std::memcpy(out + off * f, b.h_out[par], (size_t)c * f * sizeof(float));
+    std::memcpy(out_valid + off, b.h_valid[par], (size_t)c);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, fs->ev_k0[par], fs->ev_k1[par]) == cudaSuccess) kernel_ms += ms;
+    else cudaGetLastError();
+    return cudaSuccess;
+  };
+  int64_t prev_off = -1, prev_c = 0;
+  cudaError_t e = cudaSuccess;
+  for (int64_t off = 0; off < n; off += kFoldChunk, chunks++) {
+    const int64_t c = std::min<int64_t>(kFoldChunk, n - off);
+    const int par = chunks & 1;
+    e = stage(off, c, par);
+    if (e != cudaSuccess) break;
+    const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
+    if ((e = cudaEventRecord(fs->ev_k0[par], st)) != cudaSuccess) break;
+    fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
+                                         use_has_yi ? b.d_has_yi : nullptr, b.d_val, c, b.d_out[par], b.d_valid[par]);
+    if ((e = cudaGetLastError()) != cudaSuccess) break;
+    if ((e = cudaEventRecord(fs->ev_k1[par], st)) != cudaSuccess) break;
+    if ((e = cudaEventRecord(fs->ev_done[par], st)) != cudaSuccess) break;
+    if ((e = cudaStreamWaitEvent(fs->copy_stream, fs->ev_done[par], 0)) != cudaSuccess) break;
+    if ((e = cudaMemcpyAsync(b.h_out[par], b.d_out[par], (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, fs->copy_stream)) != cudaSuccess) break;
+    if ((e = cudaMemcpyAsync(b.h_valid[par], b.d_valid[par], (size_t)c, cudaMemcpyDeviceToHost, fs->copy_stream)) != cudaSuccess) break;
+    if ((e = cudaEventRecord(fs->ev_copied[par], fs->copy_stream)) != cudaSuccess) break;
+    if (prev_off >= 0 && (e = finalize(prev_off, prev_c, par ^ 1)) != cudaSuccess) break;
+    prev_off = off;
+    prev_c = c;
+  }
+  if (e == cudaSuccess && prev_off >= 0) e = finalize(prev_off, prev_c, (chunks - 1) & 1);
+  if (e != cudaSuccess) {
+    cudaStreamSynchronize(st);
+    cudaStreamSynchronize(fs->copy_stream);
+    cudaGetLastError();
+    set_error("fold-in batch failed: %s", cudaGetErrorString(e));
+    return ORYX_E_CUDA;
+  }
+  fs->last_kernel_ms = kernel_ms;
+  fs->last_chunks = chunks;
+  fs->last_n = n;
+  fs->last_wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+  return ORYX_OK;
+}
+
+struct ScopedDevice {
+  int prev = -1;
+  bool ok = false;
+  explicit ScopedDevice(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+    ok = cudaSetDevice(dev) == cudaSuccess;
+    if (!ok) { cudaGetLastError(); set_error("cannot select CUDA device %d", dev); }
+  }
+  ~ScopedDevice() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 }  // namespace
+
+void fold_scratch_free(FoldScratch* fs) {
+  for (auto& p : fs->d) { cudaFree(p); p = nullptr; }
+  for (auto& p : fs->h) { cudaFreeHost(p); p = nullptr; }
+  for (int i = 0; i < 2; i++) {
+    if (fs->ev_done[i]) cudaEventDestroy(fs->ev_done[i]);
+    if (fs->ev_copied[i]) cudaEventDestroy(fs->ev_copied[i]);
+    if (fs->ev_k0[i]) cudaEventDestroy(fs->ev_k0[i]);
+    if (fs->ev_k1[i]) cudaEventDestroy(fs->ev_k1[i]);
+  }
+  if (fs->copy_stream) cudaStreamDestroy(fs->copy_stream);
+  *fs = FoldScratch{};
+}
+
 }  // namespace oryx
 
 using namespace oryx;
@@ -200,59 +363,24 @@ int32_t oryx_fold_in_batch(oryx_solver* sh, int32_t implicit, const float* xu, c
   if (n == 0) return ORYX_OK;
   Solver* s = reinterpret_cast<Solver*>(sh);
   const int f = solver_n(s);
-  int prev = -1;
-  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
-  if (cudaSetDevice(solver_device(s)) != cudaSuccess) {
-    cudaGetLastError();
-    set_error("cannot select CUDA device %d", solver_device(s));
-    return ORYX_E_CUDA;
-  }
-  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  ScopedDevice dev(solver_device(s));
+  if (!dev.ok) return ORYX_E_CUDA;
   std::lock_guard<std::mutex> lk(solver_mutex(s));
   cudaStream_t st = solver_stream(s);
-  const int64_t chunk = 1 << 18;  // interactions per staging round
-  float *d_xu = nullptr, *d_yi = nullptr, *d_out = nullptr;
-  double* d_val = nullptr;
-  uint8_t *d_has = nullptr, *d_valid = nullptr;
-  int64_t c_max = std::min<int64_t>(chunk, n);
-  int32_t rc = ORYX_OK;
-  auto cleanup = [&]() { cudaFree(d_xu); cudaFree(d_yi); cudaFree(d_out); cudaFree(d_val); cudaFree(d_has); cudaFree(d_valid); };
-  if (cudaMalloc(&d_xu, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_yi, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_out, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_val, (size_t)c_max * sizeof(double)) != cudaSuccess ||
-      cudaMalloc(&d_has, (size_t)c_max) != cudaSuccess || cudaMalloc(&d_valid, (size_t)c_max) != cudaSuccess) {
-    cudaGetLastError();
-    cleanup();
-    set_error("device allocation failed for a fold-in batch of %lld", (long long)c_max);
-    return ORYX_E_NOMEM;
-  }
-  for (int64_t off = 0; off < n && rc == ORYX_OK; off += chunk) {
-    int64_t c = std::min<int64_t>(chunk, n - off);
-    cudaError_t e = cudaSuccess;
-    if (xu) e = cudaMemcpyAsync(d_xu, xu + off * f, (size_t)c * f * sizeof(float), cudaMemcpyHostToDevice, st);
-    else e = cudaMemsetAsync(d_xu, 0, (size_t)c * f * sizeof(float), st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_yi, yi + off * f, (size_t)c * f * sizeof(float), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+  FoldBuffers b{};
+  ORYX_TRY(fold_prepare(solver_fold_scratch(s), f, n, false, &b));
+  return fold_pipeline(s, b, f, implicit, n, false, out, out_valid, [&](int64_t off, int64_t c, int) -> cudaError_t {
+    cudaError_t e;
+    if (xu) e = cudaMemcpyAsync(b.d_xu, xu + off * f, (size_t)c * f * sizeof(float), cudaMemcpyHostToDevice, st);
+    else e = cudaMemsetAsync(b.d_xu, 0, (size_t)c * f * sizeof(float), st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b.d_yi, yi + off * f, (size_t)c * f * sizeof(float), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b.d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) {
-      if (has_xu) e = cudaMemcpyAsync(d_has, has_xu + off, (size_t)c, cudaMemcpyHostToDevice, st);
-      else e = cudaMemsetAsync(d_has, xu ? 1 : 0, (size_t)c, st);
+      if (has_xu) e = cudaMemcpyAsync(b.d_has_xu, has_xu + off, (size_t)c, cudaMemcpyHostToDevice, st);
+      else e = cudaMemsetAsync(b.d_has_xu, xu ? 1 : 0, (size_t)c, st);
     }
-    if (e == cudaSuccess) {
-      unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
-      fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, d_xu, d_has, d_yi, d_val, c, d_out, d_valid);
-      e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * f, d_out, (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out_valid + off, d_valid, (size_t)c, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) {
-      set_error("fold-in batch failed: %s", cudaGetErrorString(e));
-      rc = ORYX_E_CUDA;
-    }
-  }
-  cleanup();
-  return rc;
+    return e;
+  });
 }
 
 int32_t oryx_fold_in_rows(oryx_solver* sh, oryx_model* mh, int32_t implicit, int32_t xu_which,
@@ -267,76 +395,34 @@ int32_t oryx_fold_in_rows(oryx_solver* sh, oryx_model* mh, int32_t implicit, int
   const int f = solver_n(s);
   ORYX_ARG(f == m->cfg.features, "solver and model disagree on the number of features");
   ORYX_ARG(solver_device(s) == m->device, "solver and model live on different devices");
-  int prev = -1;
-  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
-  if (cudaSetDevice(m->device) != cudaSuccess) {
-    cudaGetLastError();
-    set_error("cannot select CUDA device %d", m->device);
-    return ORYX_E_CUDA;
-  }
-  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
   std::lock_guard<std::mutex> lk(solver_mutex(s));
   std::shared_lock<std::shared_mutex> model_lock(m->mu);  // the stores must not move while rows are gathered
   const Store* sx = &m->store[xu_which];
   const Store* sy = &m->store[xu_which == ORYX_X ? ORYX_Y : ORYX_X];
   cudaStream_t st = solver_stream(s);
-  const int64_t chunk = 1 << 18;
-  const int64_t c_max = std::min<int64_t>(chunk, n);
-  float *d_xu = nullptr, *d_yi = nullptr, *d_out = nullptr;
-  double* d_val = nullptr;
-  uint8_t *d_has = nullptr, *d_valid = nullptr;
-  int32_t* d_slots = nullptr;  // [2 x c_max]
-  int32_t* h_slots = nullptr;  // pinned
-  auto cleanup = [&]() {
-    cudaFree(d_xu); cudaFree(d_yi); cudaFree(d_out); cudaFree(d_val); cudaFree(d_has); cudaFree(d_valid);
-    cudaFree(d_slots); cudaFreeHost(h_slots);
-  };
-  if (cudaMalloc(&d_xu, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_yi, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_out, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_val, (size_t)c_max * sizeof(double)) != cudaSuccess ||
-      cudaMalloc(&d_has, (size_t)c_max) != cudaSuccess || cudaMalloc(&d_valid, (size_t)c_max) != cudaSuccess ||
-      cudaMalloc(&d_slots, (size_t)c_max * 2 * sizeof(int32_t)) != cudaSuccess ||
-      cudaMallocHost(&h_slots, (size_t)c_max * 2 * sizeof(int32_t)) != cudaSuccess) {
-    cudaGetLastError();
-    cleanup();
-    set_error("allocation failed for a fold-in batch of %lld", (long long)c_max);
-    return ORYX_E_NOMEM;
-  }
+  FoldBuffers b{};
+  ORYX_TRY(fold_prepare(solver_fold_scratch(s), f, n, true, &b));
   auto slot_of = [](const Store* store, int32_t row) -> int32_t {
     return (row >= 0 && (size_t)row < store->row2slot.size()) ? store->row2slot[(size_t)row] : -1;
   };
-  int32_t rc = ORYX_OK;
-  for (int64_t off = 0; off < n && rc == ORYX_OK; off += chunk) {
-    const int64_t c = std::min<int64_t>(chunk, n - off);
+  const int64_t cm = b.c_max;
+  return fold_pipeline(s, b, f, implicit, n, true, out, out_valid, [&](int64_t off, int64_t c, int par) -> cudaError_t {
+    int32_t* h = b.h_idx[par];
     for (int64_t i = 0; i < c; i++) {
-      h_slots[i] = slot_of(sx, xu_rows[off + i]);
-      h_slots[c_max + i] = slot_of(sy, yi_rows[off + i]);
+      h[i] = slot_of(sx, xu_rows[off + i]);
+      h[cm + i] = slot_of(sy, yi_rows[off + i]);
     }
-    cudaError_t e = cudaMemcpyAsync(d_slots, h_slots, (size_t)c_max * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) {
-      const unsigned g = (unsigned)((c * 32 + 255) / 256);
-      gather_rows_kernel<<<g, 256, 0, st>>>(sx->d_vec, sx->fpad, f, d_slots, c, d_xu, d_has);
-      gather_rows_kernel<<<g, 256, 0, st>>>(sy->d_vec, sy->fpad, f, d_slots + c_max, c, d_yi, nullptr);
-      const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
-      fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, d_xu, d_has, d_yi, d_val, c, d_out, d_valid);
-      m->launches += 3;
-      e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * f, d_out, (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out_valid + off, d_valid, (size_t)c, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) {
-      set_error("fold-in batch failed: %s", cudaGetErrorString(e));
-      rc = ORYX_E_CUDA;
-      break;
-    }
-    // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81)
-    for (int64_t i = 0; i < c; i++) if (h_slots[c_max + i] < 0) out_valid[off + i] = 0;
-  }
-  cleanup();
-  return rc;
+    cudaError_t e = cudaMemcpyAsync(b.d_idx, h, (size_t)cm * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b.d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    const unsigned g = (unsigned)((c * 32 + 255) / 256);
+    gather_rows_kernel<<<g, 256, 0, st>>>(sx->d_vec, sx->fpad, f, b.d_idx, c, b.d_xu, b.d_has_xu);
+    gather_rows_kernel<<<g, 256, 0, st>>>(sy->d_vec, sy->fpad, f, b.d_idx + cm, c, b.d_yi, b.d_has_yi);
+    m->launches += 3;
+    return cudaGetLastError();
+  });
 }
 
 int32_t oryx_fold_in_rows_sharded(oryx_solver* sh, oryx_model* const* models, int32_t world, int64_t xu_row_stride,
@@ -356,14 +442,8 @@ int32_t oryx_fold_in_rows_sharded(oryx_solver* sh, oryx_model* const* models, in
     ORYX_ARG(models[r] != nullptr, "null model in the shard list");
     ORYX_ARG(reinterpret_cast<Model*>(models[r])->cfg.features == f, "solver and shards disagree on the number of features");
   }
-  int prev = -1;
-  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
-  if (cudaSetDevice(dev) != cudaSuccess) {
-    cudaGetLastError();
-    set_error("cannot select CUDA device %d", dev);
-    return ORYX_E_CUDA;
-  }
-  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  ScopedDevice scoped(dev);
+  if (!scoped.ok) return ORYX_E_CUDA;
   // the kernels run on the solver's GPU and read the other shards' rows over NVLink
   for (int r = 0; r < world; r++) {
     const int peer = reinterpret_cast<Model*>(models[r])->device;
@@ -397,29 +477,9 @@ int32_t oryx_fold_in_rows_sharded(oryx_solver* sh, oryx_model* const* models, in
     fpad = m->store[ORYX_Y].fpad;
   }
   cudaStream_t st = solver_stream(s);
-  const int64_t chunk = 1 << 18;
-  const int64_t c_max = std::min<int64_t>(chunk, n);
-  float *d_xu = nullptr, *d_yi = nullptr, *d_out = nullptr;
-  double* d_val = nullptr;
-  uint8_t *d_has = nullptr, *d_valid = nullptr;
-  int32_t* d_idx = nullptr;  // [4 x c_max]: xu owner, xu slot, yi owner, yi slot
-  int32_t* h_idx = nullptr;  // pinned
-  auto cleanup = [&]() {
-    cudaFree(d_xu); cudaFree(d_yi); cudaFree(d_out); cudaFree(d_val); cudaFree(d_has); cudaFree(d_valid);
-    cudaFree(d_idx); cudaFreeHost(h_idx);
-  };
-  if (cudaMalloc(&d_xu, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_yi, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_out, (size_t)c_max * f * sizeof(float)) != cudaSuccess ||
-      cudaMalloc(&d_val, (size_t)c_max * sizeof(double)) != cudaSuccess ||
-      cudaMalloc(&d_has, (size_t)c_max) != cudaSuccess || cudaMalloc(&d_valid, (size_t)c_max) != cudaSuccess ||
-      cudaMalloc(&d_idx, (size_t)c_max * 4 * sizeof(int32_t)) != cudaSuccess ||
-      cudaMallocHost(&h_idx, (size_t)c_max * 4 * sizeof(int32_t)) != cudaSuccess) {
-    cudaGetLastError();
-    cleanup();
-    set_error("allocation failed for a fold-in batch of %lld", (long long)c_max);
-    return ORYX_E_NOMEM;
-  }
+  FoldBuffers b{};
+  ORYX_TRY(fold_prepare(solver_fold_scratch(s), f, n, true, &b));
+  const int64_t cm = b.c_max;
   // global row -> (owning shard, slot in that shard's store); -1 slot when the row has no vector
   auto locate = [&](int which, int64_t stride, int64_t row, int32_t* owner, int32_t* slot) {
     *owner = 0;
@@ -432,71 +492,76 @@ int32_t oryx_fold_in_rows_sharded(oryx_solver* sh, oryx_model* const* models, in
     *owner = (int32_t)r;
     if ((size_t)local < store->row2slot.size()) *slot = store->row2slot[(size_t)local];
   };
-  int32_t rc = ORYX_OK;
-  for (int64_t off = 0; off < n && rc == ORYX_OK; off += chunk) {
-    const int64_t c = std::min<int64_t>(chunk, n - off);
+  return fold_pipeline(s, b, f, implicit, n, true, out, out_valid, [&](int64_t off, int64_t c, int par) -> cudaError_t {
+    int32_t* h = b.h_idx[par];  // [4 x c_max]: xu owner, xu slot, yi owner, yi slot
     for (int64_t i = 0; i < c; i++) {
-      locate(xu_which, xu_row_stride, xu_rows[off + i], &h_idx[i], &h_idx[c_max + i]);
-      locate(yi_which, yi_row_stride, yi_rows[off + i], &h_idx[2 * c_max + i], &h_idx[3 * c_max + i]);
+      locate(xu_which, xu_row_stride, xu_rows[off + i], &h[i], &h[cm + i]);
+      locate(yi_which, yi_row_stride, yi_rows[off + i], &h[2 * cm + i], &h[3 * cm + i]);
     }
-    cudaError_t e = cudaMemcpyAsync(d_idx, h_idx, (size_t)c_max * 4 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) {
-      const unsigned g = (unsigned)((c * 32 + 255) / 256);
-      gather_rows_sharded_kernel<<<g, 256, 0, st>>>(bx, fpad, f, d_idx, d_idx + c_max, c, d_xu, d_has);
-      gather_rows_sharded_kernel<<<g, 256, 0, st>>>(by, fpad, f, d_idx + 2 * c_max, d_idx + 3 * c_max, c, d_yi, nullptr);
-      const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
-      fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, d_xu, d_has, d_yi, d_val, c, d_out, d_valid);
-      e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out + off * f, d_out, (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out_valid + off, d_valid, (size_t)c, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) {
-      set_error("sharded fold-in batch failed: %s", cudaGetErrorString(e));
-      rc = ORYX_E_CUDA;
-      break;
-    }
-    for (int64_t i = 0; i < c; i++) if (h_idx[3 * c_max + i] < 0) out_valid[off + i] = 0;  // Yi == null -> null
-  }
-  cleanup();
-  return rc;
+    cudaError_t e = cudaMemcpyAsync(b.d_idx, h, (size_t)cm * 4 * sizeof(int32_t), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b.d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    const unsigned g = (unsigned)((c * 32 + 255) / 256);
+    gather_rows_sharded_kernel<<<g, 256, 0, st>>>(bx, fpad, f, b.d_idx, b.d_idx + cm, c, b.d_xu, b.d_has_xu);
+    gather_rows_sharded_kernel<<<g, 256, 0, st>>>(by, fpad, f, b.d_idx + 2 * cm, b.d_idx + 3 * cm, c, b.d_yi, b.d_has_yi);
+    return cudaGetLastError();
+  });
+}
+
+// Development aid (not in the public header): device time of fold_in_kernel summed over the chunks of the
+// solver's last fold-in call (ms), number of chunks, interactions, wall time of the call (ms).
+int32_t oryx_debug_fold_in_timings(oryx_solver* sh, double* out4) {
+  Solver* s = reinterpret_cast<Solver*>(sh);
+  FoldScratch* fs = solver_fold_scratch(s);
+  out4[0] = fs->last_kernel_ms;
+  out4[1] = fs->last_chunks;
+  out4[2] = (double)fs->last_n;
+  out4[3] = fs->last_wall_ms;
+  return ORYX_OK;
 }
 
 int32_t oryx_gram(oryx_model* mh, int32_t which, double* out, int64_t* out_rows_used) {
   ORYX_ARG(mh && out, "null argument");
   ORYX_ARG(which == ORYX_X || which == ORYX_Y, "which must be ORYX_X or ORYX_Y");
   Model* m = reinterpret_cast<Model*>(mh);
-  int prev = -1;
-  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
-  if (cudaSetDevice(m->device) != cudaSuccess) {
-    cudaGetLastError();
-    set_error("cannot select CUDA device %d", m->device);
-    return ORYX_E_CUDA;
-  }
-  struct Restore { int p; ~Restore() { if (p >= 0) cudaSetDevice(p); } } restore{prev};
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
   const int F = m->cfg.features;
   QueryCtx* c = nullptr;
   ORYX_TRY(ctx_acquire(m, &c));
-  double* d_out = nullptr;
   int32_t rc = ORYX_OK;
-  do {
-    if (cudaMalloc(&d_out, (size_t)F * F * sizeof(double)) != cudaSuccess) {
-      cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
-    }
-    std::shared_lock<std::shared_mutex> lk(m->mu);
-    if (out_rows_used) *out_rows_used = m->store[which].live;
-    rc = gram_launch(m, which, d_out, c->stream);
-    if (rc != ORYX_OK) break;
-    if (cudaMemcpyAsync(out, d_out, (size_t)F * F * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
-        cudaStreamSynchronize(c->stream) != cudaSuccess) {
-      set_error("gram failed: %s", cudaGetErrorString(cudaGetLastError()));
-      rc = ORYX_E_CUDA;
-    }
-  } while (0);
-  cudaFree(d_out);
+  {
+    std::lock_guard<std::mutex> gram_lock(m->gram_mu);
+    do {
+      if (m->d_gram == nullptr && cudaMalloc(&m->d_gram, (size_t)F * F * sizeof(double)) != cudaSuccess) {
+        cudaGetLastError(); set_error("device allocation failed"); rc = ORYX_E_NOMEM; break;
+      }
+      std::shared_lock<std::shared_mutex> lk(m->mu);
+      if (out_rows_used) *out_rows_used = m->store[which].live;
+      cudaEventRecord(c->ev0, c->stream);
+      rc = gram_launch(m, which, m->d_gram, c->stream);
+      if (rc != ORYX_OK) break;
+      cudaEventRecord(c->ev1, c->stream);
+      if (cudaMemcpyAsync(out, m->d_gram, (size_t)F * F * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+          cudaStreamSynchronize(c->stream) != cudaSuccess) {
+        set_error("gram failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = ORYX_E_CUDA;
+        break;
+      }
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_gram_ms.store((double)ms);
+      else cudaGetLastError();
+    } while (0);
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
   ctx_release(m, c);
   return rc;
+}
+
+// Development aid (not in the public header): device time (ms) of the model's last oryx_gram, memset included.
+int32_t oryx_debug_gram_ms(oryx_model* mh, double* out_ms) {
+  *out_ms = reinterpret_cast<Model*>(mh)->last_gram_ms.load();
+  return ORYX_OK;
 }
 
 }  // extern "C"

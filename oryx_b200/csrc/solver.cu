@@ -29,6 +29,7 @@ struct Solver {
   float* d_bx = nullptr;      // [2n] staging for single solves
   cudaStream_t stream = nullptr;
   std::mutex mu;
+  FoldScratch fold;
 };
 
 namespace {
@@ -249,6 +250,7 @@ void solver_free(Solver* s) {
   if (!s) return;
   cudaFree(s->d_qrt); cudaFree(s->d_rdiag); cudaFree(s->d_perm); cudaFree(s->d_inv);
   cudaFree(s->d_work); cudaFree(s->d_bx);
+  fold_scratch_free(&s->fold);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -260,6 +262,7 @@ int solver_n(const Solver* s) { return s->n; }
 int solver_device(const Solver* s) { return s->device; }
 cudaStream_t solver_stream(const Solver* s) { return s->stream; }
 std::mutex& solver_mutex(Solver* s) { return s->mu; }
+FoldScratch* solver_fold_scratch(Solver* s) { return &s->fold; }
 
 }  // namespace oryx
 

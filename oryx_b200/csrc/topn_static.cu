@@ -114,5 +114,6 @@ extern "C" int32_t oryx_topn_device_static(oryx_model* mh, int32_t kind, const f
   rq.d_out_scores = d_out_scores;
   rq.d_out_n = d_out_n;
   std::shared_lock<std::shared_mutex> lk(m->mu);
-  return scan_topn_launch(m, &ctx, rq, st);
+  ORYX_TRY(scan_topn_launch(m, &ctx, rq, st));
+  return async_mark(m, st);  // records an existing event: mutators wait for this scan before moving rows
 }

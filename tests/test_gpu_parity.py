@@ -396,6 +396,18 @@ def test_cross_shard_merge_kernels():
 
 @pytest.mark.parametrize("n,f,nq,how_many", [(20000, 128, 64, 10), (9000, 50, 130, 100), (33000, 256, 40, 10),
                                              (5000, 64, 32, 1)])
+def _batch_counters(m):
+    """(batches answered by the tcgen05 path, full bf16 conversions of Y) of a model so far."""
+    import ctypes as C
+    from oryx_b200 import native
+    L = native.lib()
+    L.oryx_debug_batch_timings.restype = C.c_int32
+    L.oryx_debug_batch_timings.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    t = (C.c_double * 9)()
+    L.oryx_debug_batch_timings(m._h, t)
+    return int(t[7]), int(t[8])
+
+
 def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
     """oryx_topn_batch (tcgen05 scoring + exact pruning/refinement) == one exact topN per query."""
     y = random_model(n, f, seed=n + 7 * f)
@@ -411,13 +423,44 @@ def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
         part = np.where(keep, 0, -1).astype(np.int32)
         for kind in (ob.DOT, ob.COSINE):
             excl = [rng.integers(0, n, 5).astype(np.int32) if i % 3 == 0 else np.zeros(0, np.int32) for i in range(nq)]
+            runs_before = _batch_counters(m)[0]
             rows, scores, cnt = m.topn_batch(kind, queries, how_many, excluded_lists=excl)
+            # the page must have been answered by the tensor-core kernels, not by the one-by-one fallback
+            assert _batch_counters(m)[0] == runs_before + 1
             for i in range(nq):
                 e_rows, e_scores = oracle.topn(kind, queries[i], y, how_many, part=part,
                                                excluded=np.unique(excl[i]) if len(excl[i]) else None)
                 assert cnt[i] == len(e_rows), (i, cnt[i], len(e_rows))
                 _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), (e_rows, e_scores),
                                   oracle.scores_all(kind, queries[i], y))
+
+
+@pytest.mark.parametrize("n_known", [20, 60, 100])
+def test_batch_paths_with_top_scoring_rows_excluded(n_known):
+    """A user's known items are typically the rows that score highest for that user.  The batched
+    pruning cut must count them: every query here excludes its own global top `n_known` rows, through
+    oryx_topn_batch, oryx_recommend_batch and both combining entry points, against the oracle."""
+    n, f, nq, how_many = 70000, 64, 48, 10
+    y = random_model(n, f, seed=0xB2000200)
+    x = random_model(nq, f, seed=0xB2000201)
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        m.upsert(ob.X, np.arange(nq, dtype=np.int32), x)
+        known = [oracle.topn(oracle.DOT, x[i], y, n_known)[0].astype(np.int32) for i in range(nq)]
+        m.known_items_add(np.arange(nq, dtype=np.int32), known)
+        expect = [oracle.topn(oracle.DOT, x[i], y, how_many, excluded=np.sort(known[i])) for i in range(nq)]
+        runs0 = _batch_counters(m)[0]
+        rows, scores, cnt = m.topn_batch(ob.DOT, x, how_many, excluded_lists=known)
+        r_rows, r_scores, r_cnt = m.recommend_batch(np.arange(nq, dtype=np.int32), how_many)
+        assert _batch_counters(m)[0] == runs0 + 2
+        for i in range(nq):
+            assert cnt[i] == how_many and r_cnt[i] == how_many
+            _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), expect[i])
+            _assert_same_topn((r_rows[i, :r_cnt[i]], r_scores[i, :r_cnt[i]]), expect[i])
+        for i in (0, 7, nq - 1):
+            _assert_same_topn(m.topn_coalesced(ob.DOT, x[i], how_many, excluded=known[i]), expect[i])
+            got = m.recommend_coalesced(i, how_many)
+            _assert_same_topn((got[0], got[1]), expect[i])
 
 
 @pytest.mark.parametrize("n,f", [(70000, 100), (66000, 256)])
@@ -481,16 +524,7 @@ def test_batch_shadow_follows_updates():
     """The bf16 shadow of Y that the batched path scores against is kept current by upserts and
     removals of existing rows (no full rebuild), small pages of queries ride on it, and the answers
     stay identical to the single-query path."""
-    import ctypes as C
-    from oryx_b200 import native
-    L = native.lib()
-    L.oryx_debug_batch_timings.restype = C.c_int32
-    L.oryx_debug_batch_timings.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
-
-    def counters(m):
-        t = (C.c_double * 9)()
-        L.oryx_debug_batch_timings(m._h, t)
-        return int(t[7]), int(t[8])   # batches answered by the tensor-core path, full conversions of Y
+    counters = _batch_counters   # batches answered by the tensor-core path, full conversions of Y
 
     n, f, hm = 50000, 64, 10
     rng = np.random.default_rng(0xB20000C0)
