@@ -55,6 +55,7 @@ def parse_args():
     ap.add_argument("--items", type=int, default=ITEMS_PER_GPU, help="items per GPU (parity/debug runs only)")
     ap.add_argument("--features", type=int, default=FEATURES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs[2..4] legs (bench_extras.py)")
     return ap.parse_args()
 
 
@@ -525,6 +526,14 @@ def run_ours(args):
             "h2d_bytes_per_call_device_state": 0,
             "identical_results": bool(a[0].tolist() == b[0].tolist() and a[1].tobytes() == b[1].tobytes())}}
 
+    # BASELINE.json configs[2]: 4096 queries x 10 M x 128 f, top-100, on the model that is already loaded
+    if extras is not None and not args.no_extras:
+        import bench_extras
+        try:
+            extras["c3_batch"] = bench_extras.c3_batch(ob, model, y_host, n_items, F, host_threads())
+        except Exception as e:  # noqa: BLE001 -- an extra must not lose the headline line; the error is reported
+            extras["c3_batch"] = {"error": repr(e)}
+
     # 400 NATIVE request threads (the reference's Tomcat pool, ServingLayer.java:225) through the C ABI:
     # a separate process with its own copy of the model (tools/bench_coalesce.cpp); skipped if not built
     if extras is not None and not args.no_cpu_baseline:
@@ -537,6 +546,32 @@ def run_ours(args):
                 extras["native_request_threads"] = json.loads(out.stdout.strip().splitlines()[-1])
             except Exception as e:  # noqa: BLE001 -- an extra, never fatal
                 extras["native_request_threads"] = {"error": repr(e)}
+
+    # BASELINE.json configs[3] (N = 1) and configs[4] + sharded parity + Gram all-reduce (N > 1): own models, so
+    # the headline model is released first
+    if not args.no_extras:
+        import bench_extras
+        barrier()
+        if world > 1 and hasattr(pipe, "close"):
+            pipe.close()
+        model.close()
+        torch.cuda.empty_cache()
+        if world == 1:
+            try:
+                extras["c4"] = bench_extras.c4_gram_foldin(ob, torch, dev, host_threads())
+            except Exception as e:  # noqa: BLE001
+                extras["c4"] = {"error": repr(e)}
+        else:
+            extras = {}
+            try:
+                extras.update(bench_extras.sharded_parity_and_gram(ob, torch, dist, dev, rank, world, host_threads()))
+            except Exception as e:  # noqa: BLE001
+                extras["parity_vs_oracle_sharded"] = {"error": repr(e)}
+            dist.barrier()
+            try:
+                extras["c5_strong"] = bench_extras.c5_strong(ob, torch, dist, dev, rank, world)
+            except Exception as e:  # noqa: BLE001
+                extras["c5_strong"] = {"error": repr(e)}
 
     # ---- numbers
     ms_per_step = ms_total / args.steps
@@ -588,7 +623,8 @@ def run_ours(args):
                        "parity_vs_oracle_full_size": parity,
                        "exchange": (("peer-memory kernel (oryx_topn_sharded_device)" if exchange == "p2p"
                                      else "NCCL all-gather + merge kernel") if world > 1 else None),
-                       "exchange_matches_nccl_path": exchange_check if world > 1 else None},
+                       "exchange_matches_nccl_path": exchange_check if world > 1 else None,
+                       "parity_vs_oracle_sharded": (extras or {}).get("parity_vs_oracle_sharded") if world > 1 else None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes,

@@ -118,6 +118,19 @@ def transpose_times_self(m) -> np.ndarray:
     return out
 
 
+def transpose_times_self_mt(m, threads: int) -> np.ndarray:
+    """getYTYSolver's sum of per-partition transposeTimesSelf results (ALSServingModel.java:357-373):
+    contiguous row slices, one per thread, partials added in slice order."""
+    m = _f32(m)
+    n, f = m.shape
+    out = np.zeros((f, f), dtype=np.float64)
+    L = lib()
+    L.oro_transpose_times_self_mt.restype = None
+    L.oro_transpose_times_self_mt.argtypes = [C.POINTER(C.c_float), C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    L.oro_transpose_times_self_mt(_p(m, C.c_float), n, f, threads, _p(out, C.c_double))
+    return out
+
+
 def lsh_plan(sample_rate: float, num_cores: int):
     h, b = C.c_int(), C.c_int()
     lib().oro_lsh_plan(sample_rate, num_cores, C.byref(h), C.byref(b))

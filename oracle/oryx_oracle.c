@@ -681,6 +681,42 @@ int oro_topn_mt(int kind, const float* q, const float* y, int64_t n, int f,
   return n_out;
 }
 
+/* ASM:357-373 getYTYSolver(): one transposeTimesSelf per partition (FV:150-154 getVTV), the partial
+ * matrices added together in partition order (`YTY = YTY == null ? YTYpartial : YTY.add(YTYpartial)`).
+ * Here a "partition" is a contiguous slice of rows, one worker thread per slice; each partial is the
+ * exact VM:64-83 loop, and the partials are summed in slice order.  (Which rows fall in which partition
+ * is an LSH detail the sum does not depend on beyond the order of binary64 additions.) */
+typedef struct { const float* m; int64_t lo, hi; int f; double* out; } oro_gram_task;
+
+static void* gram_worker(void* arg) {
+  oro_gram_task* k = (oro_gram_task*)arg;
+  oro_transpose_times_self(k->m + k->lo * (int64_t)k->f, k->hi - k->lo, k->f, k->out);
+  return NULL;
+}
+
+void oro_transpose_times_self_mt(const float* m, int64_t rows, int f, int threads, double* out) {
+  if (threads < 1) threads = 1;
+  size_t ff = (size_t)f * (size_t)f;
+  oro_gram_task* tasks = (oro_gram_task*)calloc((size_t)threads, sizeof(oro_gram_task));
+  pthread_t* tids = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)threads);
+  double* partial = (double*)malloc(sizeof(double) * ff * (size_t)threads);
+  int64_t per = (rows + threads - 1) / threads;
+  for (int i = 0; i < threads; i++) {
+    oro_gram_task* k = &tasks[i];
+    k->m = m; k->f = f; k->out = partial + ff * (size_t)i;
+    k->lo = (int64_t)i * per; k->hi = k->lo + per; if (k->hi > rows) k->hi = rows; if (k->lo > rows) k->lo = rows;
+    pthread_create(&tids[i], NULL, gram_worker, k);
+  }
+  memset(out, 0, sizeof(double) * ff);
+  for (int i = 0; i < threads; i++) {
+    pthread_join(tids[i], NULL);
+    const double* p = partial + ff * (size_t)i;
+    if (tasks[i].hi > tasks[i].lo)
+      for (size_t e = 0; e < ff; e++) out[e] += p[e];
+  }
+  free(partial); free(tasks); free(tids);
+}
+
 /* ------------------------------------------------------------------ "faithful" CPU baseline
  *
  * The second arm of the timed CPU baseline (variant i): not only the

@@ -106,6 +106,14 @@ SIGNATURES = {
 }
 
 
+# development aids exported by the library but not part of include/oryx_b200.h (timings for bench.py)
+DEBUG_SIGNATURES = {
+    "oryx_debug_batch_timings": [C.c_void_p, _f64p],
+    "oryx_debug_gram_ms": [C.c_void_p, _f64p],
+    "oryx_debug_fold_in_timings": [C.c_void_p, _f64p],
+}
+
+
 def lib() -> C.CDLL:
     """Load liboryx_b200.so.  There is no fallback: a missing library is an error."""
     global _lib
@@ -115,7 +123,7 @@ def lib() -> C.CDLL:
                 f"{_SO} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(or `make -C oryx_b200/csrc`).  oryx_b200 has no CPU fallback.")
         L = C.CDLL(_SO)
-        for name, argtypes in SIGNATURES.items():
+        for name, argtypes in list(SIGNATURES.items()) + list(DEBUG_SIGNATURES.items()):
             fn = getattr(L, name)
             fn.restype = C.c_int32
             fn.argtypes = argtypes
@@ -377,6 +385,20 @@ class Model:
         _check(lib().oryx_gram(self._h, which, _ptr(out, C.c_double), C.byref(used)))
         return (out if used.value > 0 else None), used.value
 
+    def debug_batch_timings(self) -> dict:
+        """Phase timings (device ms) of the last tensor-core batch answered for this model."""
+        t = np.zeros(9, dtype=np.float64)
+        _check(lib().oryx_debug_batch_timings(self._h, _ptr(t, C.c_double)))
+        keys = ("convert_ms", "score_ms", "threshold_ms", "refine_ms", "padded_flops", "cand_mean", "cand_max", "runs",
+                "shadow_rebuilds")
+        return dict(zip(keys, t.tolist()))
+
+    def debug_gram_ms(self) -> float:
+        """Device time (ms) of the last gram() on this model."""
+        t = np.zeros(1, dtype=np.float64)
+        _check(lib().oryx_debug_gram_ms(self._h, _ptr(t, C.c_double)))
+        return float(t[0])
+
     def stats(self) -> dict:
         s = _Stats()
         _check(lib().oryx_stats_get(self._h, C.byref(s)))
@@ -487,6 +509,12 @@ class Solver:
                                         _ptr(yi, C.c_float), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),
                                         _ptr(valid, C.c_uint8)))
         return out, valid
+
+    def debug_fold_in_timings(self) -> dict:
+        """Of this solver's last fold-in call: device ms of fold_in_kernel (all chunks), chunks, n, wall ms."""
+        t = np.zeros(4, dtype=np.float64)
+        _check(lib().oryx_debug_fold_in_timings(self._h, _ptr(t, C.c_double)))
+        return {"kernel_ms": float(t[0]), "chunks": int(t[1]), "n": int(t[2]), "wall_ms": float(t[3])}
 
     def fold_in_rows_sharded(self, models, xu_row_stride: int, yi_row_stride: int, implicit: bool, xu_which: int,
                              xu_rows, yi_rows, values):

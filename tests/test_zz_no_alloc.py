@@ -60,6 +60,28 @@ def test_static_scratch_matches_allocating_entry_point(lsh):
         rows, scores = m.topn(ob.DOT, queries[2], 10)
         got_rows, got_scores = _run(m.topn_device_static, ob.DOT, d_qs[2], 10, torch)
         assert np.array_equal(got_rows, rows) and np.array_equal(got_scores, scores)
+        # ... and straight against the CPU oracle (rows and binary64 scores bit-equal)
+        import oracle
+        part = oracle.lsh_index_rows(hv, y) if lsh else None
+        cand = oracle.lsh_candidates(hv.shape[0], bits, oracle.lsh_index(hv, queries[2])) if lsh else None
+        e_rows, e_scores = oracle.topn(oracle.DOT, queries[2], y, 10, part=part, cand=cand)
+        assert np.array_equal(got_rows, e_rows) and np.array_equal(got_scores, e_scores)
+        # The point of the entry point: it allocates nothing.  Outputs are created up front, then the
+        # device's free memory must read the same before and after a series of calls (any cudaMalloc,
+        # pooled or not, would lower it; nothing else runs in this process meanwhile).
+        dev = d_qs[0].device
+        d_rows = torch.zeros(10, dtype=torch.int32, device=dev)
+        d_scores = torch.zeros(10, dtype=torch.float64, device=dev)
+        d_n = torch.zeros(1, dtype=torch.int32, device=dev)
+        stream = torch.cuda.current_stream(dev)
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info(dev)
+        for d_q in d_qs * 3:
+            m.topn_device_static(ob.DOT, d_q.data_ptr(), 10, d_rows.data_ptr(), d_scores.data_ptr(), d_n.data_ptr(),
+                                 stream.cuda_stream)
+        stream.synchronize()
+        free_after, _ = torch.cuda.mem_get_info(dev)
+        assert free_after == free_before, (free_before, free_after)
 
 
 def test_static_scratch_rejects_oversized_requests():
