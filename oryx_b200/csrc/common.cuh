@@ -97,6 +97,11 @@ struct Store {
   // per 256-slot block: the partition shared by all its live rows, -1 if it has no live row, -2 if
   // mixed.  Lets an LSH-filtered scan skip or stream whole blocks without per-row metadata.
   int32_t* d_block_part = nullptr;
+  // Bit pattern of the largest |x| ever written into the store (non-negative floats order like their bit
+  // patterns).  Only grows: removals and overwrites leave it in place, which keeps it an upper bound --
+  // all the tensor-core Gram needs to pick its fixed-point scale (gram_tc.cu).  Written by the row
+  // scatter kernel; NaN never enters it, +inf does (and sends the Gram to the floating-point kernels).
+  unsigned int* d_absmax_bits = nullptr;
   int64_t cap_slots = 0;
   int64_t n_slots = 0;  // high-water mark
   int64_t live = 0;
@@ -254,6 +259,7 @@ struct Model {
   void* d_gram_scratch = nullptr;
   size_t gram_scratch_bytes = 0;
   std::atomic<double> last_gram_ms{0.0};
+  std::atomic<int> last_gram_tc{0};  // 1 when the last Gram came from the tensor-core kernel
 
   std::atomic<int64_t> queries{0};
   std::atomic<int64_t> launches{0};
@@ -345,7 +351,10 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
                        int query_store = ORYX_X);
 
 // gram.cu
-int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream);
+int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream, bool allow_tc = true,
+                    float* tc_absmax = nullptr);
+// gram_tc.cu: expected largest entry error of the tensor-core Gram relative to its largest entry
+double gram_tc_error_estimate(float absmax, double max_diag);
 
 // cudaFuncSetAttribute is per device: raises the kernel's dynamic shared-memory limit on the CURRENT
 // device if it has not been raised that far yet (api.cu).

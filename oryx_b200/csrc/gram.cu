@@ -235,11 +235,28 @@ int32_t gram_fast_launch(Model* m, Store* s, double* d_out, cudaStream_t stream)
   return ORYX_OK;
 }
 
-int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream) {
+// gram_tc.cu
+bool gram_tc_applicable(const Store* s);
+int32_t gram_tc_absmax(const Store* s, cudaStream_t stream, float* out);
+int32_t gram_tc_launch(Model* m, Store* s, double* d_out, cudaStream_t stream);
+
+// `allow_tc`: let large stores take the exact-sum tensor-core kernel (gram_tc.cu).  `*tc_absmax` (optional)
+// receives the store's largest |x| when that kernel ran and 0 otherwise, so the caller can check the
+// error estimate that goes with its fixed-point scale.
+int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream, bool allow_tc, float* tc_absmax) {
   Store* s = &m->store[which];
   const int F = s->features;
+  if (tc_absmax) *tc_absmax = 0.f;
   ORYX_CUDA(cudaMemsetAsync(d_out, 0, (size_t)F * F * sizeof(double), stream));
   if (s->n_slots == 0) return ORYX_OK;
+  if (allow_tc && gram_tc_applicable(s)) {
+    float absmax = 0.f;
+    ORYX_TRY(gram_tc_absmax(s, stream, &absmax));
+    if (absmax > 0.f && absmax < 3.0e38f) {  // a store holding +-inf goes to the floating-point kernels
+      if (tc_absmax) *tc_absmax = absmax;
+      return gram_tc_launch(m, s, d_out, stream);
+    }
+  }
   if (s->n_slots >= kGramFastMinRows) return gram_fast_launch(m, s, d_out, stream);
   const int nb = (F + kTile - 1) / kTile;
   const int n_blocks = nb * (nb + 1) / 2;

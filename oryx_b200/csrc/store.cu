@@ -25,7 +25,8 @@ __global__ void scatter_rows_kernel(const float* __restrict__ in, int64_t in_str
                                     int fpad, const int32_t* __restrict__ dst_slot,
                                     const int32_t* __restrict__ rows, const int32_t* __restrict__ parts,
                                     int64_t n, float* __restrict__ vec, int32_t* __restrict__ slot_row,
-                                    int32_t* __restrict__ slot_part, int32_t* __restrict__ row_slot) {
+                                    int32_t* __restrict__ slot_part, int32_t* __restrict__ row_slot,
+                                    unsigned int* __restrict__ absmax_bits) {
   int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (w >= n) return;
@@ -33,7 +34,16 @@ __global__ void scatter_rows_kernel(const float* __restrict__ in, int64_t in_str
   if (slot < 0) return;  // superseded by a later occurrence of the same row in this batch
   const float* src = in + w * in_stride;
   float* dst = vec + (int64_t)slot * fpad;
-  for (int j = lane; j < fpad; j += 32) dst[j] = j < features ? src[j] : 0.0f;
+  float amax = 0.f;
+  for (int j = lane; j < fpad; j += 32) {
+    const float v = j < features ? src[j] : 0.0f;
+    dst[j] = v;
+    amax = fmaxf(amax, fabsf(v));  // fmaxf drops NaN
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  // the running maximum settles after the first few rows: nearly every warp only reads it
+  if (lane == 0 && __float_as_uint(amax) > *(volatile unsigned int*)absmax_bits) atomicMax(absmax_bits, __float_as_uint(amax));
   if (lane == 0) {
     slot_row[slot] = rows[w];
     slot_part[slot] = parts ? parts[w] : 0;
@@ -308,13 +318,16 @@ int32_t store_init(Model* m, int which, int64_t capacity_hint) {
   s->fpad = round_up(m->cfg.features, 4);
   s->hashed = (which == ORYX_Y) && m->num_hashes > 0;
   s->track_row_slot = which == ORYX_Y;
+  ORYX_CUDA(cudaMalloc(&s->d_absmax_bits, sizeof(unsigned int)));
+  ORYX_CUDA(cudaMemset(s->d_absmax_bits, 0, sizeof(unsigned int)));
   if (capacity_hint > 0) ORYX_TRY(grow(m, s, capacity_hint));
   return ORYX_OK;
 }
 
 void store_free(Store* s) {
   cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(s->d_block_part);
-  cudaFree(s->d_row_slot);
+  cudaFree(s->d_row_slot); cudaFree(s->d_absmax_bits);
+  s->d_absmax_bits = nullptr;
   s->d_vec = nullptr; s->d_slot_row = nullptr; s->d_slot_part = nullptr; s->d_block_part = nullptr;
   s->d_row_slot = nullptr; s->row_slot_cap = 0;
   s->cap_slots = s->n_slots = s->live = 0;
@@ -354,7 +367,7 @@ int32_t store_upsert(Model* m, int which, const int32_t* rows, const float* vecs
     int64_t blocks = (c * 32 + threads - 1) / threads;
     scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
         g.d_vec, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
-        s->d_slot_row, s->d_slot_part, s->d_row_slot);
+        s->d_slot_row, s->d_slot_part, s->d_row_slot, s->d_absmax_bits);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
     if (shadow_ok) shadow_ok = batch_shadow_rows_changed(m, d_dst, c, version_before, st);
@@ -398,7 +411,7 @@ int32_t store_upsert_device(Model* m, int which, int32_t first_row, const float*
     int64_t blocks = (c * 32 + threads - 1) / threads;
     scatter_rows_kernel<<<(unsigned)blocks, threads, 0, st>>>(
         src, F, F, s->fpad, d_dst, d_rows, s->hashed ? d_parts : nullptr, c, s->d_vec,
-        s->d_slot_row, s->d_slot_part, s->d_row_slot);
+        s->d_slot_row, s->d_slot_part, s->d_row_slot, s->d_absmax_bits);
     m->launches++;
     ORYX_CUDA(cudaGetLastError());
     if (shadow_ok) shadow_ok = batch_shadow_rows_changed(m, d_dst, c, version_before, st);

@@ -395,9 +395,13 @@ class Model:
 
     def debug_gram_ms(self) -> float:
         """Device time (ms) of the last gram() on this model."""
-        t = np.zeros(1, dtype=np.float64)
+        return self.debug_gram()[0]
+
+    def debug_gram(self):
+        """(device ms of the last gram(), True when the tensor-core kernel produced it)."""
+        t = np.zeros(2, dtype=np.float64)
         _check(lib().oryx_debug_gram_ms(self._h, _ptr(t, C.c_double)))
-        return float(t[0])
+        return float(t[0]), bool(t[1])
 
     def stats(self) -> dict:
         s = _Stats()

@@ -394,8 +394,6 @@ def test_cross_shard_merge_kernels():
         assert np.array_equal(o_rows.cpu().numpy(), e_rows) and np.array_equal(o_scores.cpu().numpy(), e_scores)
 
 
-@pytest.mark.parametrize("n,f,nq,how_many", [(20000, 128, 64, 10), (9000, 50, 130, 100), (33000, 256, 40, 10),
-                                             (5000, 64, 32, 1)])
 def _batch_counters(m):
     """(batches answered by the tcgen05 path, full bf16 conversions of Y) of a model so far."""
     import ctypes as C
@@ -408,6 +406,8 @@ def _batch_counters(m):
     return int(t[7]), int(t[8])
 
 
+@pytest.mark.parametrize("n,f,nq,how_many", [(20000, 128, 64, 10), (9000, 50, 130, 100), (33000, 256, 40, 10),
+                                             (5000, 64, 32, 1)])
 def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
     """oryx_topn_batch (tcgen05 scoring + exact pruning/refinement) == one exact topN per query."""
     y = random_model(n, f, seed=n + 7 * f)
@@ -479,6 +479,58 @@ def test_gram_large_store_fast_path(n, f):
         assert used == n - 2
         assert np.max(np.abs(g - exp)) <= 1e-8 * np.max(np.abs(exp))
         assert np.array_equal(g, g.T)
+
+
+@pytest.mark.parametrize("n,f", [(1_100_000, 256), (1_048_576 + 777, 200), (1_200_000, 128)])
+def test_gram_tensor_core_path(n, f):
+    """Stores of >= 2^20 rows with 128..256 padded features take the exact-sum tcgen05 kernel (int8 digit
+    planes, int32 TMEM accumulators).  Against the oracle's float-multiply / double-accumulate Gram the only
+    difference is the 24-bit fixed-point quantisation of the inputs: tolerance 1e-8 relative to the largest
+    entry (the bound the floating-point large-store kernel is held to); the result is exactly symmetric and
+    tombstones contribute nothing."""
+    import os
+    y = random_model(n, f, seed=n + f) * 0.3
+    gone = np.array([5, 60000, n - 1, n // 2], dtype=np.int32)
+    with ob.Model(f, capacity_hint=n) as m:
+        for off in range(0, n, 250_000):
+            m.upsert(ob.Y, np.arange(off, min(n, off + 250_000), dtype=np.int32), y[off:off + 250_000])
+        m.remove(ob.Y, gone)
+        g, used = m.gram(ob.Y)
+        ms, on_tensor_cores = m.debug_gram()
+        assert on_tensor_cores, "the large store did not take the tensor-core Gram"
+        assert used == n - len(gone)
+        keep = np.ones(n, bool)
+        keep[gone] = False
+        exp = oracle.transpose_times_self_mt(y[keep], os.cpu_count() or 4)
+        err = np.max(np.abs(g - exp)) / np.max(np.abs(exp))
+        assert err <= 1e-8, err
+        assert np.array_equal(g, g.T)
+        # a second call (partials and counters are reused) gives the same matrix up to the order in which
+        # the CTAs' binary64 partials were formed
+        g2, _ = m.gram(ob.Y)
+        assert np.max(np.abs(g2 - g)) <= 1e-13 * np.max(np.abs(g))
+
+
+def test_gram_tensor_core_falls_back_on_heavy_tails():
+    """One huge outlier sets the fixed-point scale so coarse that the error estimate of the tensor-core Gram
+    exceeds its tolerance: oryx_gram must then answer from the floating-point kernel."""
+    import os
+    n, f = 1_050_000, 128
+    y = random_model(n, f, seed=77) * 0.1
+    y[12345, 7] = 3.0e4
+    with ob.Model(f, capacity_hint=n) as m:
+        for off in range(0, n, 350_000):
+            m.upsert(ob.Y, np.arange(off, min(n, off + 350_000), dtype=np.int32), y[off:off + 350_000])
+        g, _ = m.gram(ob.Y)
+        assert not m.debug_gram()[1]
+        # off the outlier's row and column the entries must still be accurate to the usual tolerance of the
+        # floating-point kernel, measured against the largest of THOSE entries
+        exp = oracle.transpose_times_self_mt(y, os.cpu_count() or 4)
+        sel = np.ones(f, bool)
+        sel[7] = False
+        sub, esub = g[np.ix_(sel, sel)], exp[np.ix_(sel, sel)]
+        assert np.max(np.abs(sub - esub)) <= 1e-7 * np.max(np.abs(esub))
+        assert abs(g[7, 7] - exp[7, 7]) <= 1e-7 * exp[7, 7]
 
 
 def test_fold_in_rows_equals_host_buffer_path():
