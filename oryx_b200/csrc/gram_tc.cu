@@ -46,19 +46,24 @@ constexpr int kKStep = 32;        // rows per tcgen05.mma kind::i8 instruction (
 constexpr int kBlk = 128;         // features per block: UMMA M, and the N of one block
 constexpr int kUnitRows = 2048;   // rows per scheduled work unit
 constexpr int kDrainRows = 32768; // rows accumulated in int32 between drains (<= 2^31 / (3 * 2^14) = 43690)
-constexpr int kConvWarps = 8;
-constexpr int kThreads = 64 + kConvWarps * 32;  // warp 0: TMA, warp 1: MMA + TMEM, warps 2..9: convert / drain
+constexpr int kConvGroups = 4;     // converter groups: group k converts tiles k, k + 4, ... into operand slot k
+constexpr int kGroupWarps = 4;
+constexpr int kConvWarps = kConvGroups * kGroupWarps;
+constexpr int kThreads = 64 + kConvWarps * 32;  // warp 0: TMA, warp 1: MMA + TMEM, warps 2..17: convert / drain
 constexpr int kHalfStageBytes = kKStep * kBlk * 4;  // 16 KB: 32 rows x 128 fp32
 constexpr int kTileBytes = kBlk * 128;              // 16 KB: 128 feature rows x 128 K-bytes (4 K-steps)
 constexpr int kOpRing = 4;                          // K-step slots in an operand tile
 constexpr int kMaxStages = 8;
 constexpr uint32_t kOperandBytes = 6 * kTileBytes;  // 96 KB (diagonal roles use the first 48 KB)
-constexpr uint32_t kStagingBytes = 6 * kHalfStageBytes;  // 96 KB: 3 stages x 2 halves, or 6 stages x 1 half
+constexpr uint32_t kStagingBytes = 8 * kHalfStageBytes;  // 128 KB: 4 stages x 2 halves, or 8 stages x 1 half
 constexpr size_t kSmemBytes = 1024 + kOperandBytes + kStagingBytes + 1024;
 constexpr float kScaleTop = 8388608.0f - 65536.0f;  // |x| * scale <= 2^23 - 2^16
 constexpr int kDigitOffset = 32768 + 128;           // makes the two low bytes balanced digits after ^ 0x80
 
-constexpr int kFlagDrain = 1, kFlagEnd = 2;
+// kFlagDrain: after this tile's MMAs the accumulators are drained (issuer and converters); kFlagJoin: the
+// converters of this tile take part in a drain flagged on one of the three tiles before it.
+// kFlagIdle (on end markers): nothing has been accumulated since the last drain, so there is no final drain.
+constexpr int kFlagDrain = 1, kFlagEnd = 2, kFlagJoin = 4, kFlagIdle = 8;
 enum { kRoleD0 = 0, kRoleD1 = 1, kRoleO = 2 };
 
 struct GramTcParams {
@@ -72,6 +77,7 @@ struct GramTcParams {
   uint8_t role_of[256];
   unsigned int n_units;
   unsigned int window_units;
+  int drain_rows;          // rows accumulated in int32 between drains (kDrainRows; tests lower it)
   unsigned int* counters;  // [4], zeroed before the launch
   const unsigned int* absmax_bits;
   double* partials;        // [grid][2][128 x 128], element (i, j) at [j * 128 + i]
@@ -149,13 +155,10 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// |x| * scale rounded to the nearest integer (exact in the binary32 mantissa), sign restored, offset so
-// that the two low bytes become balanced digits: result = d0 * 65536 + (s1 + 128) * 256 + (s2 + 128).
-__device__ __forceinline__ int quantise(float x, float scale) {
-  const float t = fmaf(fabsf(x), scale, 8388608.0f);
-  const int m = __float_as_int(t) - 0x4B000000;
-  const int sg = __float_as_int(x) >> 31;
-  return ((m ^ sg) - sg) + kDigitOffset;
+// x * scale rounded to an integer, offset so that the two low bytes become balanced digits:
+// result = d0 * 65536 + (s1 + 128) * 256 + (s2 + 128) with d0 the (signed) third byte.
+__device__ __forceinline__ uint32_t quantise(float x, float scale) {
+  return (uint32_t)__float2int_rn(fmaf(x, scale, (float)kDigitOffset));
 }
 
 __device__ __forceinline__ float gram_scale(const unsigned int* absmax_bits) {
@@ -184,13 +187,13 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
   const int bid = blockIdx.x;
   const int role = p.role_of[bid];
   const int halves = role == kRoleO ? 2 : 1;
-  const int n_stages = role == kRoleO ? 3 : 6;
+  const int n_stages = role == kRoleO ? 4 : 8;
   const int col_a = role == kRoleD1 ? kBlk : 0;  // first column of the A-side block (the B side of (0,1) is 128)
 
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm) : "memory");
-    for (int i = 0; i < kMaxStages; i++) { mbar_init(&stage_full[i], 1); mbar_init(&stage_empty[i], kConvWarps); }
-    for (int i = 0; i < kOpRing; i++) { mbar_init(&op_full[i], kConvWarps); mbar_init(&op_empty[i], 1); }
+    for (int i = 0; i < kMaxStages; i++) { mbar_init(&stage_full[i], 1); mbar_init(&stage_empty[i], kGroupWarps); }
+    for (int i = 0; i < kOpRing; i++) { mbar_init(&op_full[i], kGroupWarps); mbar_init(&op_empty[i], 1); }
     mbar_init(acc_full, 1);
     mbar_init(acc_empty, kConvWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -208,7 +211,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
     // ===== producer: work units, liveness masks, TMA =====
     int stage = 0;
     uint32_t sphase = 0;
-    int rows_since_drain = 0;
+    int rows_since_drain = 0, join_left = 0;
     for (;;) {
       unsigned int u = 0;
       if (lane == 0) u = atomicAdd(&p.counters[role], 1u);
@@ -248,7 +251,8 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
             mbar_wait(&stage_empty[stage], sphase ^ 1u);
             rows_since_drain += kKStep;
             int flags = 0;
-            if (rows_since_drain >= kDrainRows) { flags = kFlagDrain; rows_since_drain = 0; }
+            if (join_left > 0) { flags = kFlagJoin; join_left--; }
+            if (rows_since_drain >= p.drain_rows) { flags |= kFlagDrain; rows_since_drain = 0; join_left = kConvGroups - 1; }
             meta[stage].row0 = row0;
             meta[stage].alive = alive;
             meta[stage].flags = flags;
@@ -263,12 +267,16 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
         for (int t = 0; t < 4; t++) cur[t] = nxt[t];
       }
     }
-    if (lane == 0) {  // end marker: no data behind it
-      mbar_wait(&stage_empty[stage], sphase ^ 1u);
-      meta[stage].row0 = 0;
-      meta[stage].alive = 0;
-      meta[stage].flags = kFlagEnd;
-      mbar_arrive(&stage_full[stage]);
+    if (lane == 0) {  // end markers, one per converter group: no data behind them
+      for (int k = 0; k < kConvGroups; k++) {
+        mbar_wait(&stage_empty[stage], sphase ^ 1u);
+        meta[stage].row0 = 0;
+        meta[stage].alive = 0;
+        meta[stage].flags = kFlagEnd | (join_left > 0 ? kFlagJoin : 0) | (rows_since_drain == 0 ? kFlagIdle : 0);
+        if (join_left > 0) join_left--;
+        mbar_arrive(&stage_full[stage]);
+        if (++stage == n_stages) { stage = 0; sphase ^= 1u; }
+      }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
@@ -318,17 +326,22 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
     }
   } else {
     // ===== converters: fp32 tile -> digit planes in the tensor core's operand layout; TMEM drains =====
-    const int cw = warp - 2;                  // 0..7
-    const int col = 32 * (cw & 3) + lane;     // column of the 128-column half this thread converts
-    const int rg_hi = cw >> 2;                // which 16 of the 32 rows
+    // Four groups of four warps; group k converts tiles k, k + 4, ... into K-step slot k of the operand tiles,
+    // so four tiles are in flight and the wait -> load -> convert -> store -> fence -> arrive latency of one
+    // tile overlaps the others'.  A 32-row x 128-column tile is 8 row groups (4 rows = one 32-bit word of K
+    // bytes) x 128 columns; a warp takes 32 columns.  In pass q lane l handles row group ((l >> 3) + q) & 3 of
+    // each half of the rows, so the 32 lanes read 32 different banks of the fp32 tile (column = lane) and
+    // write 32 different banks of the swizzled operand rows (8 chunk positions x 4 words).
+    const int cw = warp - 2;                  // 0..15
+    const int group = cw >> 2, wig = cw & 3;
+    const int col = 32 * wig + lane;          // column of the 128-column half this thread converts
     const uint32_t r8 = (uint32_t)col & 7u;
     const uint32_t row_off = ((uint32_t)col >> 3) * 1024u + r8 * 128u;  // start of this feature's 128-byte row
     const float scale = gram_scale(p.absmax_bits);
     double* part = p.partials + (size_t)bid * 2 * kBlk * kBlk;
-    int stage = 0, slot = 0;
-    uint32_t sphase = 0, ophase = 0, aphase = 0;
+    const int slot = group;
+    uint32_t aphase = 0;
     bool first_drain = true;
-    int pending_rows = 0;
 
     auto drain = [&]() {
       mbar_wait(acc_full, aphase);
@@ -336,10 +349,10 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
       tcgen05_fence_after();
       const int lq = warp & 3;                 // TMEM lane quarter this warp may read
       const int i = 32 * lq + lane;            // row of the block (A-side feature)
-      const int j_base = 64 * (cw >> 2);       // two warps share a quarter: 64 columns each
+      const int j_base = 32 * (cw >> 2);       // four warps share a quarter: 32 columns each
       const uint32_t t0 = tmem_base + ((uint32_t)(32 * lq) << 16);
 #pragma unroll 1
-      for (int jc = 0; jc < 4; jc++) {
+      for (int jc = 0; jc < 2; jc++) {
         const int j0 = j_base + 16 * jc;
         uint32_t a0[16], a1[16], a2[16], a3[16];
         tmem_ld_32x32b_x16(t0 + 0 + (uint32_t)j0, a0);
@@ -363,71 +376,68 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
         }
       }
       first_drain = false;
-      pending_rows = 0;
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty);
     };
 
-    for (;;) {
-      mbar_wait(&stage_full[stage], sphase);
+    for (int i = group;; i += kConvGroups) {
+      const int stage = i % n_stages;
+      mbar_wait(&stage_full[stage], (uint32_t)(i / n_stages) & 1u);
       const int flags = *(volatile int32_t*)&meta[stage].flags;
       const uint32_t alive = *(volatile uint32_t*)&meta[stage].alive;
-      mbar_wait(&op_empty[slot], ophase ^ 1u);
+      mbar_wait(&op_empty[slot], ((uint32_t)(i / kOpRing) & 1u) ^ 1u);
       if (flags & kFlagEnd) {
-        if (cw == 0 && lane == 0) *(volatile int32_t*)&op_meta[slot] = kFlagEnd;
+        if (wig == 0 && lane == 0) *(volatile int32_t*)&op_meta[slot] = flags;
         __syncwarp();
         if (lane == 0) mbar_arrive(&op_full[slot]);
-        // the issuer answers with a commit on acc_full; drain what has accumulated since the last drain
-        if (pending_rows > 0) {
-          drain();
-        } else {
-          mbar_wait(acc_full, aphase);
-        }
+        if (flags & kFlagJoin) drain();
+        // the issuer answers its first end marker with a last commit on acc_full; when nothing was issued
+        // since the last drain the accumulators still hold what that drain already took: leave them alone
+        if (!(flags & kFlagIdle)) drain();
         break;
       }
       const float* src0 = reinterpret_cast<const float*>(staging + (size_t)stage * halves * kHalfStageBytes);
+      // byte offset of this K-step's words inside the swizzled 128-byte row: 16-byte chunk (2 slot + rg_hi) ^ r8
+      const uint32_t chunk0 = ((((uint32_t)(2 * slot)) ^ r8) & 7u) << 4, chunk1 = ((((uint32_t)(2 * slot + 1)) ^ r8) & 7u) << 4;
+      auto convert = [&](const float* src, int rg, unsigned char* dst) {
+        float x0 = src[(4 * rg + 0) * kBlk], x1 = src[(4 * rg + 1) * kBlk];
+        float x2 = src[(4 * rg + 2) * kBlk], x3 = src[(4 * rg + 3) * kBlk];
+        if (alive != 0xffffffffu) {  // tombstones are NaN rows: they contribute nothing
+          const uint32_t m4 = alive >> (4 * rg);
+          x0 = (m4 & 1u) ? x0 : 0.f;
+          x1 = (m4 & 2u) ? x1 : 0.f;
+          x2 = (m4 & 4u) ? x2 : 0.f;
+          x3 = (m4 & 8u) ? x3 : 0.f;
+        }
+        const uint32_t v0 = quantise(x0, scale), v1 = quantise(x1, scale);
+        const uint32_t v2 = quantise(x2, scale), v3 = quantise(x3, scale);
+        // bytes of four consecutive rows, per digit: byte 2 -> d0, byte 1 -> s1 + 128, byte 0 -> s2 + 128
+        const uint32_t lo01 = __byte_perm(v0, v1, 0x5140), lo23 = __byte_perm(v2, v3, 0x5140);
+        const uint32_t hi01 = __byte_perm(v0, v1, 0x0062), hi23 = __byte_perm(v2, v3, 0x0062);
+        *reinterpret_cast<uint32_t*>(dst) = __byte_perm(hi01, hi23, 0x5410);
+        *reinterpret_cast<uint32_t*>(dst + kTileBytes) = __byte_perm(lo01, lo23, 0x7632) ^ 0x80808080u;
+        *reinterpret_cast<uint32_t*>(dst + 2 * kTileBytes) = __byte_perm(lo01, lo23, 0x5410) ^ 0x80808080u;
+      };
       for (int h = 0; h < halves; h++) {
         const float* src = src0 + h * (kKStep * kBlk) + col;
         unsigned char* t_d0 = op + (size_t)(h * 3) * kTileBytes + row_off;
 #pragma unroll
-        for (int it = 0; it < 4; it++) {
-          const int rg = 4 * rg_hi + (((lane >> 3) + it) & 3);  // rows 4 rg .. 4 rg + 3 of the tile
-          float x0 = src[(4 * rg + 0) * kBlk], x1 = src[(4 * rg + 1) * kBlk];
-          float x2 = src[(4 * rg + 2) * kBlk], x3 = src[(4 * rg + 3) * kBlk];
-          const uint32_t m4 = (alive >> (4 * rg)) & 15u;
-          if (m4 != 15u) {  // tombstones are NaN rows: they contribute nothing
-            x0 = (m4 & 1u) ? x0 : 0.f;
-            x1 = (m4 & 2u) ? x1 : 0.f;
-            x2 = (m4 & 4u) ? x2 : 0.f;
-            x3 = (m4 & 8u) ? x3 : 0.f;
-          }
-          const uint32_t v0 = (uint32_t)quantise(x0, scale), v1 = (uint32_t)quantise(x1, scale);
-          const uint32_t v2 = (uint32_t)quantise(x2, scale), v3 = (uint32_t)quantise(x3, scale);
-          // bytes of four consecutive rows, per digit: byte 2 -> d0, byte 1 -> s1 + 128, byte 0 -> s2 + 128
-          const uint32_t lo01 = __byte_perm(v0, v1, 0x5140), lo23 = __byte_perm(v2, v3, 0x5140);
-          const uint32_t hi01 = __byte_perm(v0, v1, 0x0062), hi23 = __byte_perm(v2, v3, 0x0062);
-          const uint32_t w_s2 = __byte_perm(lo01, lo23, 0x5410) ^ 0x80808080u;
-          const uint32_t w_s1 = __byte_perm(lo01, lo23, 0x7632) ^ 0x80808080u;
-          const uint32_t w_d0 = __byte_perm(hi01, hi23, 0x5410);
-          const uint32_t kb = (uint32_t)slot * kKStep + 4u * (uint32_t)rg;  // K-byte inside the 128-byte row
-          const uint32_t off = ((((kb >> 4) ^ r8) & 7u) << 4) + (kb & 15u);
-          *reinterpret_cast<uint32_t*>(t_d0 + off) = w_d0;
-          *reinterpret_cast<uint32_t*>(t_d0 + kTileBytes + off) = w_s1;
-          *reinterpret_cast<uint32_t*>(t_d0 + 2 * kTileBytes + off) = w_s2;
+        for (int q = 0; q < 4; q++) {
+          const int rgl = ((lane >> 3) + q) & 3;
+          convert(src, rgl, t_d0 + chunk0 + 4 * rgl);          // rows 0..15
+          convert(src, 4 + rgl, t_d0 + chunk1 + 4 * rgl);      // rows 16..31
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // these stores are read by the tensor core
-      if (cw == 0 && lane == 0) *(volatile int32_t*)&op_meta[slot] = flags;
+      if (wig == 0 && lane == 0) *(volatile int32_t*)&op_meta[slot] = flags;
       __syncwarp();
       if (lane == 0) {
         mbar_arrive(&op_full[slot]);
         mbar_arrive(&stage_empty[stage]);
       }
-      pending_rows += kKStep;
+      if (flags & kFlagJoin) drain();
       if (flags & kFlagDrain) drain();
-      if (++stage == n_stages) { stage = 0; sphase ^= 1u; }
-      if (++slot == kOpRing) { slot = 0; ophase ^= 1u; }
     }
     if (cw == 0 && lane == 0) p.contributed[bid] = first_drain ? 0 : 1;
   }
@@ -549,6 +559,11 @@ int32_t gram_tc_launch(Model* m, Store* s, double* d_out, cudaStream_t stream) {
   }
   p.n_units = (unsigned int)((s->n_slots + kUnitRows - 1) / kUnitRows);
   p.window_units = 24;  // 24 x 2048 rows x 1 KB = 48 MB of the 126 MB L2
+  p.drain_rows = kDrainRows;
+  if (const char* e = std::getenv("ORYX_GRAM_TC_DRAIN_ROWS")) {  // test hook: exercise the drain protocol on small stores
+    const int v = std::atoi(e);
+    if (v >= kKStep && v <= kDrainRows) p.drain_rows = v / kKStep * kKStep;
+  }
   const size_t head = 256 + (size_t)grid * sizeof(int32_t);
   const size_t head_pad = (head + 255) & ~(size_t)255;
   const size_t need = head_pad + (size_t)grid * 2 * kBlk * kBlk * sizeof(double);

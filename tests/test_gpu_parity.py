@@ -509,6 +509,18 @@ def test_gram_tensor_core_path(n, f):
         # the CTAs' binary64 partials were formed
         g2, _ = m.gram(ob.Y)
         assert np.max(np.abs(g2 - g)) <= 1e-13 * np.max(np.abs(g))
+        # The int32 accumulators are drained every 32768 rows per CTA, which a store of this size never
+        # reaches.  Lower the interval so that every CTA drains many times -- including intervals that end
+        # exactly where a CTA's work ends (2048-row units) -- and the protocol is covered here too.
+        for drain_rows in (2048, 4096, 1024, 6144):
+            os.environ["ORYX_GRAM_TC_DRAIN_ROWS"] = str(drain_rows)
+            try:
+                for _ in range(2):
+                    g3, _ = m.gram(ob.Y)
+                    assert m.debug_gram()[1]
+                    assert np.max(np.abs(g3 - g)) <= 1e-13 * np.max(np.abs(g)), drain_rows
+            finally:
+                del os.environ["ORYX_GRAM_TC_DRAIN_ROWS"]
 
 
 def test_gram_tensor_core_falls_back_on_heavy_tails():
