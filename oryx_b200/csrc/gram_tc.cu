@@ -166,7 +166,7 @@ __device__ __forceinline__ float gram_scale(const unsigned int* absmax_bits) {
   return absmax > 0.f ? __fdiv_rd(kScaleTop, absmax) : 0.f;
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 1)  // 18 warps = 5 on one scheduler: 96 registers per thread at most
 gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ GramTcParams p) {
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -328,10 +328,9 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
     // ===== converters: fp32 tile -> digit planes in the tensor core's operand layout; TMEM drains =====
     // Four groups of four warps; group k converts tiles k, k + 4, ... into K-step slot k of the operand tiles,
     // so four tiles are in flight and the wait -> load -> convert -> store -> fence -> arrive latency of one
-    // tile overlaps the others'.  A 32-row x 128-column tile is 8 row groups (4 rows = one 32-bit word of K
-    // bytes) x 128 columns; a warp takes 32 columns.  In pass q lane l handles row group ((l >> 3) + q) & 3 of
-    // each half of the rows, so the 32 lanes read 32 different banks of the fp32 tile (column = lane) and
-    // write 32 different banks of the swizzled operand rows (8 chunk positions x 4 words).
+    // tile overlaps the others'.  A thread owns one column of the 32-row x 128-column tile: its 32 values
+    // become 8 words per digit plane (4 rows = one 32-bit word of K bytes), i.e. two 16-byte chunks of that
+    // feature's swizzled operand row.
     const int cw = warp - 2;                  // 0..15
     const int group = cw >> 2, wig = cw & 3;
     const int col = 32 * wig + lane;          // column of the 128-column half this thread converts
@@ -397,36 +396,38 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ G
         if (!(flags & kFlagIdle)) drain();
         break;
       }
-      const float* src0 = reinterpret_cast<const float*>(staging + (size_t)stage * halves * kHalfStageBytes);
-      // byte offset of this K-step's words inside the swizzled 128-byte row: 16-byte chunk (2 slot + rg_hi) ^ r8
+      // 16-byte chunks of this K-step inside the swizzled 128-byte row: rows 0..15 and rows 16..31
       const uint32_t chunk0 = ((((uint32_t)(2 * slot)) ^ r8) & 7u) << 4, chunk1 = ((((uint32_t)(2 * slot + 1)) ^ r8) & 7u) << 4;
-      auto convert = [&](const float* src, int rg, unsigned char* dst) {
-        float x0 = src[(4 * rg + 0) * kBlk], x1 = src[(4 * rg + 1) * kBlk];
-        float x2 = src[(4 * rg + 2) * kBlk], x3 = src[(4 * rg + 3) * kBlk];
-        if (alive != 0xffffffffu) {  // tombstones are NaN rows: they contribute nothing
-          const uint32_t m4 = alive >> (4 * rg);
-          x0 = (m4 & 1u) ? x0 : 0.f;
-          x1 = (m4 & 2u) ? x1 : 0.f;
-          x2 = (m4 & 4u) ? x2 : 0.f;
-          x3 = (m4 & 8u) ? x3 : 0.f;
-        }
-        const uint32_t v0 = quantise(x0, scale), v1 = quantise(x1, scale);
-        const uint32_t v2 = quantise(x2, scale), v3 = quantise(x3, scale);
-        // bytes of four consecutive rows, per digit: byte 2 -> d0, byte 1 -> s1 + 128, byte 0 -> s2 + 128
-        const uint32_t lo01 = __byte_perm(v0, v1, 0x5140), lo23 = __byte_perm(v2, v3, 0x5140);
-        const uint32_t hi01 = __byte_perm(v0, v1, 0x0062), hi23 = __byte_perm(v2, v3, 0x0062);
-        *reinterpret_cast<uint32_t*>(dst) = __byte_perm(hi01, hi23, 0x5410);
-        *reinterpret_cast<uint32_t*>(dst + kTileBytes) = __byte_perm(lo01, lo23, 0x7632) ^ 0x80808080u;
-        *reinterpret_cast<uint32_t*>(dst + 2 * kTileBytes) = __byte_perm(lo01, lo23, 0x5410) ^ 0x80808080u;
-      };
       for (int h = 0; h < halves; h++) {
-        const float* src = src0 + h * (kKStep * kBlk) + col;
         unsigned char* t_d0 = op + (size_t)(h * 3) * kTileBytes + row_off;
+        const float* src = reinterpret_cast<const float*>(staging + ((size_t)stage * halves + h) * kHalfStageBytes) + col;
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          const int rgl = ((lane >> 3) + q) & 3;
-          convert(src, rgl, t_d0 + chunk0 + 4 * rgl);          // rows 0..15
-          convert(src, 4 + rgl, t_d0 + chunk1 + 4 * rgl);      // rows 16..31
+        for (int hh = 0; hh < 2; hh++) {  // rows 0..15, rows 16..31 of this thread's column
+          float x[16];
+#pragma unroll
+          for (int r = 0; r < 16; r++) x[r] = src[(16 * hh + r) * kBlk];  // lanes = consecutive columns: one wavefront
+          const uint32_t alive16 = (alive >> (16 * hh)) & 0xffffu;
+          if (alive16 != 0xffffu) {  // tombstones are NaN rows: they contribute nothing
+#pragma unroll
+            for (int r = 0; r < 16; r++) x[r] = ((alive16 >> r) & 1u) ? x[r] : 0.f;
+          }
+          uint32_t wd[4], w1[4], w2[4];
+#pragma unroll
+          for (int g4 = 0; g4 < 4; g4++) {
+            const uint32_t v0 = quantise(x[4 * g4 + 0], scale), v1 = quantise(x[4 * g4 + 1], scale);
+            const uint32_t v2 = quantise(x[4 * g4 + 2], scale), v3 = quantise(x[4 * g4 + 3], scale);
+            // bytes of four consecutive rows, per digit: byte 2 -> d0, byte 1 -> s1 + 128, byte 0 -> s2 + 128
+            const uint32_t lo01 = __byte_perm(v0, v1, 0x5140), lo23 = __byte_perm(v2, v3, 0x5140);
+            const uint32_t hi01 = __byte_perm(v0, v1, 0x0062), hi23 = __byte_perm(v2, v3, 0x0062);
+            wd[g4] = __byte_perm(hi01, hi23, 0x5410);
+            w1[g4] = __byte_perm(lo01, lo23, 0x7632) ^ 0x80808080u;
+            w2[g4] = __byte_perm(lo01, lo23, 0x5410) ^ 0x80808080u;
+          }
+          // 128-bit stores: a quarter warp (8 consecutive features = one swizzle atom) covers all 32 banks
+          const uint32_t chunk = hh == 0 ? chunk0 : chunk1;
+          *reinterpret_cast<uint4*>(t_d0 + chunk) = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+          *reinterpret_cast<uint4*>(t_d0 + kTileBytes + chunk) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
+          *reinterpret_cast<uint4*>(t_d0 + 2 * kTileBytes + chunk) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // these stores are read by the tensor core
