@@ -209,11 +209,23 @@ struct ScoreSmem {
   }
 };
 
-template <int NCH>
+// LSH filtering (template flag): query q only competes for rows whose partition p satisfies
+// popcount(p ^ main_q) <= max_bits (LocalitySensitiveHash.getCandidateIndices, LSH.java:156-177).  Y tiles are
+// the store's 256-slot blocks, so block_part says per tile whether all live rows share one partition
+// (one test per query and tile; non-candidate tiles are not even read back from TMEM), hold no live row, or
+// are mixed (-2: per-row test against slot_part).  After oryx_items_compact nearly every tile is pure.
+struct BatchLsh {
+  const int32_t* block_part;
+  const int32_t* slot_part;
+  const int32_t* qmain;  // [nq_pad] LSH index of every query
+  int max_bits;
+};
+
+template <int NCH, bool LSH>
 __global__ void __launch_bounds__(kScoreThreads, 1)
 batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_y,
                    int n_qtiles, int n_ytiles, int64_t n_slots, float* __restrict__ bmax, int64_t bmax_stride,
-                   float* __restrict__ tmax, int64_t tmax_stride) {
+                   float* __restrict__ tmax, int64_t tmax_stride, const BatchLsh lsh) {
   constexpr int YB = (NCH <= 2) ? 2 : 1;  // double-buffer the resident Y tile when it fits
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
@@ -313,12 +325,24 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     for (int t = blockIdx.x; t < n_ytiles; t += gridDim.x) {
       const int64_t col0 = (int64_t)t * BN;
       const bool ragged = col0 + BN > n_slots;
+      const int bp = LSH ? __ldg(lsh.block_part + t) : 0;
       for (int qt = 0; qt < n_qtiles; qt++, acc_it++) {
         const int acc = acc_it & 1;
         const uint32_t aph = (uint32_t)(acc_it >> 1) & 1u;
         mbar_wait(&t_full[acc], aph);
         tcgen05_fence_after();
         float mx[SUBS_PER_TILE];
+        int main_q = 0;
+        bool q_cand = true;  // may this thread's query see this tile at all?
+        if (LSH) {
+          main_q = __ldg(lsh.qmain + (int64_t)qt * BM + w4 * 32 + lane);
+          q_cand = bp == -2 || (bp >= 0 && __popc(bp ^ main_q) <= lsh.max_bits);
+        }
+        if (LSH && !__any_sync(0xffffffffu, q_cand)) {
+          // no query of this warp has the tile's partition among its candidates: nothing to read back
+#pragma unroll
+          for (int j = 0; j < SUBS_PER_TILE; j++) mx[j] = -INFINITY;
+        } else {
         // TMEM loads are software-pipelined: the load of sub-block j+1 is in flight while the 32 values of
         // sub-block j are reduced (waiting for each load before touching it left the tensor pipe idle
         // behind the epilogue)
@@ -331,7 +355,16 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
           if (j + 1 < SUBS_PER_TILE) tmem_ld_32x32b_x32(taddr0 + (uint32_t)((j + 1) * SUB), r[(j + 1) & 1]);
           const uint32_t* rr = r[j & 1];
           float m = -INFINITY;
-          if (!ragged) {
+          if (LSH && bp == -2) {
+            // mixed tile: row by row (the partition load has the same address for the whole warp)
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+              const int64_t slot = col0 + j * SUB + i;
+              const int part = slot < n_slots ? __ldg(lsh.slot_part + slot) : -1;
+              const float v = __uint_as_float(rr[i]);
+              if (part >= 0 && __popc(part ^ main_q) <= lsh.max_bits) m = fmaxf(m, v);
+            }
+          } else if (!ragged) {
 #pragma unroll
             for (int i = 0; i < 32; i++) m = fmaxf(m, __uint_as_float(rr[i]));  // fmaxf drops NaN (tombstones)
           } else {
@@ -341,7 +374,8 @@ batch_score_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
               if (col0 + j * SUB + i < n_slots) m = fmaxf(m, v);
             }
           }
-          mx[j] = m;
+          mx[j] = (LSH && !q_cand) ? -INFINITY : m;
+        }
         }
         tcgen05_fence_before();
         __syncwarp();
@@ -573,6 +607,7 @@ batch_refine_kernel(const float* __restrict__ y, const __nv_bfloat16* __restrict
                     const int32_t* __restrict__ cand, int cand_cap, const int32_t* __restrict__ cand_n,
                     const float* __restrict__ cutv,
                     const int32_t* __restrict__ excl_offsets, const int32_t* __restrict__ excl_slots,
+                    const BatchLsh lsh,  // slot_part == nullptr: no LSH filtering
                     int32_t* __restrict__ out_rows, double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   // layout: q[kpad] f32 | arr[k] u64 | exact[k] f64 | rows[k] i32
@@ -595,6 +630,7 @@ batch_refine_kernel(const float* __restrict__ y, const __nv_bfloat16* __restrict
   const int n_excl = excl_offsets ? excl_offsets[qi + 1] - excl_offsets[qi] : 0;
   const int32_t* my_cand = cand + (int64_t)qi * cand_cap;
   const float cut = cutv[qi];
+  const int main_q = lsh.slot_part ? __ldg(lsh.qmain + qi) : 0;
 
   const int gl = lane & 7, grp = lane >> 3;
   const int f4 = fpad >> 2;
@@ -661,7 +697,11 @@ batch_refine_kernel(const float* __restrict__ y, const __nv_bfloat16* __restrict
 #pragma unroll
         for (int o = 4; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         const int64_t slot = sub0 + (half * 4 + h) * 4 + grp;
-        const bool keep = gl == 0 && slot < n_slots && acc >= cut;  // NaN (tombstone) compares false
+        bool keep = gl == 0 && slot < n_slots && acc >= cut;  // NaN (tombstone) compares false
+        if (keep && lsh.slot_part) {  // rows outside the query's candidate partitions do not compete
+          const int part = __ldg(lsh.slot_part + slot);
+          keep = part >= 0 && __popc(part ^ main_q) <= lsh.max_bits;
+        }
         const unsigned ball = __ballot_sync(0xffffffffu, keep);     // bits 0, 8, 16, 24 <-> grp 0..3
         pass_mask |= (((ball >> 0) & 1u) | (((ball >> 8) & 1u) << 1) | (((ball >> 16) & 1u) << 2) |
                       (((ball >> 24) & 1u) << 3))
@@ -779,15 +819,16 @@ int32_t make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t kpad, uin
   return ORYX_OK;
 }
 
-template <int NCH>
+template <int NCH, bool LSH>
 int32_t launch_score(const CUtensorMap& tq, const CUtensorMap& ty, int n_qtiles, int n_ytiles, int64_t n_slots,
-                     float* bmax, int64_t bmax_stride, float* tmax, int64_t tmax_stride, int num_sms, cudaStream_t st) {
+                     float* bmax, int64_t bmax_stride, float* tmax, int64_t tmax_stride, const BatchLsh& lsh, int num_sms,
+                     cudaStream_t st) {
   constexpr int YB = (NCH <= 2) ? 2 : 1;
   const size_t smem = ScoreSmem::bytes(NCH, YB);
-  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_score_kernel<NCH>), smem));
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(batch_score_kernel<NCH, LSH>), smem));
   const int grid = std::min(num_sms, n_ytiles);
-  batch_score_kernel<NCH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride, tmax,
-                                                             tmax_stride);
+  batch_score_kernel<NCH, LSH><<<grid, kScoreThreads, smem, st>>>(tq, ty, n_qtiles, n_ytiles, n_slots, bmax, bmax_stride,
+                                                                  tmax, tmax_stride, lsh);
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }
@@ -838,18 +879,16 @@ thread_local bool tl_batch_small_pages_ok = false;
 
 bool batch_topn_possible(Model* m) {
   Store* s = &m->store[ORYX_Y];
-  const bool lsh = s->hashed && m->num_hashes != m->max_bits;
-  return !lsh && round_up(s->features, BK) <= 256 && s->n_slots >= 4096 && encode_tiled_fn() != nullptr;
+  return round_up(s->features, BK) <= 256 && s->n_slots >= 4096 && encode_tiled_fn() != nullptr;
 }
 
 bool batch_topn_supported(Model* m, int nq) {
   Store* s = &m->store[ORYX_Y];
-  const bool lsh = s->hashed && m->num_hashes != m->max_bits;
   const int kpad = round_up(s->features, BK);
   // Below 32 queries the path only pays off while the bf16 shadow of Y is current (it then reads half the
   // bytes of an fp32 scan even for a single query); building the shadow for a handful of queries does not.
   const bool shadow_current = m->batch.y_version == s->version && m->batch.y_rows == s->n_slots;
-  return !lsh && kpad <= 256 && (nq >= 32 || (nq >= 1 && (shadow_current || tl_batch_small_pages_ok))) && s->n_slots >= 4096 &&
+  return kpad <= 256 && (nq >= 32 || (nq >= 1 && (shadow_current || tl_batch_small_pages_ok))) && s->n_slots >= 4096 &&
          encode_tiled_fn() != nullptr;
 }
 
@@ -936,13 +975,32 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
   CUtensorMap tq, ty;
   ORYX_TRY(make_map(&tq, d_qbf.p, (uint64_t)nq_pad, (uint64_t)kpad, BM));
   ORYX_TRY(make_map(&ty, d_ybf.p, (uint64_t)n, (uint64_t)kpad, BN));
-  int32_t rc;
-  switch (nch) {
-    case 1: rc = launch_score<1>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
-    case 2: rc = launch_score<2>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
-    case 3: rc = launch_score<3>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
-    default: rc = launch_score<4>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, tmax_stride, m->num_sms, st); break;
+  // LSH filtering on: every query's partition index, by the same kernel that hashes rows at ingest
+  const bool lsh_on = s->hashed && m->num_hashes != m->max_bits;
+  BatchLsh lsh{};
+  if (lsh_on) {
+    void* d_qmain = nullptr;
+    ORYX_TRY(scratch(bs, 13, (size_t)nq_pad * 4, &d_qmain));
+    ORYX_CUDA(cudaMemsetAsync(d_qmain, 0, (size_t)nq_pad * 4, st));
+    ORYX_TRY(lsh_hash_rows_device(m, (const float*)d_q.p, nq, F, (int32_t*)d_qmain, st));
+    lsh.block_part = s->d_block_part;
+    lsh.slot_part = s->d_slot_part;
+    lsh.qmain = (const int32_t*)d_qmain;
+    lsh.max_bits = m->max_bits;
   }
+  int32_t rc;
+#define ORYX_SCORE(NCH_)                                                                                              \
+  (lsh_on ? launch_score<NCH_, true>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, \
+                                     tmax_stride, lsh, m->num_sms, st)                                                \
+          : launch_score<NCH_, false>(tq, ty, n_qtiles, n_ytiles, n, (float*)d_bmax.p, bmax_stride, (float*)d_tmax.p, \
+                                      tmax_stride, lsh, m->num_sms, st))
+  switch (nch) {
+    case 1: rc = ORYX_SCORE(1); break;
+    case 2: rc = ORYX_SCORE(2); break;
+    case 3: rc = ORYX_SCORE(3); break;
+    default: rc = ORYX_SCORE(4); break;
+  }
+#undef ORYX_SCORE
   ORYX_TRY(rc);
   ORYX_CUDA(cudaEventRecord(ev[2], st));
 
@@ -960,7 +1018,7 @@ int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how
     kern<<<nq, kRefineThreads, rsmem, st>>>(
         s->d_vec, (const __nv_bfloat16*)d_ybf.p, kpad, s->d_slot_row, n, fpad, F, (const float*)d_q.p, kind, k,
         how_many, (const int32_t*)d_cand.p, cand_cap, (const int32_t*)d_candn.p, (const float*)d_cut.p,
-        excl_offsets ? (const int32_t*)d_eo.p : nullptr, excl_offsets ? (const int32_t*)d_es.p : nullptr,
+        excl_offsets ? (const int32_t*)d_eo.p : nullptr, excl_offsets ? (const int32_t*)d_es.p : nullptr, lsh,
         (int32_t*)d_orows.p, (double*)d_oscores.p, (int32_t*)d_on.p);
     return ORYX_OK;
   };

@@ -29,7 +29,7 @@ FoldScratch* solver_fold_scratch(Solver* s);
 
 namespace {
 
-constexpr int kRowsPerCta = 64;  // interactions per CTA
+constexpr int kRowsPerCta = 128;  // interactions per CTA
 
 // One warp per interaction: copy the row living in `slots[i]` of a store (or zeros when the slot is
 // negative) into a packed [n x f] buffer.
@@ -88,21 +88,30 @@ __device__ __forceinline__ double target_qui(bool implicit, double value, double
   return value;
 }
 
-// One CTA = 64 interactions x all F outputs.  Phase 1: one thread per interaction computes Qui with
-// the exact sequential arithmetic and the scalar dQui.  Phase 2: binary64 GEMM
-// X[k][r] = sum_c inv[r][c] * b[k][c], tiled 64 (interactions) x 64 (outputs) x 16 (c).
-__global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__ inv, int f, int implicit,
-                                                      const float* __restrict__ xu,
-                                                      const uint8_t* __restrict__ has_xu,
-                                                      const float* __restrict__ yi,
-                                                      const uint8_t* __restrict__ has_yi,
-                                                      const double* __restrict__ values, int64_t n,
-                                                      float* __restrict__ out, uint8_t* __restrict__ out_valid) {
+// One CTA = 128 interactions x all F outputs.  Phase 1: one thread per interaction computes Qui with the
+// exact sequential arithmetic and the scalar dQui.  Phase 2: binary64 GEMM
+// X[k][r] = sum_c inv[r][c] * b[k][c], tiled 128 (interactions) x 64 (outputs) x 16 (c); a thread owns 8
+// interactions x 4 outputs (32 binary64 accumulators), and both operand tiles are read with 128-bit
+// loads laid out so that a warp touches at most two 128-byte wavefronts per load (the 4 x 4 version with
+// 64-bit loads spent three cycles in the load/store unit for every cycle of binary64 FMA).  The sum over c
+// runs in index order with one FMA per term, for every output.
+constexpr int kFoldK = 16;                 // c per tile
+constexpr int kFoldOut = 64;               // outputs per tile
+constexpr int kFoldBLd = kRowsPerCta + 2;  // padded row strides (doubles), multiples of 2 for 128-bit loads
+constexpr int kFoldILd = kFoldOut + 2;
+
+__global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restrict__ inv, int f, int implicit,
+                                                         const float* __restrict__ xu,
+                                                         const uint8_t* __restrict__ has_xu,
+                                                         const float* __restrict__ yi,
+                                                         const uint8_t* __restrict__ has_yi,
+                                                         const double* __restrict__ values, int64_t n,
+                                                         float* __restrict__ out, uint8_t* __restrict__ out_valid) {
   __shared__ double s_dq[kRowsPerCta];
   __shared__ uint8_t s_valid[kRowsPerCta];
   __shared__ uint8_t s_has[kRowsPerCta];
-  __shared__ double Bs[16][kRowsPerCta + 1];  // b tile: [c][k]
-  __shared__ double Is[16][64 + 1];           // inverse tile: [c][r]
+  __shared__ __align__(16) double Bs[kFoldK][kFoldBLd];  // b tile: [c][k]
+  __shared__ __align__(16) double Is[kFoldK][kFoldILd];  // inverse tile: [c][r]
   const int tid = threadIdx.x;
   const int64_t k0 = (int64_t)blockIdx.x * kRowsPerCta;
 
@@ -132,17 +141,17 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
   }
   __syncthreads();
 
-  const int tx = tid & 15, ty = tid >> 4;  // ty -> interactions (4 each), tx -> outputs (4 each)
-  for (int r0 = 0; r0 < f; r0 += 64) {
-    double acc[4][4];
+  const int tx = tid & 15, ty = tid >> 4;  // ty -> interactions 8 ty .. 8 ty + 7; tx -> outputs 2 tx, 2 tx + 1, 32 + 2 tx, 33 + 2 tx
+  for (int r0 = 0; r0 < f; r0 += kFoldOut) {
+    double acc[8][4];
 #pragma unroll
-    for (int i = 0; i < 4; i++)
+    for (int i = 0; i < 8; i++)
 #pragma unroll
       for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
-    for (int c0 = 0; c0 < f; c0 += 16) {
+    for (int c0 = 0; c0 < f; c0 += kFoldK) {
       __syncthreads();
       // b tile: b[k][c] = (float)((double)yi[k][c] * dQui[k])  (ALSUtils.java:93-95)
-      for (int e = tid; e < 16 * kRowsPerCta; e += 256) {
+      for (int e = tid; e < kFoldK * kRowsPerCta; e += 256) {
         int kk = e >> 4, c = e & 15;
         int64_t k = k0 + kk;
         double v = 0.0;
@@ -153,32 +162,37 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
         Bs[c][kk] = v;
       }
       // inverse tile: inv[r][c] (row-major)
-      for (int e = tid; e < 16 * 64; e += 256) {
+      for (int e = tid; e < kFoldK * kFoldOut; e += 256) {
         int r = e >> 4, c = e & 15;
         Is[c][r] = (r0 + r < f && c0 + c < f) ? inv[(size_t)(r0 + r) * f + c0 + c] : 0.0;
       }
       __syncthreads();
 #pragma unroll
-      for (int c = 0; c < 16; c++) {
-        double bv[4], iv[4];
+      for (int c = 0; c < kFoldK; c++) {
+        double bv[8], iv[4];
 #pragma unroll
-        for (int i = 0; i < 4; i++) bv[i] = Bs[c][ty * 4 + i];
+        for (int i = 0; i < 4; i++) {
+          const double2 t = *reinterpret_cast<const double2*>(&Bs[c][ty * 8 + 2 * i]);
+          bv[2 * i] = t.x;
+          bv[2 * i + 1] = t.y;
+        }
+        const double2 i0 = *reinterpret_cast<const double2*>(&Is[c][2 * tx]);
+        const double2 i1 = *reinterpret_cast<const double2*>(&Is[c][32 + 2 * tx]);
+        iv[0] = i0.x; iv[1] = i0.y; iv[2] = i1.x; iv[3] = i1.y;
 #pragma unroll
-        for (int j = 0; j < 4; j++) iv[j] = Is[c][tx * 4 + j];
-#pragma unroll
-        for (int i = 0; i < 4; i++)
+        for (int i = 0; i < 8; i++)
 #pragma unroll
           for (int j = 0; j < 4; j++) acc[i][j] = fma(bv[i], iv[j], acc[i][j]);
       }
     }
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-      int kk = ty * 4 + i;
+    for (int i = 0; i < 8; i++) {
+      int kk = ty * 8 + i;
       int64_t k = k0 + kk;
       if (k >= n) continue;
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        int r = r0 + tx * 4 + j;
+        int r = r0 + (j < 2 ? 0 : 32) + 2 * tx + (j & 1);
         if (r >= f) continue;
         float dxu = (float)acc[i][j];  // Solver.java:40-42
         float res = 0.0f;
@@ -188,7 +202,6 @@ __global__ void __launch_bounds__(256) fold_in_kernel(const double* __restrict__
     }
   }
 }
-
 
 constexpr int64_t kFoldChunk = 1 << 17;  // interactions per pipeline stage
 

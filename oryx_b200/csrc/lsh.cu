@@ -23,51 +23,114 @@ int64_t binom(int n, int k) {
   return r;
 }
 
-// One thread per row; the row tile and the hash vectors are staged in shared memory so global
-// reads stay coalesced while each thread walks its own row sequentially (stride features+1 floats
-// => conflict-free).  Hashes are processed four at a time for ILP across the dependent DADD chains.
+// One thread per row; the row tile and the hash vectors are staged in shared memory so global reads stay
+// coalesced while each thread walks its own row (row stride a multiple of 4 floats with an odd number of
+// 16-byte units: 128-bit accesses of a quarter warp then cover all 32 banks).
+//
+// Only the SIGN of each dot product enters the index, so the kernel first evaluates all hashes of a row
+// with fp32 FMAs (H + 1 independent chains: the H dot products and |v|^2) and accepts a sign whenever the
+// fp32 value is further from zero than a rigorous bound on its distance from the reference's value:
+//   reference  R = sum_j fl32(h_j v_j), accumulated in binary64      |R - sum h_j v_j| <= (2^-24 + F 2^-53) sum |h_j v_j|
+//   fast       D = fp32 FMA chain                                    |D - sum h_j v_j| <= F 2^-24 / (1 - F 2^-24) sum |h_j v_j|
+//   sum |h_j v_j| <= |h| |v| (Cauchy-Schwarz), |v|^2 from its own fp32 chain (relative error <= F 2^-24)
+//   =>  |D - R| <= bound = 1.02 (F + 2) 2^-24 |h|_up sqrt(|v|^2_fp32)        (|h|_up: the norm rounded up, per hash)
+// |D| > bound  =>  sign(R) = sign(D) and R != 0.  Otherwise (about one pair in 10^4 for Gaussian data, plus
+// zero, tiny, NaN and infinite cases) the thread repeats that hash with the reference's exact operation
+// sequence (__fmul_rn, widen, __dadd_rn, index order).  The resulting index is bit-identical either way.
+constexpr int kLshGroup = 8;  // hashes evaluated per pass over a row
+
+template <int G>
+__device__ __forceinline__ int lsh_group_bits(const float* __restrict__ y, const float* __restrict__ s_hv, int ld,
+                                              const float* __restrict__ s_hnorm, int h0, int f4, int features,
+                                              float bound_scale) {
+  float dot[G], v2 = 0.f;
+#pragma unroll
+  for (int k = 0; k < G; k++) dot[k] = 0.f;
+  const float4* y4 = reinterpret_cast<const float4*>(y);
+  for (int j = 0; j < f4; j++) {
+    const float4 v = y4[j];
+    v2 = fmaf(v.x, v.x, v2); v2 = fmaf(v.y, v.y, v2); v2 = fmaf(v.z, v.z, v2); v2 = fmaf(v.w, v.w, v2);
+#pragma unroll
+    for (int k = 0; k < G; k++) {
+      const float4 h = reinterpret_cast<const float4*>(s_hv + (size_t)(h0 + k) * ld)[j];  // same address for the whole warp
+      dot[k] = fmaf(v.x, h.x, dot[k]); dot[k] = fmaf(v.y, h.y, dot[k]);
+      dot[k] = fmaf(v.z, h.z, dot[k]); dot[k] = fmaf(v.w, h.w, dot[k]);
+    }
+  }
+  const float vnorm = sqrtf(v2) * bound_scale;
+  int bits = 0;
+#pragma unroll
+  for (int k = 0; k < G; k++) {
+    const float bound = vnorm * s_hnorm[h0 + k];
+    bool positive;
+    if (fabsf(dot[k]) > bound && fabsf(dot[k]) > 1e-30f && bound < 3.0e38f) {
+      positive = dot[k] > 0.f;
+    } else {
+      // too close to zero to call (or NaN / inf / denormal range): the reference's arithmetic, exactly
+      const float* hv = s_hv + (size_t)(h0 + k) * ld;
+      double acc = 0.0;
+      for (int j = 0; j < features; j++) acc = exact_step(acc, hv[j], y[j]);
+      positive = acc > 0.0;
+    }
+    if (positive) bits |= 1 << (h0 + k);
+  }
+  return bits;
+}
+
 __global__ void lsh_hash_kernel(const float* __restrict__ rows, int64_t n, int64_t stride, int features,
                                 const float* __restrict__ hash_vectors, int hv_stride, int num_hashes,
-                                int tile_rows, int32_t* __restrict__ out, int32_t* __restrict__ zero_counter) {
-  extern __shared__ float smem[];
-  float* s_hv = smem;                                  // [num_hashes x features]
-  float* s_rows = smem + (size_t)num_hashes * features;  // [tile_rows x (features+1)]
-  const int ld = features + 1;
+                                int tile_rows, int ld, int32_t* __restrict__ out, int32_t* __restrict__ zero_counter) {
+  extern __shared__ __align__(16) float smem[];
+  float* s_hv = smem;                                  // [num_hashes x ld], zero padded
+  float* s_hnorm = s_hv + (size_t)num_hashes * ld;     // [16] norms, rounded up
+  float* s_rows = s_hnorm + 16;                        // [tile_rows x ld], zero padded
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int f4 = (features + 3) >> 2;
   // a query's hashing kernel also resets the count of its work list (built by the next kernel)
   if (zero_counter && blockIdx.x == 0 && threadIdx.x == 0) *zero_counter = 0;
 
-  for (int e = threadIdx.x; e < num_hashes * features; e += blockDim.x) {
-    int h = e / features, j = e - h * features;
-    s_hv[e] = hash_vectors[(size_t)h * hv_stride + j];
+  for (int e = threadIdx.x; e < num_hashes * ld; e += blockDim.x) {
+    int h = e / ld, j = e - h * ld;
+    s_hv[e] = j < features ? hash_vectors[(size_t)h * hv_stride + j] : 0.f;
   }
+  __syncthreads();
+  if (threadIdx.x < num_hashes) {
+    double ss = 0.0;
+    for (int j = 0; j < features; j++) { const double v = (double)s_hv[(size_t)threadIdx.x * ld + j]; ss += v * v; }
+    s_hnorm[threadIdx.x] = __double2float_ru(sqrt(ss) * (1.0 + 1e-12));
+  }
+  const float bound_scale = 1.02f * (float)(features + 2) * 5.9604645e-08f;  // 1.02 (F + 2) 2^-24
+  const bool vec4 = (stride & 3) == 0 && ((uintptr_t)rows & 15) == 0;
   for (int64_t row0 = (int64_t)blockIdx.x * tile_rows; row0 < n; row0 += (int64_t)gridDim.x * tile_rows) {
     __syncthreads();
     for (int r = warp; r < tile_rows; r += nwarps) {
-      int64_t row = row0 + r;
-      if (row < n) {
-        const float* src = rows + row * stride;
-        for (int j = lane; j < features; j += 32) s_rows[r * ld + j] = src[j];
+      const int64_t row = row0 + r;
+      if (row >= n) break;
+      const float* src = rows + row * stride;
+      float* dst = s_rows + (size_t)r * ld;
+      if (vec4) {
+        const int full4 = features >> 2;
+        for (int j = lane; j < full4; j += 32) reinterpret_cast<float4*>(dst)[j] = ldg_stream(reinterpret_cast<const float4*>(src) + j);
+        for (int j = 4 * full4 + lane; j < 4 * f4; j += 32) dst[j] = j < features ? src[j] : 0.f;
+      } else {
+        for (int j = lane; j < 4 * f4; j += 32) dst[j] = j < features ? src[j] : 0.f;
       }
     }
     __syncthreads();
-    int t = threadIdx.x;
+    const int t = threadIdx.x;
     if (t < tile_rows && row0 + t < n) {
-      const float* y = s_rows + t * ld;
+      const float* y = s_rows + (size_t)t * ld;
       int index = 0;
-      for (int h0 = 0; h0 < num_hashes; h0 += 4) {
-        double acc[4] = {0.0, 0.0, 0.0, 0.0};
-        const float* hv[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) hv[k] = s_hv + (size_t)min(h0 + k, num_hashes - 1) * features;
-        for (int j = 0; j < features; j++) {
-          float v = y[j];
-#pragma unroll
-          for (int k = 0; k < 4; k++) acc[k] = exact_step(acc[k], hv[k][j], v);
-        }
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-          if (h0 + k < num_hashes && acc[k] > 0.0) index |= 1 << (h0 + k);
+      for (int h0 = 0; h0 < num_hashes; h0 += kLshGroup) {
+        switch (min(kLshGroup, num_hashes - h0)) {
+          case 1: index |= lsh_group_bits<1>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 2: index |= lsh_group_bits<2>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 3: index |= lsh_group_bits<3>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 4: index |= lsh_group_bits<4>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 5: index |= lsh_group_bits<5>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 6: index |= lsh_group_bits<6>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          case 7: index |= lsh_group_bits<7>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
+          default: index |= lsh_group_bits<8>(y, s_hv, ld, s_hnorm, h0, f4, features, bound_scale); break;
         }
       }
       out[row0 + t] = index;
@@ -175,16 +238,20 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
     if (d_zero_counter) ORYX_CUDA(cudaMemsetAsync(d_zero_counter, 0, sizeof(int32_t), stream));
     return ORYX_OK;
   }
-  size_t hv_bytes = (size_t)H * F * sizeof(float);
-  size_t budget = 200 * 1024 - hv_bytes;
-  int tile_rows = (int)std::min<size_t>(128, budget / ((size_t)(F + 1) * sizeof(float)));
+  // shared-memory row stride: features rounded up to 4, then to an odd number of 16-byte units
+  int ld = round_up(F, 4);
+  if (((ld >> 2) & 1) == 0) ld += 4;
+  const size_t hv_bytes = ((size_t)H * ld + 16) * sizeof(float);
+  const size_t budget = 200 * 1024 - hv_bytes;
+  int tile_rows = (int)std::min<size_t>(128, budget / ((size_t)ld * sizeof(float)));
   tile_rows = tile_rows / 32 * 32;
   if (tile_rows < 32) {
     set_error("features=%d too large for the LSH hashing kernel's shared-memory tile", F);
     return ORYX_E_UNSUPPORTED;
   }
-  size_t smem = hv_bytes + (size_t)tile_rows * (F + 1) * sizeof(float);
-  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(lsh_hash_kernel), smem));
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(lsh_hash_kernel), hv_bytes + (size_t)tile_rows * ld * sizeof(float)));
+  if (n < tile_rows) tile_rows = (int)round_up((int)n, 32);  // a query: one warp is enough
+  const size_t smem = hv_bytes + (size_t)tile_rows * ld * sizeof(float);
   int64_t tiles = (n + tile_rows - 1) / tile_rows;
   int grid = (int)std::min<int64_t>(tiles, (int64_t)m->num_sms * 8);
   // `early_start`: the kernel depends on nothing the stream's previous kernels write (a query vector
@@ -200,7 +267,7 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   ORYX_CUDA(cudaLaunchKernelEx(&cfg, lsh_hash_kernel, d_rows, n, (int64_t)stride, F, (const float*)m->d_hash_vectors,
-                               m->store[ORYX_Y].fpad, H, tile_rows, d_out, d_zero_counter));
+                               m->store[ORYX_Y].fpad, H, tile_rows, ld, d_out, d_zero_counter));
   m->launches++;
   return ORYX_OK;
 }

@@ -203,6 +203,47 @@ def test_lsh_bit_exact_and_filtered_topn(rate, cores, f):
         assert p[0] == oracle.lsh_index(hv, newv)
 
 
+@pytest.mark.parametrize("f,h", [(128, 5), (50, 8), (33, 16), (256, 3)])
+def test_lsh_index_near_orthogonal_and_degenerate_rows(f, h):
+    """The hashing kernel calls a sign from fp32 arithmetic only when the value clears a rigorous error
+    bound and otherwise repeats the reference's exact float-multiply / double-add chain.  Rows built to sit
+    on (or within rounding of) a hash hyperplane, zero / denormal / huge / NaN / infinite rows and exact
+    cancellations must all get the oracle's index."""
+    rng = np.random.default_rng(f * 31 + h)
+    hv = random_hash_vectors(h, f, seed=f + h)
+    rows = []
+    w = rng.standard_normal((4000, f))
+    for i in range(len(w)):                       # remove the component along one hash vector (in binary64),
+        k = i % h                                 # then round to binary32: the dot product is ~1e-8 of |w|
+        hk = hv[k].astype(np.float64)
+        rows.append(w[i] - (w[i] @ hk) / (hk @ hk) * hk)
+    rows = np.asarray(rows)
+    rows[::7] *= 1e-3
+    rows[1::7] *= 1e4
+    extra = np.zeros((12, f))
+    extra[1, :] = 1e-42                            # denormals
+    extra[2, :] = 3e37
+    extra[3, :] = -3e37
+    extra[4, 0] = np.nan
+    extra[5, 0] = np.inf
+    extra[6, :2] = [np.inf, -np.inf]
+    extra[7] = hv[0]                               # on the normal itself
+    extra[8] = -hv[0]
+    extra[9, :2] = [1.0, -1.0]                     # exact cancellation against a constant hash vector (below)
+    extra[10, :] = 1e-30
+    extra[11, :] = -1e-30
+    y = np.concatenate([rows, extra]).astype(np.float32)
+    hv2 = hv.copy()
+    hv2[h - 1, :] = 0.0
+    hv2[h - 1, :2] = 0.5                           # dot with row 9 is exactly 0 -> bit must be 0
+    for vecs in (hv, hv2):
+        with ob.Model(f, hash_vectors=vecs, max_bits_differing=0) as m:
+            with np.errstate(all="ignore"):
+                exp = oracle.lsh_index_rows(vecs, y)
+            assert np.array_equal(m.lsh_index_rows(y), exp)
+            assert np.array_equal(m.upsert(ob.Y, np.arange(len(y), dtype=np.int32), y), exp)
+
+
 def test_lsh_edge_vectors():
     # zero vector -> index 0; candidates lists of LocalitySensitiveHashTest.java:85-139
     L = load_golden("lsh")
@@ -433,6 +474,52 @@ def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
                 assert cnt[i] == len(e_rows), (i, cnt[i], len(e_rows))
                 _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), (e_rows, e_scores),
                                   oracle.scores_all(kind, queries[i], y))
+
+
+@pytest.mark.parametrize("rate,cores", [(0.3, 32), (0.5, 8), (0.1, 8)])
+def test_topn_batch_with_lsh_filtering(rate, cores):
+    """With LSH filtering on, a page of queries still rides on the tensor-core path: every query only
+    competes for rows of its own candidate partitions (LocalitySensitiveHash.getCandidateIndices).  Batch ==
+    one query at a time == oracle, before compaction (every 256-slot tile mixes partitions) and after it
+    (tiles are pure and non-candidate tiles are skipped), with removals and exclusions, through
+    oryx_topn_batch, oryx_recommend_batch and the combining entry point."""
+    n, f, nq, how_many = 60000, 64, 70, 10
+    h, bits = ob.lsh_plan(rate, cores)
+    hv = random_hash_vectors(h, f, seed=h + 100)
+    y = random_model(n, f, seed=0xB2000300 + h)
+    rng = np.random.default_rng(h)
+    q = rng.standard_normal((nq, f), dtype=np.float32)
+    gone = rng.choice(n, 300, replace=False).astype(np.int32)
+    with ob.Model(f, hash_vectors=hv, max_bits_differing=bits) as m:
+        parts = m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        m.upsert(ob.X, np.arange(nq, dtype=np.int32), q)
+        m.remove(ob.Y, gone)
+        part = parts.copy()
+        part[gone] = -1
+        excl = [rng.integers(0, n, 7).astype(np.int32) if i % 2 else np.zeros(0, np.int32) for i in range(nq)]
+        m.known_items_add(np.arange(nq, dtype=np.int32), excl)
+        for phase in ("as loaded", "compacted"):
+            for kind in (ob.DOT, ob.COSINE):
+                runs0 = _batch_counters(m)[0]
+                rows, scores, cnt = m.topn_batch(kind, q, how_many, excluded_lists=excl)
+                assert _batch_counters(m)[0] == runs0 + 1, "LSH filtering switched the tensor-core path off"
+                for i in range(nq):
+                    cand = oracle.lsh_candidates(h, bits, oracle.lsh_index(hv, q[i]))
+                    e = oracle.topn(kind, q[i], y, how_many, part=part, cand=cand,
+                                    excluded=np.unique(excl[i]) if len(excl[i]) else None)
+                    assert cnt[i] == len(e[0]), (phase, kind, i)
+                    _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), e, oracle.scores_all(kind, q[i], y))
+                    if i < 6:
+                        _assert_same_topn(m.topn(kind, q[i], how_many, excl[i]), e, oracle.scores_all(kind, q[i], y))
+            r_rows, r_scores, r_cnt = m.recommend_batch(np.arange(nq, dtype=np.int32), how_many)
+            for i in (0, 1, nq - 1):
+                cand = oracle.lsh_candidates(h, bits, oracle.lsh_index(hv, q[i]))
+                e = oracle.topn(oracle.DOT, q[i], y, how_many, part=part, cand=cand,
+                                excluded=np.unique(excl[i]) if len(excl[i]) else None)
+                _assert_same_topn((r_rows[i, :r_cnt[i]], r_scores[i, :r_cnt[i]]), e, oracle.scores_all(oracle.DOT, q[i], y))
+                _assert_same_topn(m.topn_coalesced(ob.DOT, q[i], how_many, excluded=excl[i]), e,
+                                  oracle.scores_all(oracle.DOT, q[i], y))
+            m.compact(ob.Y)
 
 
 @pytest.mark.parametrize("n_known", [20, 60, 100])
