@@ -169,8 +169,47 @@ struct DeviceGuard {
 
 // Second half of a query: the query vector and the sorted exclusion slots already sit in device
 // memory (d_query; c->d_excl[0..n_excl_slots)).  Launch, copy the packed record back, wait.
+static int32_t ctx_tmp(QueryCtx* c, int i, size_t bytes, void** out);
+static void ctx_tmp_trim(QueryCtx* c);
+
+// how_many beyond the fused scan's limit: exact scores of every row, radix select, sort (topn_deep.cu).
+static int32_t run_topn_deep(Model* m, QueryCtx* c, int32_t kind, const float* d_query, int32_t n_excl_slots,
+                             int32_t how_many, int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  Store* s = &m->store[ORYX_Y];
+  const size_t work = (deep_scratch_bytes(s->n_slots, how_many) + 255) & ~(size_t)255;
+  const size_t scores_off = work, rows_off = scores_off + (size_t)how_many * 8, n_off = rows_off + (((size_t)how_many * 4 + 15) & ~(size_t)15);
+  unsigned char* buf = nullptr;
+  ORYX_TRY(ctx_tmp(c, 0, n_off + 16, (void**)&buf));
+  ORYX_CUDA(cudaEventRecord(c->ev0, c->stream));
+  int32_t rc = topn_deep_launch(m, c, kind, d_query, how_many, c->d_excl, n_excl_slots, buf,
+                                reinterpret_cast<int32_t*>(buf + rows_off), reinterpret_cast<double*>(buf + scores_off),
+                                reinterpret_cast<int32_t*>(buf + n_off), c->stream);
+  if (rc == ORYX_OK) {
+    int32_t n = 0;
+    cudaEventRecord(c->ev1, c->stream);
+    if (cudaMemcpyAsync(&n, buf + n_off, sizeof(n), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess || n < 0 || n > how_many) {
+      set_error("deep top-N failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    } else {
+      if (n > 0 && (cudaMemcpy(out_rows, buf + rows_off, (size_t)n * 4, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                    cudaMemcpy(out_scores, buf + scores_off, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess)) {
+        set_error("deep top-N copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = ORYX_E_CUDA;
+      }
+      *out_n = n;
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) m->last_query_ms.store((double)ms);
+      else cudaGetLastError();
+    }
+  }
+  ctx_tmp_trim(c);
+  return rc;
+}
+
 static int32_t run_topn_staged(Model* m, QueryCtx* c, int32_t kind, const float* d_query, int32_t n_excl_slots,
                                int32_t how_many, int32_t* out_rows, double* out_scores, int32_t* out_n) {
+  if (how_many > ORYX_MAX_HOW_MANY) return run_topn_deep(m, c, kind, d_query, n_excl_slots, how_many, out_rows, out_scores, out_n);
   // packed result record (see ctx_create)
   const size_t rows_off = 8, scores_off = 8 + (((size_t)how_many * 4 + 7) & ~(size_t)7);
   const size_t rec_bytes = scores_off + (size_t)how_many * 8;
@@ -508,7 +547,7 @@ int32_t oryx_topn(oryx_model* mh, int32_t kind, const float* query, int32_t how_
                   int32_t* out_rows, double* out_scores, int32_t* out_n) {
   ORYX_ARG(mh && query && out_rows && out_scores && out_n, "null argument");
   ORYX_ARG(n_excluded >= 0 && (n_excluded == 0 || excluded_rows), "bad exclusion list");
-  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY_DEEP, "how_many out of range [1, ORYX_MAX_HOW_MANY_DEEP]");
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   QueryCtx* c = nullptr;
@@ -585,7 +624,7 @@ int32_t oryx_known_counts(oryx_model* mh, int32_t which, int32_t* out_counts, in
 int32_t oryx_recommend(oryx_model* mh, int32_t user_row, int32_t how_many, int32_t consider_known_items,
                        int32_t* out_rows, double* out_scores, int32_t* out_n, int32_t* found) {
   ORYX_ARG(mh && out_rows && out_scores && out_n && found, "null argument");
-  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY_DEEP, "how_many out of range [1, ORYX_MAX_HOW_MANY_DEEP]");
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   *out_n = 0;

@@ -317,6 +317,11 @@ struct TopnRequest {
   unsigned long long gate_value = 0;
 };
 int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStream_t stream);
+// topn_deep.cu: how_many beyond the fused scan's limit
+size_t deep_scratch_bytes(int64_t n_slots, int how_many);
+int32_t topn_deep_launch(Model* m, QueryCtx* ctx, int kind, const float* d_query, int how_many, const int32_t* d_excl,
+                         int n_excl, void* d_scratch, int32_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
+                         cudaStream_t stream);
 int32_t scores_all_launch(Model* m, int kind, const float* d_query, int32_t n_rows, double* d_out,
                           cudaStream_t stream);
 

@@ -39,6 +39,13 @@ int64_t binom(int n, int k) {
 // sequence (__fmul_rn, widen, __dadd_rn, index order).  The resulting index is bit-identical either way.
 constexpr int kLshGroup = 8;  // hashes evaluated per pass over a row
 
+__device__ __forceinline__ void cp_async_16(float* smem_dst, const float* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(float* smem_dst, const float* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+
 template <int G>
 __device__ __forceinline__ int lsh_group_bits(const float* __restrict__ y, const float* __restrict__ s_hv, int ld,
                                               const float* __restrict__ s_hnorm, int h0, int f4, int features,
@@ -108,14 +115,21 @@ __global__ void lsh_hash_kernel(const float* __restrict__ rows, int64_t n, int64
       if (row >= n) break;
       const float* src = rows + row * stride;
       float* dst = s_rows + (size_t)r * ld;
+      // asynchronous global -> shared copies: every row of the tile is in flight at once (a load-then-store
+      // loop waited for each row's load in turn and left the kernel bound by memory latency)
       if (vec4) {
         const int full4 = features >> 2;
-        for (int j = lane; j < full4; j += 32) reinterpret_cast<float4*>(dst)[j] = ldg_stream(reinterpret_cast<const float4*>(src) + j);
-        for (int j = 4 * full4 + lane; j < 4 * f4; j += 32) dst[j] = j < features ? src[j] : 0.f;
+        for (int j = lane; j < full4; j += 32) cp_async_16(dst + 4 * j, src + 4 * j);
+        for (int j = 4 * full4 + lane; j < 4 * f4; j += 32) {
+          if (j < features) cp_async_4(dst + j, src + j); else dst[j] = 0.f;
+        }
       } else {
-        for (int j = lane; j < 4 * f4; j += 32) dst[j] = j < features ? src[j] : 0.f;
+        for (int j = lane; j < 4 * f4; j += 32) {
+          if (j < features) cp_async_4(dst + j, src + j); else dst[j] = 0.f;
+        }
       }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
     const int t = threadIdx.x;
     if (t < tile_rows && row0 + t < n) {

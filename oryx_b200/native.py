@@ -14,7 +14,8 @@ _SO = os.path.join(_HERE, "liboryx_b200.so")
 OK, E_INVALID, E_CUDA, E_SINGULAR, E_NOMEM, E_UNSUPPORTED = 0, 1, 2, 3, 4, 5
 DOT, COSINE = 0, 1
 X, Y = 0, 1
-MAX_HOW_MANY = 1016
+MAX_HOW_MANY = 1016          # fused scan
+MAX_HOW_MANY_DEEP = 65536    # oryx_topn / oryx_recommend (exact select-and-sort path above MAX_HOW_MANY)
 STATIC_MAX_HOW_MANY = 56
 
 

@@ -97,6 +97,49 @@ def test_topn_matches_oracle(n, f, how_many):
                 _assert_same_topn(got, exp, oracle.scores_all(kind, q, y))
 
 
+@pytest.mark.parametrize("n,f,how_many,lsh", [(60000, 32, 2000, False), (50000, 50, 5000, True), (70000, 16, 65536, False),
+                                             (3000, 8, 4000, False)])
+def test_topn_deep_pages_match_oracle(n, f, how_many, lsh):
+    """howMany + offset has no upper bound in the reference (Recommend.java:81-82,108-112).  Beyond the fused
+    scan's 1016 the library scores every row exactly, radix-selects and sorts on the device; rows and
+    binary64 scores must equal the oracle's list (LSH filtering, exclusions, removals, duplicate rows,
+    fewer competing rows than requested)."""
+    from oryx_b200 import native
+    y = random_model(n, f, seed=n + how_many)
+    y[100:140] = y[99]                      # a block of identical rows: equal scores, ranked by row
+    rng = np.random.default_rng(how_many)
+    hv, bits, h = None, 0, 0
+    if lsh:
+        h, bits = ob.lsh_plan(0.5, 8)
+        hv = random_hash_vectors(h, f, seed=3)
+    with ob.Model(f, hash_vectors=hv, max_bits_differing=bits) as m:
+        parts = m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        gone = rng.choice(n, 50, replace=False).astype(np.int32)
+        m.remove(ob.Y, gone)
+        part = (parts if lsh else np.zeros(n, np.int32)).copy()
+        part[gone] = -1
+        for kind in (ob.DOT, ob.COSINE):
+            q = rng.standard_normal(f, dtype=np.float32)
+            excl = rng.integers(0, n, 300).astype(np.int32)
+            cand = oracle.lsh_candidates(h, bits, oracle.lsh_index(hv, q)) if lsh else None
+            e_rows, e_scores = oracle.topn(kind, q, y, how_many, part=part, cand=cand, excluded=np.unique(excl))
+            rows, scores = m.topn(kind, q, how_many, excluded=excl)
+            assert len(rows) == len(e_rows)
+            assert np.array_equal(scores, e_scores)
+            # equal scores are ordered by ascending row here; the oracle's heap leaves ties unspecified
+            _assert_same_topn((rows, scores), (e_rows, e_scores), oracle.scores_all(kind, q, y))
+            assert len(set(rows.tolist())) == len(rows)
+            same = np.nonzero(np.diff(scores) == 0)[0]
+            assert np.all(rows[same] < rows[same + 1])
+            # the fused scan and the deep path agree on a page both can serve
+            r1, s1 = m.topn(kind, q, native.MAX_HOW_MANY, excluded=excl)
+            assert np.array_equal(s1, scores[:len(s1)])
+    with pytest.raises(ob.OryxError):
+        with ob.Model(f) as m2:
+            m2.upsert(ob.Y, np.arange(10, dtype=np.int32), y[:10])
+            m2.topn(ob.DOT, y[0], native.MAX_HOW_MANY_DEEP + 1)
+
+
 def test_topn_with_exclusions_and_removals():
     n, f = 5000, 32
     y = random_model(n, f, seed=11)
