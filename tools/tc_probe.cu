@@ -126,6 +126,63 @@ __global__ void __launch_bounds__(128, 1) probe_kernel(const uint8_t* a_g, const
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
 }
 
+// ---- no-swizzle K-major layout: 8-row x 16-byte core matrices (128 B each); per 32-byte K-step tile the two
+// core matrices along K are `lbo` bytes apart, 8-row groups `sbo` bytes apart.
+__host__ __device__ inline uint32_t nosw(uint32_t r, uint32_t b, uint32_t lbo, uint32_t sbo) {
+  return (r >> 3) * sbo + (b >> 4) * lbo + (r & 7u) * 16u + (b & 15u);
+}
+__device__ __forceinline__ uint64_t desc_k_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// a_g: [128][ksteps*32] bytes, b_g: [n][ksteps*32]; every K-step is its own tile: A tile 128 rows (4 KB), B tile n rows.
+__global__ void __launch_bounds__(128, 1) probe_nosw_kernel(const uint8_t* a_g, const uint8_t* b_g, int n, int ksteps, uint32_t idesc,
+                                                             uint32_t lbo, uint32_t sbo, uint32_t* d_out) {
+  extern __shared__ unsigned char smem_dyn[];
+  unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+  const uint32_t a_tile = 128 / 8 * sbo, b_tile = (uint32_t)n / 8 * sbo;
+  unsigned char* a_s = base;
+  unsigned char* b_s = base + (size_t)ksteps * a_tile;
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_holder;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kb = ksteps * 32;
+  for (int t = 0; t < ksteps; t++) {
+    for (int e = tid; e < 128 * 32; e += 128) { const int r = e >> 5, b = e & 31; a_s[(size_t)t * a_tile + nosw(r, b, lbo, sbo)] = a_g[(size_t)r * kb + t * 32 + b]; }
+    for (int e = tid; e < n * 32; e += 128) { const int r = e >> 5, b = e & 31; b_s[(size_t)t * b_tile + nosw(r, b, lbo, sbo)] = b_g[(size_t)r * kb + t * 32 + b]; }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (tid == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&tmem_holder)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_holder;
+  if (tid == 0) {
+    for (int t = 0; t < ksteps; t++)
+      umma<0>(tmem, desc_k_nosw(smem_u32(a_s + (size_t)t * a_tile), lbo, sbo), desc_k_nosw(smem_u32(b_s + (size_t)t * b_tile), lbo, sbo), idesc, (uint32_t)(t != 0));
+    tcgen05_commit(&bar);
+    mbar_wait(&bar, 0);
+  }
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  for (int c0 = 0; c0 < n; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, r);
+    for (int i = 0; i < 32; i++) d_out[(size_t)tid * n + c0 + i] = r[i];
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+}
+
 static uint32_t idesc_i8(int m, int n, int a_signed, int b_signed) {
   return (2u << 4) | ((uint32_t)a_signed << 7) | ((uint32_t)b_signed << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
@@ -172,6 +229,31 @@ int main() {
         if (s != d[(size_t)i * n + j]) { if (bad < 3) printf("  mismatch (%d,%d): got %d want %d\n", i, j, d[(size_t)i * n + j], s); bad++; }
       }
     printf("i8 probe: M=128 N=%d K=%d A=s8 B=%s8 -> %s (%lld mismatches)\n", n, kb, b_signed ? "s" : "u", bad ? "WRONG" : "exact", bad);
+  }
+
+  // ---- 1b. kind::i8 on the no-swizzle K-major layout (independent 32-byte K-step tiles)
+  CK(cudaFuncSetAttribute(probe_nosw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int variant = 0; variant < 4; variant++) {
+    const int n = (variant & 1) ? 256 : 128, ksteps = (variant & 2) ? 5 : 1, kb = ksteps * 32;
+    std::vector<uint8_t> a((size_t)M * kb), b((size_t)n * kb);
+    srand(99 + variant);
+    for (auto& v : a) v = (uint8_t)(rand() & 255);
+    for (auto& v : b) v = (uint8_t)(rand() & 255);
+    CK(cudaMemcpy(d_a, a.data(), a.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_b, b.data(), b.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_d, 0, 128 * 256 * 4));
+    probe_nosw_kernel<<<1, 128, smem>>>(d_a, d_b, n, ksteps, idesc_i8(M, n, 1, 1), 128, 256, d_d);
+    CK(cudaDeviceSynchronize());
+    std::vector<int32_t> d((size_t)M * n);
+    CK(cudaMemcpy(d.data(), d_d, d.size() * 4, cudaMemcpyDeviceToHost));
+    long long bad = 0;
+    for (int i = 0; i < M; i++)
+      for (int j = 0; j < n; j++) {
+        int32_t sacc = 0;
+        for (int k = 0; k < kb; k++) sacc += (int)(int8_t)a[(size_t)i * kb + k] * (int)(int8_t)b[(size_t)j * kb + k];
+        if (sacc != d[(size_t)i * n + j]) { if (bad < 3) printf("  mismatch (%d,%d): got %d want %d\n", i, j, d[(size_t)i * n + j], sacc); bad++; }
+      }
+    printf("i8 probe, no-swizzle layout (LBO=128, SBO=256): M=128 N=%d K=%d -> %s (%lld mismatches)\n", n, kb, bad ? "WRONG" : "exact", bad);
   }
 
   // ---- 2. fp32 accumulator rounding of kind::f16 (bf16 operands)
