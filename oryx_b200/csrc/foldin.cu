@@ -95,7 +95,7 @@ __device__ __forceinline__ double target_qui(bool implicit, double value, double
 // loads laid out so that a warp touches at most two 128-byte wavefronts per load (the 4 x 4 version with
 // 64-bit loads spent three cycles in the load/store unit for every cycle of binary64 FMA).  The sum over c
 // runs in index order with one FMA per term, for every output.
-constexpr int kFoldK = 16;                 // c per tile
+constexpr int kFoldK = 32;                 // c per tile
 constexpr int kFoldOut = 64;               // outputs per tile
 constexpr int kFoldBLd = kRowsPerCta + 2;  // padded row strides (doubles), multiples of 2 for 128-bit loads
 constexpr int kFoldILd = kFoldOut + 2;
@@ -110,8 +110,9 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   __shared__ double s_dq[kRowsPerCta];
   __shared__ uint8_t s_valid[kRowsPerCta];
   __shared__ uint8_t s_has[kRowsPerCta];
-  __shared__ __align__(16) double Bs[kFoldK][kFoldBLd];  // b tile: [c][k]
-  __shared__ __align__(16) double Is[kFoldK][kFoldILd];  // inverse tile: [c][r]
+  extern __shared__ __align__(16) unsigned char fold_smem[];
+  double (*Bs)[kFoldBLd] = reinterpret_cast<double (*)[kFoldBLd]>(fold_smem);                                   // b tile: [c][k]
+  double (*Is)[kFoldILd] = reinterpret_cast<double (*)[kFoldILd]>(fold_smem + sizeof(double) * kFoldK * kFoldBLd);  // inverse tile: [c][r]
   const int tid = threadIdx.x;
   const int64_t k0 = (int64_t)blockIdx.x * kRowsPerCta;
 
@@ -152,7 +153,7 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
       __syncthreads();
       // b tile: b[k][c] = (float)((double)yi[k][c] * dQui[k])  (ALSUtils.java:93-95)
       for (int e = tid; e < kFoldK * kRowsPerCta; e += 256) {
-        int kk = e >> 4, c = e & 15;
+        int kk = e / kFoldK, c = e % kFoldK;
         int64_t k = k0 + kk;
         double v = 0.0;
         if (k < n && c0 + c < f) {
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
       }
       // inverse tile: inv[r][c] (row-major)
       for (int e = tid; e < kFoldK * kFoldOut; e += 256) {
-        int r = e >> 4, c = e & 15;
+        int r = e / kFoldK, c = e % kFoldK;
         Is[c][r] = (r0 + r < f && c0 + c < f) ? inv[(size_t)(r0 + r) * f + c0 + c] : 0.0;
       }
       __syncthreads();
@@ -203,6 +204,7 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   }
 }
 
+constexpr size_t kFoldSmem = sizeof(double) * kFoldK * (kFoldBLd + kFoldILd);
 constexpr int64_t kFoldChunk = 1 << 17;  // interactions per pipeline stage
 
 int32_t fold_buf(FoldScratch* fs, int i, size_t bytes, void** out) {
@@ -286,6 +288,7 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
                       uint8_t* out_valid, Stage stage) {
   FoldScratch* fs = solver_fold_scratch(s);
   cudaStream_t st = solver_stream(s);
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(fold_in_kernel), kFoldSmem));
   const auto wall0 = std::chrono::steady_clock::now();
   double kernel_ms = 0;
   int chunks = 0;
@@ -308,7 +311,7 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     if (e != cudaSuccess) break;
     const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
     if ((e = cudaEventRecord(fs->ev_k0[par], st)) != cudaSuccess) break;
-    fold_in_kernel<<<grid, 256, 0, st>>>(solver_inverse(s), f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
+    fold_in_kernel<<<grid, 256, kFoldSmem, st>>>(solver_inverse(s), f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
                                          use_has_yi ? b.d_has_yi : nullptr, b.d_val, c, b.d_out[par], b.d_valid[par]);
     if ((e = cudaGetLastError()) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_k1[par], st)) != cudaSuccess) break;

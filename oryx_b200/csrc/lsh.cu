@@ -54,15 +54,27 @@ __device__ __forceinline__ int lsh_group_bits(const float* __restrict__ y, const
 #pragma unroll
   for (int k = 0; k < G; k++) dot[k] = 0.f;
   const float4* y4 = reinterpret_cast<const float4*>(y);
+  // all loads of a quad first, then the FMAs component by component across the G chains: consecutive
+  // instructions are independent (issuing the four FMAs of one chain back to back left the warp waiting on
+  // the FMA latency), and the unrolled loop has the next quad's loads in flight meanwhile
+#pragma unroll 2
   for (int j = 0; j < f4; j++) {
     const float4 v = y4[j];
-    v2 = fmaf(v.x, v.x, v2); v2 = fmaf(v.y, v.y, v2); v2 = fmaf(v.z, v.z, v2); v2 = fmaf(v.w, v.w, v2);
+    float4 h[G];
 #pragma unroll
-    for (int k = 0; k < G; k++) {
-      const float4 h = reinterpret_cast<const float4*>(s_hv + (size_t)(h0 + k) * ld)[j];  // same address for the whole warp
-      dot[k] = fmaf(v.x, h.x, dot[k]); dot[k] = fmaf(v.y, h.y, dot[k]);
-      dot[k] = fmaf(v.z, h.z, dot[k]); dot[k] = fmaf(v.w, h.w, dot[k]);
-    }
+    for (int k = 0; k < G; k++) h[k] = reinterpret_cast<const float4*>(s_hv + (size_t)(h0 + k) * ld)[j];  // same address for the whole warp
+    v2 = fmaf(v.x, v.x, v2);
+#pragma unroll
+    for (int k = 0; k < G; k++) dot[k] = fmaf(v.x, h[k].x, dot[k]);
+    v2 = fmaf(v.y, v.y, v2);
+#pragma unroll
+    for (int k = 0; k < G; k++) dot[k] = fmaf(v.y, h[k].y, dot[k]);
+    v2 = fmaf(v.z, v.z, v2);
+#pragma unroll
+    for (int k = 0; k < G; k++) dot[k] = fmaf(v.z, h[k].z, dot[k]);
+    v2 = fmaf(v.w, v.w, v2);
+#pragma unroll
+    for (int k = 0; k < G; k++) dot[k] = fmaf(v.w, h[k].w, dot[k]);
   }
   const float vnorm = sqrtf(v2) * bound_scale;
   int bits = 0;
