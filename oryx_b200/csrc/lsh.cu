@@ -54,15 +54,18 @@ __device__ __forceinline__ int lsh_group_bits(const float* __restrict__ y, const
 #pragma unroll
   for (int k = 0; k < G; k++) dot[k] = 0.f;
   const float4* y4 = reinterpret_cast<const float4*>(y);
+  const float4* hp[G];  // row pointers hoisted: the loop body is loads and FMAs only
+#pragma unroll
+  for (int k = 0; k < G; k++) hp[k] = reinterpret_cast<const float4*>(s_hv + (h0 + k) * ld);
   // all loads of a quad first, then the FMAs component by component across the G chains: consecutive
   // instructions are independent (issuing the four FMAs of one chain back to back left the warp waiting on
   // the FMA latency), and the unrolled loop has the next quad's loads in flight meanwhile
-#pragma unroll 2
+#pragma unroll 4
   for (int j = 0; j < f4; j++) {
     const float4 v = y4[j];
     float4 h[G];
 #pragma unroll
-    for (int k = 0; k < G; k++) h[k] = reinterpret_cast<const float4*>(s_hv + (size_t)(h0 + k) * ld)[j];  // same address for the whole warp
+    for (int k = 0; k < G; k++) h[k] = hp[k][j];  // same address for the whole warp
     v2 = fmaf(v.x, v.x, v2);
 #pragma unroll
     for (int k = 0; k < G; k++) dot[k] = fmaf(v.x, h[k].x, dot[k]);
@@ -122,20 +125,30 @@ __global__ void lsh_hash_kernel(const float* __restrict__ rows, int64_t n, int64
   const bool vec4 = (stride & 3) == 0 && ((uintptr_t)rows & 15) == 0;
   for (int64_t row0 = (int64_t)blockIdx.x * tile_rows; row0 < n; row0 += (int64_t)gridDim.x * tile_rows) {
     __syncthreads();
-    for (int r = warp; r < tile_rows; r += nwarps) {
-      const int64_t row = row0 + r;
-      if (row >= n) break;
-      const float* src = rows + row * stride;
-      float* dst = s_rows + (size_t)r * ld;
-      // asynchronous global -> shared copies: every row of the tile is in flight at once (a load-then-store
-      // loop waited for each row's load in turn and left the kernel bound by memory latency)
-      if (vec4) {
-        const int full4 = features >> 2;
-        for (int j = lane; j < full4; j += 32) cp_async_16(dst + 4 * j, src + 4 * j);
-        for (int j = 4 * full4 + lane; j < 4 * f4; j += 32) {
-          if (j < features) cp_async_4(dst + j, src + j); else dst[j] = 0.f;
+    // asynchronous global -> shared copies: every row of the tile is in flight at once (a load-then-store
+    // loop waited for each row's load in turn and left the kernel bound by memory latency)
+    const int rows_here = (int)min((int64_t)tile_rows, n - row0);
+    if (vec4 && (features & 3) == 0) {
+      // the common case (rows 16-byte aligned, features a multiple of 4): one flat loop over the tile's
+      // 16-byte units, a handful of instructions per copy
+      const int q = features >> 2;
+      const float* src0 = rows + row0 * stride;
+      if ((q & (q - 1)) == 0) {
+        const int sh = 31 - __clz(q);
+        for (int e = threadIdx.x; e < rows_here * q; e += blockDim.x) {
+          const int r = e >> sh, j = e & (q - 1);
+          cp_async_16(s_rows + r * ld + 4 * j, src0 + (int64_t)r * stride + 4 * j);
         }
       } else {
+        for (int e = threadIdx.x; e < rows_here * q; e += blockDim.x) {
+          const int r = e / q, j = e - r * q;
+          cp_async_16(s_rows + r * ld + 4 * j, src0 + (int64_t)r * stride + 4 * j);
+        }
+      }
+    } else {
+      for (int r = warp; r < rows_here; r += nwarps) {
+        const float* src = rows + (row0 + r) * stride;
+        float* dst = s_rows + (size_t)r * ld;
         for (int j = lane; j < 4 * f4; j += 32) {
           if (j < features) cp_async_4(dst + j, src + j); else dst[j] = 0.f;
         }
@@ -269,8 +282,11 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
   if (((ld >> 2) & 1) == 0) ld += 4;
   const size_t hv_bytes = ((size_t)H * ld + 16) * sizeof(float);
   const size_t budget = 200 * 1024 - hv_bytes;
-  int tile_rows = (int)std::min<size_t>(128, budget / ((size_t)ld * sizeof(float)));
+  // up to 128 rows per tile, but small enough that three CTAs fit on an SM (their load and compute phases
+  // then overlap); never below one warp
+  int tile_rows = (int)std::min<size_t>(128, std::min<size_t>(budget, 70 * 1024) / ((size_t)ld * sizeof(float)));
   tile_rows = tile_rows / 32 * 32;
+  if (tile_rows < 32 && budget / ((size_t)ld * sizeof(float)) >= 32) tile_rows = 32;
   if (tile_rows < 32) {
     set_error("features=%d too large for the LSH hashing kernel's shared-memory tile", F);
     return ORYX_E_UNSUPPORTED;
