@@ -36,6 +36,7 @@
 #include <cuda_bf16.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -892,11 +893,60 @@ bool batch_topn_supported(Model* m, int nq) {
          encode_tiled_fn() != nullptr;
 }
 
+static int32_t batch_topn_run_pass(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
+                                   const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
+                                   cudaStream_t st, BatchTimings* timings, const int32_t* query_slots, int query_store);
+
 // queries: HOST [nq x features].  Outputs: HOST arrays.  out_n[i] == -1 marks a query the caller must
 // answer unbatched (candidate overflow; pathological score distributions only).
+//
+// The sub-block maxima take nq x (N/32 + N/256) x 4 bytes of scratch (5.8 GB for 4096 queries over 10 M items).
+// That grows with nq x N, so a page is answered in passes of as many queries as fit a scratch budget (8 GB, or
+// ORYX_BATCH_SCRATCH_MB): 4096 queries over 100 M items run as eight passes of 512 instead of asking for 57 GB.
 int32_t batch_topn_run(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
                        const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
                        cudaStream_t st, BatchTimings* timings, const int32_t* query_slots, int query_store) {
+  Store* s = &m->store[ORYX_Y];
+  const char* budget_env = std::getenv("ORYX_BATCH_SCRATCH_MB");  // read per call: tests lower it to force passes
+  const size_t budget = (size_t)std::max<long long>(budget_env ? std::atoll(budget_env) : 8192, 1) << 20;
+  const int64_t n_tiles = (s->n_slots + BN - 1) / BN;
+  const size_t per_query = (size_t)(n_tiles * SUBS_PER_TILE + (n_tiles + 3) / 4 * 4) * 4;
+  int pass = (int)std::min<size_t>((size_t)nq, std::max<size_t>(BM, budget / std::max<size_t>(per_query, 1) / BM * BM));
+  if (pass >= nq)
+    return batch_topn_run_pass(m, kind, queries, nq, how_many, excl_offsets, excl_slots, out_rows, out_scores, out_n, st,
+                               timings, query_slots, query_store);
+  const int F = s->features;
+  BatchTimings total{};
+  std::vector<int32_t> eo;
+  for (int off = 0; off < nq; off += pass) {
+    const int c = std::min(pass, nq - off);
+    const int32_t* eo_p = nullptr;
+    const int32_t* es_p = nullptr;
+    if (excl_offsets) {  // offsets of this pass, rebased to its first exclusion
+      eo.assign((size_t)c + 1, 0);
+      for (int i = 0; i <= c; i++) eo[(size_t)i] = excl_offsets[off + i] - excl_offsets[off];
+      eo_p = eo.data();
+      es_p = excl_slots + excl_offsets[off];
+    }
+    BatchTimings t{};
+    ORYX_TRY(batch_topn_run_pass(m, kind, queries ? queries + (size_t)off * F : nullptr, c, how_many, eo_p, es_p,
+                                 out_rows + (size_t)off * how_many, out_scores + (size_t)off * how_many, out_n + off, st,
+                                 timings ? &t : nullptr, query_slots ? query_slots + off : nullptr, query_store));
+    total.convert_ms += t.convert_ms; total.score_ms += t.score_ms; total.threshold_ms += t.threshold_ms;
+    total.refine_ms += t.refine_ms; total.flops += t.flops; total.shadow_rebuilds += t.shadow_rebuilds;
+    total.cand_mean += t.cand_mean * c / nq; total.cand_max = std::max(total.cand_max, t.cand_max);
+  }
+  if (timings) {
+    total.runs = timings->runs + 1;
+    total.shadow_rebuilds += timings->shadow_rebuilds;
+    *timings = total;
+  }
+  return ORYX_OK;
+}
+
+static int32_t batch_topn_run_pass(Model* m, int kind, const float* queries, int nq, int how_many, const int32_t* excl_offsets,
+                                   const int32_t* excl_slots, int32_t* out_rows, double* out_scores, int32_t* out_n,
+                                   cudaStream_t st, BatchTimings* timings, const int32_t* query_slots, int query_store) {
   Store* s = &m->store[ORYX_Y];
   const int F = s->features, fpad = s->fpad;
   const int kpad = round_up(F, BK), nch = kpad / BK;

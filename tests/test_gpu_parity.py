@@ -519,6 +519,32 @@ def test_topn_batch_tensor_core_path_is_exact(n, f, nq, how_many):
                                   oracle.scores_all(kind, queries[i], y))
 
 
+def test_topn_batch_in_passes_when_scratch_is_bounded():
+    """The sub-block maxima need nq x N / 32 floats of scratch; a page that would exceed the budget is answered
+    in passes of fewer queries.  Same answers, exclusions sliced per pass."""
+    import os
+    n, f, nq, how_many = 40000, 64, 300, 10
+    y = random_model(n, f, seed=0xB2000400)
+    rng = np.random.default_rng(5)
+    q = rng.standard_normal((nq, f), dtype=np.float32)
+    excl = [rng.integers(0, n, int(rng.integers(0, 9))).astype(np.int32) for _ in range(nq)]
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        whole = m.topn_batch(ob.DOT, q, how_many, excluded_lists=excl)
+        os.environ["ORYX_BATCH_SCRATCH_MB"] = "1"      # 1 MB: passes of 128 queries
+        try:
+            runs0 = _batch_counters(m)[0]
+            parts = m.topn_batch(ob.DOT, q, how_many, excluded_lists=excl)
+            assert _batch_counters(m)[0] == runs0 + 1
+        finally:
+            del os.environ["ORYX_BATCH_SCRATCH_MB"]
+        for a, b in zip(whole, parts):
+            assert np.array_equal(a, b)
+        for i in (0, 127, 128, 299):
+            e = oracle.topn(oracle.DOT, q[i], y, how_many, excluded=np.unique(excl[i]) if len(excl[i]) else None)
+            _assert_same_topn((parts[0][i, :parts[2][i]], parts[1][i, :parts[2][i]]), e)
+
+
 @pytest.mark.parametrize("rate,cores", [(0.3, 32), (0.5, 8), (0.1, 8)])
 def test_topn_batch_with_lsh_filtering(rate, cores):
     """With LSH filtering on, a page of queries still rides on the tensor-core path: every query only
