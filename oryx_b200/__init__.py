@@ -6,7 +6,7 @@ the benchmark and Python callers; it contains no compute and has no CPU fallback
 ``oryx_b200.native`` without the built library raises.
 """
 from .native import (COSINE, DOT, X, Y, Exchange, Model, OryxError, SingularMatrixSolverException, Solver,
-                     build, lib, lsh_plan, merge_topn_device, merge_topn_packed, packed_record_bytes)
+                     build, lib, lsh_plan, merge_topn_batch_device, merge_topn_device, merge_topn_packed, packed_record_bytes)
 
 __all__ = ["COSINE", "DOT", "X", "Y", "Exchange", "Model", "OryxError", "SingularMatrixSolverException",
-           "Solver", "build", "lib", "lsh_plan", "merge_topn_device", "merge_topn_packed", "packed_record_bytes"]
+           "Solver", "build", "lib", "lsh_plan", "merge_topn_batch_device", "merge_topn_device", "merge_topn_packed", "packed_record_bytes"]

@@ -922,6 +922,18 @@ int32_t oryx_merge_topn_device(const double* d_scores, const int32_t* d_rows, co
                            d_out_n, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int32_t oryx_merge_topn_batch_device(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int32_t n_lists,
+                                     int32_t nq, int32_t how_many, int64_t row_stride, int64_t* d_out_rows,
+                                     double* d_out_scores, int32_t* d_out_n, void* stream) {
+  ORYX_ARG(d_scores && d_rows && d_n && d_out_rows && d_out_scores && d_out_n, "null argument");
+  ORYX_ARG(n_lists >= 1 && n_lists <= 1024, "n_lists out of range [1, 1024]");
+  ORYX_ARG(nq >= 0, "nq must be >= 0");
+  ORYX_ARG(how_many >= 1 && how_many <= ORYX_MAX_HOW_MANY, "how_many out of range [1, ORYX_MAX_HOW_MANY]");
+  if (nq == 0) return ORYX_OK;
+  return merge_topn_batch_launch(d_scores, d_rows, d_n, n_lists, nq, how_many, row_stride, d_out_rows, d_out_scores, d_out_n,
+                                 reinterpret_cast<cudaStream_t>(stream));
+}
+
 int32_t oryx_merge_topn_packed(const void* d_records, int32_t n_lists, int32_t record_bytes, int32_t how_many,
                                int64_t row_stride, int64_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
                                void* stream) {

@@ -335,6 +335,10 @@ int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const i
                           int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
                           int32_t* d_out_n, cudaStream_t stream);
 
+int32_t merge_topn_batch_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists, int nq,
+                                int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
+                                int32_t* d_out_n, cudaStream_t stream);
+
 int32_t merge_topn_packed_launch(const void* d_records, int n_lists, int record_bytes, int how_many,
                                  int64_t row_stride, int64_t* d_out_rows, double* d_out_scores, int32_t* d_out_n,
                                  cudaStream_t stream);

@@ -91,7 +91,15 @@ __global__ void merge_topn_kernel(const unsigned char* __restrict__ scores_b, co
                                   const unsigned char* __restrict__ counts_b, int64_t scores_stride,
                                   int64_t rows_stride, int64_t counts_stride, int n_lists, int how_many,
                                   int64_t row_stride, int64_t* __restrict__ out_rows,
-                                  double* __restrict__ out_scores, int32_t* __restrict__ out_n) {
+                                  double* __restrict__ out_scores, int32_t* __restrict__ out_n,
+                                  int64_t q_scores_stride = 0, int64_t q_rows_stride = 0, int64_t q_counts_stride = 0) {
+  // one CTA per query (blockIdx.x): a page of queries answered by every shard is merged in one launch
+  scores_b += (int64_t)blockIdx.x * q_scores_stride;
+  rows_b += (int64_t)blockIdx.x * q_rows_stride;
+  counts_b += (int64_t)blockIdx.x * q_counts_stride;
+  out_rows += (int64_t)blockIdx.x * how_many;
+  out_scores += (int64_t)blockIdx.x * how_many;
+  out_n += blockIdx.x;
   // list l: scores at scores_b + l*scores_stride, rows at rows_b + l*rows_stride, count at counts_b + l*counts_stride
   auto score_at = [&](int l, int j) { return reinterpret_cast<const double*>(scores_b + l * scores_stride)[j]; };
   auto row_at = [&](int l, int j) { return reinterpret_cast<const int32_t*>(rows_b + l * rows_stride)[j]; };
@@ -180,6 +188,20 @@ int32_t merge_topn_launch(const double* d_scores, const int32_t* d_rows, const i
                                            reinterpret_cast<const unsigned char*>(d_n), (int64_t)how_many * 8,
                                            (int64_t)how_many * 4, 4, n_lists, how_many, row_stride, d_out_rows,
                                            d_out_scores, d_out_n);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+// d_scores [n_lists][nq][how_many] f64, d_rows [n_lists][nq][how_many] i32, d_n [n_lists][nq] i32 (what every shard's
+// oryx_topn_batch returned, gathered); outputs [nq][how_many] / [nq].
+int32_t merge_topn_batch_launch(const double* d_scores, const int32_t* d_rows, const int32_t* d_n, int n_lists, int nq,
+                                int how_many, int64_t row_stride, int64_t* d_out_rows, double* d_out_scores,
+                                int32_t* d_out_n, cudaStream_t stream) {
+  merge_topn_kernel<<<nq, 256, 0, stream>>>(reinterpret_cast<const unsigned char*>(d_scores),
+                                            reinterpret_cast<const unsigned char*>(d_rows),
+                                            reinterpret_cast<const unsigned char*>(d_n), (int64_t)nq * how_many * 8,
+                                            (int64_t)nq * how_many * 4, (int64_t)nq * 4, n_lists, how_many, row_stride,
+                                            d_out_rows, d_out_scores, d_out_n, (int64_t)how_many * 8, (int64_t)how_many * 4, 4);
   ORYX_CUDA(cudaGetLastError());
   return ORYX_OK;
 }

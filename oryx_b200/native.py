@@ -86,6 +86,8 @@ SIGNATURES = {
     "oryx_topn_device": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_topn_device_static": [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "oryx_merge_topn_batch_device": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_merge_topn_packed": [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "oryx_exchange_create": [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)],
     "oryx_exchange_handle": [C.c_void_p, C.c_char_p],
@@ -457,6 +459,14 @@ def merge_topn_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, how_ma
     _check(lib().oryx_merge_topn_device(C.c_void_p(d_scores), C.c_void_p(d_rows), C.c_void_p(d_n), n_lists,
                                         how_many, row_stride, C.c_void_p(d_out_rows), C.c_void_p(d_out_scores),
                                         C.c_void_p(d_out_n), C.c_void_p(stream)))
+
+
+def merge_topn_batch_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, nq: int, how_many: int, row_stride: int,
+                            d_out_rows: int, d_out_scores: int, d_out_n: int, stream: int):
+    """Merge of every shard's answers to a page of queries, one launch (oryx_merge_topn_batch_device)."""
+    _check(lib().oryx_merge_topn_batch_device(C.c_void_p(d_scores), C.c_void_p(d_rows), C.c_void_p(d_n), n_lists, nq, how_many,
+                                              row_stride, C.c_void_p(d_out_rows), C.c_void_p(d_out_scores),
+                                              C.c_void_p(d_out_n), C.c_void_p(stream)))
 
 
 def packed_record_bytes(how_many: int) -> int:

@@ -230,3 +230,25 @@ def merge_batch_topn(shard_results, row_stride: int, how_many: int):
         out_rows[q, :order.size] = rows[order]
         out_scores[q, :order.size] = scores[order]
     return out_rows, out_scores, out_cnt
+
+
+def merge_batch_topn_device(ob, torch, shard_results, row_stride: int, how_many: int, device, gather=None):
+    """Device half of a sharded oryx_topn_batch: every shard's (rows, scores, counts) for the page are stacked in
+    device memory -- by ``gather`` (e.g. three NCCL all-gathers between processes) or, inside one process, by plain
+    copies -- and merged by ONE launch of oryx_merge_topn_batch_device (one CTA per query).  Returns device tensors
+    (rows int64 [nq x how_many], scores float64, counts int32)."""
+    nq = shard_results[0][0].shape[0]
+    world = len(shard_results)
+    d_rows = torch.stack([torch.as_tensor(r[0], dtype=torch.int32) for r in shard_results]).to(device).contiguous()
+    d_scores = torch.stack([torch.as_tensor(r[1], dtype=torch.float64) for r in shard_results]).to(device).contiguous()
+    d_n = torch.stack([torch.as_tensor(r[2], dtype=torch.int32) for r in shard_results]).to(device).contiguous()
+    if gather is not None:
+        d_rows, d_scores, d_n = gather(d_rows, d_scores, d_n)
+        world = d_n.shape[0]
+    out_rows = torch.zeros((nq, how_many), dtype=torch.int64, device=device)
+    out_scores = torch.zeros((nq, how_many), dtype=torch.float64, device=device)
+    out_n = torch.zeros(nq, dtype=torch.int32, device=device)
+    ob.merge_topn_batch_device(d_scores.data_ptr(), d_rows.data_ptr(), d_n.data_ptr(), world, nq, how_many, row_stride,
+                               out_rows.data_ptr(), out_scores.data_ptr(), out_n.data_ptr(),
+                               torch.cuda.current_stream(device).cuda_stream)
+    return out_rows, out_scores, out_n

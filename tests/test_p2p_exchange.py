@@ -8,20 +8,26 @@ import torch
 
 import oracle
 import oryx_b200 as ob
-from als_harness import random_model
+from als_harness import random_hash_vectors, random_model
 
 pytestmark = pytest.mark.gpu
 
 
-def _run(world, n_per, f, hm, steps, kind=ob.DOT, seed=0xB2000050):
+def _run(world, n_per, f, hm, steps, kind=ob.DOT, seed=0xB2000050, lsh=None, compact=False):
     ys = [random_model(n_per, f, seed + r) for r in range(world)]
     y_all = np.concatenate(ys)
     models, xs, outs, streams, dqs = [], [], [], [], []
     qs = random_model(steps, f, seed + 100)
+    hv, bits, h = None, 0, 0
+    if lsh is not None:                      # (sample_rate, cores): LSH candidate filtering on every shard
+        h, bits = ob.lsh_plan(*lsh)
+        hv = random_hash_vectors(h, f, seed=seed + 7)
     for r in range(world):
         with torch.cuda.device(r):
-            m = ob.Model(f, device=r)
+            m = ob.Model(f, device=r, hash_vectors=hv, max_bits_differing=bits)
             m.upsert(ob.Y, np.arange(n_per, dtype=np.int32), ys[r])
+            if compact:
+                m.compact(ob.Y)
             models.append(m)
             xs.append(ob.Exchange(r, world, r, max(hm, 16)))
             dev = torch.device("cuda", r)
@@ -39,8 +45,10 @@ def _run(world, n_per, f, hm, steps, kind=ob.DOT, seed=0xB2000050):
                        n.data_ptr(), streams[r].cuda_stream)
     for r in range(world):
         streams[r].synchronize()
+    part_all = oracle.lsh_index_rows(hv, y_all) if lsh is not None else None
     for i in range(steps):
-        want_rows, want_scores = oracle.topn(kind, qs[i], y_all, hm)
+        cand = oracle.lsh_candidates(h, bits, oracle.lsh_index(hv, qs[i])) if lsh is not None else None
+        want_rows, want_scores = oracle.topn(kind, qs[i], y_all, hm, part=part_all, cand=cand)
         for r in range(world):
             rows, scores, n = outs[r][i]
             k = int(n.item())
@@ -61,10 +69,24 @@ def test_exchange_world_1_short_shard_and_cosine():
     _run(1, 7, 16, 10, steps=3, kind=ob.COSINE)  # fewer rows than how_many
 
 
+@pytest.mark.parametrize("compact", [False, True])
+def test_exchange_world_1_with_lsh_filtering(compact):
+    _run(1, 40000, 32, 10, steps=8, lsh=(0.3, 32), compact=compact)
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 @pytest.mark.parametrize("hm", [10, 100])
 def test_exchange_two_gpus_matches_oracle(hm):
     _run(2, 50000, 64, hm, steps=40)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("compact", [False, True])
+def test_exchange_two_gpus_with_lsh_filtering(compact):
+    """LSH candidate filtering AND the sharded exchange together: every shard hashes the query itself and scans
+    only its candidate partitions; the merged list equals the oracle's over the concatenated shards."""
+    _run(2, 60000, 48, 10, steps=24, lsh=(0.3, 32), compact=compact)
+    _run(2, 30000, 64, 10, steps=8, kind=ob.COSINE, lsh=(0.5, 8), compact=compact)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs four GPUs")
@@ -139,3 +161,12 @@ def test_sharded_batch_merges_to_the_unsharded_answer():
     for i in range(len(q)):
         wr, ws = oracle.topn(ob.DOT, q[i], y_all, hm)
         assert cnt[i] == len(wr) and rows[i, :cnt[i]].tolist() == wr.tolist() and scores[i, :cnt[i]].tobytes() == ws.tobytes()
+    # the same merge on the device: one launch for the whole page (oryx_merge_topn_batch_device)
+    from oryx_b200.sharded import merge_batch_topn_device
+    d_rows, d_scores, d_cnt = merge_batch_topn_device(ob, torch, res, n_per, hm, torch.device("cuda", 0))
+    torch.cuda.synchronize()
+    assert np.array_equal(d_cnt.cpu().numpy(), cnt)
+    for i in range(len(q)):
+        k = int(cnt[i])
+        assert np.array_equal(d_rows[i, :k].cpu().numpy(), rows[i, :k])
+        assert d_scores[i, :k].cpu().numpy().tobytes() == scores[i, :k].tobytes()
