@@ -188,8 +188,10 @@ def test_empty_and_tiny_models():
         assert len(rows) == 0
         with pytest.raises(ob.OryxError):
             m.topn(ob.DOT, np.ones(5, np.float32), 0)
+        rows, scores = m.topn(ob.DOT, np.ones(5, np.float32), 5000)   # deep page over a one-row model
+        assert list(rows) == [3] and list(scores) == [5.0]
         with pytest.raises(ob.OryxError):
-            m.topn(ob.DOT, np.ones(5, np.float32), 5000)
+            m.topn(ob.DOT, np.ones(5, np.float32), 70000)              # beyond ORYX_MAX_HOW_MANY_DEEP
 
 
 def test_nan_and_ties():
