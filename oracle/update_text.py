@@ -136,3 +136,33 @@ def to_update_json(matrix, ident, vector, other):
 
 def to_feature_line(ident, vector):
     return "[" + _json_string(ident) + "," + format_floats(vector) + "]"
+
+
+def sum_with_nan(ordered_strengths):
+    """MLFunctions.SUM_WITH_NAN (app/oryx-app-common/.../common/fn/MLFunctions.java:67-78): a NaN (a delete)
+    poisons the tally, the next value starts it afresh."""
+    final = float("nan")
+    for s in ordered_strengths:
+        if final != final:
+            final = s
+        else:
+            final += s
+    return final
+
+
+def aggregate_interactions(users, items, strengths, timestamps, implicit):
+    """The aggregation step of ALSSpeedModelManager.buildUpdates (app/oryx-app/.../speed/als/
+    ALSSpeedModelManager.java:141-171): stable sort by timestamp, group by (user, item), SUM_WITH_NAN (implicit)
+    or last-wins (explicit, :164), drop NaN results (:167-168), strength narrowed to float (:171).
+    Returns a dict {(user, item): strength}."""
+    import numpy as np
+    order = sorted(range(len(users)), key=lambda i: timestamps[i])   # sorted() is stable
+    groups = {}
+    for i in order:
+        groups.setdefault((int(users[i]), int(items[i])), []).append(float(strengths[i]))
+    out = {}
+    for key, vals in groups.items():
+        r = sum_with_nan(vals) if implicit else vals[-1]
+        if r == r:
+            out[key] = float(np.float32(r))
+    return out

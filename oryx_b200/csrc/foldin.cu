@@ -14,6 +14,7 @@
 // derives from the same QR factors; everything else is the reference's operation sequence.
 #include <algorithm>
 #include <chrono>
+#include <thread>
 
 #include "common.cuh"
 
@@ -295,7 +296,23 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
   auto finalize = [&](int64_t off, int64_t c, int par) -> cudaError_t {
     cudaError_t e = cudaEventSynchronize(fs->ev_copied[par]);
     if (e != cudaSuccess) return e;
-    std::memcpy(out + off * f, b.h_out[par], (size_t)c * f * sizeof(float));
+    // pinned staging -> the caller's (pageable, often freshly allocated) array: a few threads, because one
+    // core's memcpy and first-touch page faults were what the whole call waited for
+    const size_t bytes = (size_t)c * f * sizeof(float);
+    const int n_thr = bytes >= ((size_t)16 << 20) ? 4 : 1;
+    if (n_thr == 1) {
+      std::memcpy(out + off * f, b.h_out[par], bytes);
+    } else {
+      std::thread workers[4];
+      const size_t piece = (bytes / n_thr + 4095) & ~(size_t)4095;
+      for (int t = 0; t < n_thr; t++) {
+        const size_t lo = std::min(bytes, piece * t), hi = std::min(bytes, piece * (t + 1));
+        workers[t] = std::thread([=, &b] {
+          std::memcpy(reinterpret_cast<char*>(out + off * f) + lo, reinterpret_cast<const char*>(b.h_out[par]) + lo, hi - lo);
+        });
+      }
+      for (int t = 0; t < n_thr; t++) workers[t].join();
+    }
     std::memcpy(out_valid + off, b.h_valid[par], (size_t)c);
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, fs->ev_k0[par], fs->ev_k1[par]) == cudaSuccess) kernel_ms += ms;

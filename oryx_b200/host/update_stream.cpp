@@ -1236,6 +1236,41 @@ std::vector<UserItemStrength> ALSSpeedModelManager::aggregate(const std::vector<
     throw BadMessage("Bad input: " + lines[(size_t)firstBad.load()] + " (" + w + ")");  // :153-156
   }
   std::stable_sort(rows.begin(), rows.end(), [](const Row& a, const Row& b) { return a.timestamp < b.timestamp; });  // :142-143
+  if (model_ && model_->handle() != nullptr && !rows.empty()) {
+    // With a model (hence a GPU) at hand the grouping and the ordered reduction run on the device
+    // (oryx_aggregate_interactions): ids are interned to batch-local integers in order of appearance, so a
+    // user or item the model has not seen yet takes part like any other.
+    std::unordered_map<std::string, int32_t> uid, iid;
+    std::vector<const std::string*> unames, inames;
+    std::vector<int32_t> u(rows.size()), it(rows.size());
+    std::vector<double> st(rows.size());
+    std::vector<int64_t> ts(rows.size());
+    for (size_t k = 0; k < rows.size(); k++) {
+      auto a = uid.emplace(rows[k].user, (int32_t)uid.size());
+      if (a.second) unames.push_back(&a.first->first);
+      auto b = iid.emplace(rows[k].item, (int32_t)iid.size());
+      if (b.second) inames.push_back(&b.first->first);
+      u[k] = a.first->second;
+      it[k] = b.first->second;
+      st[k] = rows[k].strength;
+      ts[k] = rows[k].timestamp;
+    }
+    std::vector<int32_t> ou(rows.size()), oi(rows.size());
+    std::vector<double> os(rows.size());
+    int64_t kept = 0;
+    const int32_t status = oryx_aggregate_interactions(model_->handle(), u.data(), it.data(), st.data(), ts.data(),
+                                                       (int64_t)rows.size(), implicit ? 1 : 0, ou.data(), oi.data(), os.data(), &kept);
+    if (status != ORYX_OK) {
+      char msg[512] = {0};
+      oryx_last_error(msg, sizeof(msg));
+      throw std::runtime_error(std::string("oryx_aggregate_interactions: ") + msg);
+    }
+    std::vector<UserItemStrength> result;
+    result.reserve((size_t)kept);
+    for (int64_t k = 0; k < kept; k++) result.push_back(UserItemStrength{*unames[(size_t)ou[(size_t)k]], *inames[(size_t)oi[(size_t)k]], os[(size_t)k]});
+    return result;
+  }
+  // no model yet (nothing to fold into either): the same reduction on the host
   // (user,item) -> slot in first-appearance order; the key joins the two ids with a byte that cannot
   // appear in either after parsing a line
   std::unordered_map<std::string, size_t> slot;

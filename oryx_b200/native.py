@@ -104,6 +104,7 @@ SIGNATURES = {
     "oryx_solver_destroy": [C.c_void_p],
     "oryx_solve_f2f": [C.c_void_p, _f32p, _f32p],
     "oryx_fold_in_batch": [C.c_void_p, C.c_int32, _f32p, _u8p, _f32p, _f64p, C.c_int64, _f32p, _u8p],
+    "oryx_aggregate_interactions": [C.c_void_p, _i32p, _i32p, _f64p, _i64p, C.c_int64, C.c_int32, _i32p, _i32p, _f64p, _i64p],
     "oryx_last_error": [C.c_char_p, C.c_int32],
     "oryx_stats_get": [C.c_void_p, C.POINTER(_Stats)],
 }
@@ -387,6 +388,21 @@ class Model:
         used = C.c_int64()
         _check(lib().oryx_gram(self._h, which, _ptr(out, C.c_double), C.byref(used)))
         return (out if used.value > 0 else None), used.value
+
+    def aggregate_interactions(self, user_rows, item_rows, strengths, timestamps, implicit: bool):
+        """ALSSpeedModelManager.buildUpdates' aggregation step on the GPU -> (user_rows, item_rows, strengths)."""
+        u = np.ascontiguousarray(user_rows, dtype=np.int32)
+        it = np.ascontiguousarray(item_rows, dtype=np.int32)
+        st = np.ascontiguousarray(strengths, dtype=np.float64)
+        ts = np.ascontiguousarray(timestamps, dtype=np.int64)
+        n = u.size
+        ou, oi, os_ = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        kept = C.c_int64()
+        _check(lib().oryx_aggregate_interactions(self._h, _ptr(u, C.c_int32), _ptr(it, C.c_int32), _ptr(st, C.c_double),
+                                                 _ptr(ts, C.c_int64), n, int(implicit), _ptr(ou, C.c_int32),
+                                                 _ptr(oi, C.c_int32), _ptr(os_, C.c_double), C.byref(kept)))
+        k = kept.value
+        return ou[:k].copy(), oi[:k].copy(), os_[:k].copy()
 
     def debug_batch_timings(self) -> dict:
         """Phase timings (device ms) of the last tensor-core batch answered for this model."""

@@ -193,3 +193,19 @@ def test_managers_fail_loudly_without_a_device():
     with pytest.raises(native.OryxError) as ei:
         mgr.consume([("MODEL", pmml)])  # creating the device model needs a GPU: no CPU fallback
     assert "no CPU fallback" in str(ei.value)
+
+
+def test_oracle_sum_with_nan_reference_vectors():
+    """MLFunctionsTest.testSumWithNaN (app/oryx-app-common/src/test/.../fn/MLFunctionsTest.java:60-67)."""
+    import math
+    from oracle import update_text as ut
+    nan = float("nan")
+    assert ut.sum_with_nan([1.0]) == 1.0
+    assert ut.sum_with_nan([1.0, 2.0, 3.0]) == 6.0
+    assert ut.sum_with_nan([1.0, nan, 3.0]) == 3.0
+    assert math.isnan(ut.sum_with_nan([1.0, 2.0, nan]))
+    assert math.isnan(ut.sum_with_nan([nan]))
+    agg = ut.aggregate_interactions([1, 1, 2, 1], [5, 5, 5, 5], [1.0, 2.5, nan, nan], [30, 10, 5, 20], True)
+    assert agg == {(1, 5): 1.0}          # by time: 2.5, NaN, 1.0 -> the delete resets the tally; (2,5) is dropped
+    agg = ut.aggregate_interactions([1, 1, 2, 1], [5, 5, 5, 5], [1.0, 2.5, nan, 4.0], [30, 10, 5, 20], False)
+    assert agg == {(1, 5): 1.0}          # explicit: last by time wins
