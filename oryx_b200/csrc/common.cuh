@@ -161,9 +161,11 @@ struct QueryCtx {
   int32_t* d_main_index = nullptr;
   // LSH-filtered scans: the candidate (or mixed) 256-slot blocks of the current query, built on the
   // device right after the query is hashed; [0] = count, [1..] = block ids.  Null in a context that
-  // owns no memory (the scan then tests every block itself).
+  // owns no memory (the scan then tests every block itself).  Two lists of worklist_cap entries alternate
+  // per query (worklist_flip): the kernel that fills one zeroes the other's count.
   int32_t* d_worklist = nullptr;
   int64_t worklist_cap = 0;
+  int worklist_flip = 0;
   int32_t* d_out_rows = nullptr;  // [max_k]
   double* d_out_scores = nullptr; // [max_k]
   int32_t* d_out_n = nullptr;
@@ -299,6 +301,8 @@ int32_t lsh_plan(double sample_rate, int num_cores, int* hashes, int* bits);
 int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int stride, int32_t* d_out,
                              cudaStream_t stream, int32_t* d_zero_counter = nullptr, bool early_start = false);
 int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream);
+int32_t lsh_query_worklist_device(Model* m, const float* d_query, int32_t* d_main_index, int32_t* d_worklist,
+                                  int32_t* d_other_count, cudaStream_t stream);
 int32_t lsh_candidates_device(Model* m, const int32_t* d_main_index, int32_t* d_out, int32_t* d_out_n,
                               cudaStream_t stream);
 

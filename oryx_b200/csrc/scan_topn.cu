@@ -207,7 +207,12 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
 
   // A scan released early must still see what its immediate predecessors wrote: the exclusion list
   // (a device-resident known-items list is prepared by a kernel) and, below, the LSH index / work list.
-  if (LSH || p.n_excl > 0) pdl_wait_primary();
+  // An owning context's LSH scan (p.worklist != nullptr) does NOT wait here: griddepcontrol.wait would wait for
+  // the whole chain in front of it -- the previous query's finishing kernel included (measured, round 2: 29 us
+  // between two pipelined filtered scans = that kernel's duration).  Its inputs are complete anyway: the kernel
+  // that hashes the query and builds the list never releases its dependents early, so this grid is launched
+  // only after every thread of it has fenced its writes and exited; they are read with ld.global.cg below.
+  if ((LSH && p.worklist == nullptr) || p.n_excl > 0) pdl_wait_primary();
   const int32_t* excl = p.excl_in_smem ? s_excl_buf : p.excl;
   if (p.excl_in_smem) {
     for (int i = tid; i < p.n_excl; i += T) s_excl_buf[i] = __ldg(p.excl + i);
@@ -224,7 +229,7 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
     int idx = gl + v * G;
     qv[v] = idx < f4 ? __ldg(reinterpret_cast<const float4*>(p.q) + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  const int main_idx = LSH ? __ldg(p.main_index) : 0;
+  const int main_idx = LSH ? __ldcg(p.main_index) : 0;
   const bool full_width = (f4 == G * NV);  // every lane's every float4 is inside the row
 
   const int warps_total = (int)gridDim.x * (T / 32);
@@ -368,9 +373,9 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
     if (p.worklist != nullptr) {
       // the candidate blocks were listed on the device after the query was hashed: every work item
       // below is real work, so the hybrid schedule balances it like an unfiltered scan
-      const int n_items = __ldg(p.worklist) * units_per_block;
+      const int n_items = __ldcg(p.worklist) * units_per_block;
       for_each_tile(n_items, [&](int w) {
-        const int b = __ldg(p.worklist + 1 + w / units_per_block);
+        const int b = __ldcg(p.worklist + 1 + w / units_per_block);
         scan_unit(b * units_per_block + (w % units_per_block), __ldg(p.block_part + b));
       });
     } else {
@@ -794,6 +799,7 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
     return ORYX_OK;
   }
   const bool lsh = s->hashed && m->num_hashes != m->max_bits;  // LSH.java:160-162: all partitions otherwise
+  int32_t* worklist = nullptr;
   if (lsh) {
     const bool owns = ctx->scratch_sets == 2;  // a context that owns memory: list the candidate blocks
     if (owns) {
@@ -803,23 +809,27 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
         ctx->d_worklist = nullptr;
         ctx->worklist_cap = 0;
         const int64_t cap = (s->cap_slots + kBlockRows - 1) / kBlockRows + 2;
-        ORYX_CUDA(cudaMalloc(&ctx->d_worklist, (size_t)cap * sizeof(int32_t)));
+        ORYX_CUDA(cudaMalloc(&ctx->d_worklist, 2 * (size_t)cap * sizeof(int32_t)));
+        ORYX_CUDA(cudaMemsetAsync(ctx->d_worklist, 0, 2 * (size_t)cap * sizeof(int32_t), stream));  // both counts start at zero
         ctx->worklist_cap = cap;
       }
+      // One launch hashes the query and lists its candidate blocks.  It depends on nothing earlier in the
+      // stream, so it starts while the previous query's finishing kernel still runs; the previous scan (the
+      // only reader of main_index and of the work lists) has completed by then, because the finishing kernel
+      // that releases us is itself only launched when its scan has exited.
+      worklist = ctx->d_worklist + (size_t)(ctx->worklist_flip ^= 1) * ctx->worklist_cap;
+      ORYX_TRY(lsh_query_worklist_device(m, rq.d_query, ctx->d_main_index, worklist,
+                                         ctx->d_worklist + (size_t)(ctx->worklist_flip ^ 1) * ctx->worklist_cap, stream));
+    } else {
+      ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream, nullptr, false));
     }
-    // Hashing the query depends on nothing earlier in the stream, so it starts while the previous
-    // query's finishing kernel still runs; the previous scan (the only reader of main_index and of the
-    // work list) has completed by then, because the finishing kernel that releases us waits for it.
-    ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream,
-                                  owns ? ctx->d_worklist : nullptr, owns));
-    if (owns) ORYX_TRY(lsh_worklist_device(m, ctx->d_main_index, ctx->d_worklist, stream));
   }
   ScanParams p{};
   p.y = reinterpret_cast<const float4*>(s->d_vec);
   p.slot_row = s->d_slot_row;
   p.slot_part = s->d_slot_part;
   p.block_part = s->d_block_part;
-  p.worklist = (lsh && ctx->scratch_sets == 2) ? ctx->d_worklist : nullptr;
+  p.worklist = worklist;
   p.q = rq.d_query;
   p.excl = rq.d_excl;
   p.n_excl = rq.n_excl;

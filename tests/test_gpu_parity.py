@@ -248,6 +248,45 @@ def test_lsh_bit_exact_and_filtered_topn(rate, cores, f):
         assert p[0] == oracle.lsh_index(hv, newv)
 
 
+@pytest.mark.parametrize("compact", [False, True])
+def test_lsh_pipelined_device_queries_match_oracle(compact):
+    """oryx_topn_device calls queued back to back on one stream, LSH on: every query is hashed and its candidate
+    blocks are listed by one kernel, and the scan that follows is released without waiting for the previous
+    query's finishing kernel (scan_topn.cu).  Each answer must still be the oracle's for ITS query."""
+    import torch
+    f, n, hm, nq = 64, 300_000, 10, 96
+    h, bits = ob.lsh_plan(0.3, 32)
+    hv = random_hash_vectors(h, f, seed=41)
+    y = random_model(n, f, seed=42)
+    qs = np.random.default_rng(43).standard_normal((nq, f)).astype(np.float32)
+    # a few queries that sit on a hash hyperplane (the exact fallback decides their bit)
+    qs[5] = hv[1]
+    qs[6] = np.float32(1e-30)
+    parts = oracle.lsh_index_rows(hv, y)
+    dev = torch.device("cuda", 0)
+    with ob.Model(f, hash_vectors=hv, max_bits_differing=bits, capacity_hint=n) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        if compact:
+            m.compact(ob.Y)
+        d_q = torch.from_numpy(qs).to(dev)
+        d_rows = torch.full((nq, hm), -1, dtype=torch.int32, device=dev)
+        d_scores = torch.zeros((nq, hm), dtype=torch.float64, device=dev)
+        d_n = torch.zeros(nq, dtype=torch.int32, device=dev)
+        st = torch.cuda.current_stream(dev)
+        torch.cuda.synchronize()
+        for rep in range(3):
+            for i in range(nq):
+                m.topn_device(ob.DOT, d_q[i].data_ptr(), hm, d_rows[i].data_ptr(), d_scores[i].data_ptr(),
+                              d_n[i:].data_ptr(), st.cuda_stream)
+        torch.cuda.synchronize()
+        rows, scores, cnt = d_rows.cpu().numpy(), d_scores.cpu().numpy(), d_n.cpu().numpy()
+        for i in range(nq):
+            main = oracle.lsh_index(hv, qs[i])
+            cand = oracle.lsh_candidates(h, bits, main)
+            exp = oracle.topn(ob.DOT, qs[i], y, hm, part=parts, cand=cand)
+            _assert_same_topn((rows[i, :cnt[i]], scores[i, :cnt[i]]), exp)
+
+
 @pytest.mark.parametrize("f,h", [(128, 5), (50, 8), (33, 16), (256, 3)])
 def test_lsh_index_near_orthogonal_and_degenerate_rows(f, h):
     """The hashing kernel calls a sign from fp32 arithmetic only when the value clears a rigorous error
