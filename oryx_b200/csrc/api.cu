@@ -405,6 +405,7 @@ int32_t oryx_model_destroy(oryx_model* mh) {
     for (auto& b : m->batch.buf) cudaFree(b);
     for (auto& e : m->batch.ev) if (e) cudaEventDestroy(e);
     cudaFree(m->d_debug_ts);
+    cudaFree(m->d_share_desc);
     if (m->async_done) cudaEventDestroy(m->async_done);
     if (m->update_stream) cudaStreamDestroy(m->update_stream);
     cudaGetLastError();

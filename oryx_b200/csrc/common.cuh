@@ -109,11 +109,15 @@ struct Store {
 
   std::vector<int32_t> row2slot;
   std::vector<int32_t> free_slots;
-  // Device copy of row -> slot (-1 = absent), kept for the Y store only: lets a query translate a
-  // device-resident list of known-item ROWS into the slots the scan filters on (known.cu).
+  // Device copy of row -> slot (-1 = absent): lets a query translate a device-resident list of known-item
+  // ROWS into the slots the scan filters on (known.cu), and lets a peer process gather rows by row id
+  // (peer_stores.cu).
   bool track_row_slot = false;
   int32_t* d_row_slot = nullptr;
   int64_t row_slot_cap = 0;
+  // Bumped whenever d_vec or d_row_slot is reallocated; mirrored in Model::d_share_desc once the stores
+  // have been exported to peer processes, so that a peer holding a stale mapping fails instead of reading it.
+  unsigned long long layout_gen = 1;
 
   int64_t device_bytes() const { return cap_slots * ((int64_t)fpad * 4 + 8) + row_slot_cap * 4; }
 };
@@ -246,6 +250,7 @@ struct Model {
   BatchScratch batch;
   BatchTimings last_batch;  // phase timings of the most recent tensor-core batch (oryx_debug_batch_timings)
   unsigned long long* d_debug_ts = nullptr;  // development aid, see oryx_debug_scan_timestamps
+  unsigned long long* d_share_desc = nullptr;  // [2] layout_gen of X and Y, read by peer processes (peer_stores.cu)
   QueryCtx* async_ctx = nullptr;  // dedicated to oryx_topn_device (stream-ordered by the caller)
   // The stream-ordered entry points return with their kernels still queued on the CALLER's stream.  Each
   // records this event behind its launches; every mutator makes update_stream wait for it before touching

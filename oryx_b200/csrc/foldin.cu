@@ -73,6 +73,48 @@ __global__ void gather_rows_sharded_kernel(const __grid_constant__ ShardBases sh
   if (lane == 0 && has) has[w] = slot >= 0 ? 1 : 0;
 }
 
+// The same over shards that live in other PROCESSES (peer_stores below): interaction i names a GLOBAL row;
+// its owner is row / stride, the slot comes from the owner's device row -> slot table and the row from the
+// owner's vector array -- both mapped through CUDA IPC, read with plain loads over NVLink.  One warp per
+// interaction: lane 0 looks the slot up, every lane copies its share of the row once.
+struct PeerView {
+  const float* vec[ORYX_MAX_WORLD];
+  const int32_t* row_slot[ORYX_MAX_WORLD];
+  long long row_slot_cap[ORYX_MAX_WORLD];
+  long long cap_slots[ORYX_MAX_WORLD];
+  int world;
+};
+__global__ void gather_rows_peers_kernel(const __grid_constant__ PeerView pv, long long stride, int fpad, int f,
+                                         const long long* __restrict__ rows, int64_t n, float* __restrict__ out,
+                                         uint8_t* __restrict__ has) {
+  const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (w >= n) return;
+  const long long row = rows[w];
+  int owner = 0;
+  int32_t slot = -1;
+  if (lane == 0 && row >= 0) {
+    const long long r = row / stride;
+    if (r < pv.world && pv.row_slot[r] != nullptr) {
+      const long long local = row - r * stride;
+      if (local < pv.row_slot_cap[r]) {
+        const int32_t sl = pv.row_slot[r][local];
+        if (sl >= 0 && sl < pv.cap_slots[r]) { slot = sl; owner = (int)r; }
+      }
+    }
+  }
+  slot = __shfl_sync(0xffffffffu, slot, 0);
+  owner = __shfl_sync(0xffffffffu, owner, 0);
+  float* dst = out + w * f;
+  if (slot >= 0) {
+    const float* src = pv.vec[owner] + (int64_t)slot * fpad;
+    for (int j = lane; j < f; j += 32) dst[j] = src[j];
+  } else {
+    for (int j = lane; j < f; j += 32) dst[j] = 0.f;
+  }
+  if (lane == 0 && has) has[w] = slot >= 0 ? 1 : 0;
+}
+
 // ALSUtils.java:37-59
 __device__ __forceinline__ double target_qui(bool implicit, double value, double current) {
   if (implicit) {
@@ -386,7 +428,251 @@ void fold_scratch_free(FoldScratch* fs) {
 
 using namespace oryx;
 
+// ---- stores of other processes (oryx_peer_stores_*): what one rank knows about every rank's X and Y.
+namespace {
+
+constexpr uint32_t kPeerMagic = 0x4f525950u;  // "ORYP"
+
+struct PeerStoreWire {
+  uint32_t present;               // 0: the store holds nothing that could be mapped (no rows yet)
+  uint32_t pad;
+  unsigned long long gen;         // Store::layout_gen when the handle was made
+  long long row_slot_cap, cap_slots;
+  cudaIpcMemHandle_t vec, row_slot;
+};
+struct PeerWire {
+  uint32_t magic, version;
+  int32_t device, features, fpad, rank;
+  PeerStoreWire st[2];
+  cudaIpcMemHandle_t desc;        // the owner's [2] layout generations
+};
+static_assert(sizeof(PeerWire) <= ORYX_PEER_STORES_HANDLE_BYTES, "handle size");
+
+struct PeerRank {
+  bool connected = false;
+  void* vec[2] = {nullptr, nullptr};
+  void* row_slot[2] = {nullptr, nullptr};
+  unsigned long long* desc = nullptr;
+  unsigned long long gen[2] = {0, 0};
+  long long row_slot_cap[2] = {0, 0}, cap_slots[2] = {0, 0};
+  bool opened_vec[2] = {false, false}, opened_rs[2] = {false, false}, opened_desc = false;
+};
+
+void peer_rank_close(PeerRank* r) {
+  for (int w = 0; w < 2; w++) {
+    if (r->opened_vec[w]) cudaIpcCloseMemHandle(r->vec[w]);
+    if (r->opened_rs[w]) cudaIpcCloseMemHandle(r->row_slot[w]);
+  }
+  if (r->opened_desc) cudaIpcCloseMemHandle(r->desc);
+  cudaGetLastError();
+  *r = PeerRank{};
+}
+
+}  // namespace
+
+struct oryx_peer_stores {
+  Model* m = nullptr;
+  int world = 1, rank = 0;
+  PeerRank peer[ORYX_MAX_WORLD];
+  unsigned long long* h_gens = nullptr;  // pinned [world x 2]: the owners' current generations, read per call
+};
+
 extern "C" {
+
+int32_t oryx_peer_stores_create(oryx_model* mh, int32_t world, int32_t rank, oryx_peer_stores** out) {
+  ORYX_ARG(mh && out, "null argument");
+  ORYX_ARG(world >= 1 && world <= ORYX_MAX_WORLD, "world out of range [1, ORYX_MAX_WORLD]");
+  ORYX_ARG(rank >= 0 && rank < world, "rank out of range");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
+  auto* p = new (std::nothrow) oryx_peer_stores();
+  if (!p) { set_error("host allocation failed"); return ORYX_E_NOMEM; }
+  p->m = m;
+  p->world = world;
+  p->rank = rank;
+  if (cudaMallocHost(&p->h_gens, sizeof(unsigned long long) * 2 * ORYX_MAX_WORLD) != cudaSuccess) {
+    cudaGetLastError();
+    delete p;
+    set_error("pinned allocation failed");
+    return ORYX_E_NOMEM;
+  }
+  *out = p;
+  return ORYX_OK;
+}
+
+int32_t oryx_peer_stores_handle(oryx_peer_stores* p, void* out_handle) {
+  ORYX_ARG(p && out_handle, "null argument");
+  Model* m = p->m;
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
+  std::unique_lock<std::shared_mutex> lk(m->mu);  // the stores must not move while they are described
+  if (m->d_share_desc == nullptr) {
+    ORYX_CUDA(cudaMalloc(&m->d_share_desc, 256));
+    ORYX_CUDA(cudaMemset(m->d_share_desc, 0, 256));
+  }
+  unsigned long long gens[2] = {m->store[0].layout_gen, m->store[1].layout_gen};
+  ORYX_CUDA(cudaMemcpy(m->d_share_desc, gens, sizeof(gens), cudaMemcpyHostToDevice));
+  PeerWire w{};
+  w.magic = kPeerMagic;
+  w.version = 1;
+  w.device = m->device;
+  w.features = m->cfg.features;
+  w.fpad = m->store[ORYX_Y].fpad;
+  w.rank = p->rank;
+  ORYX_CUDA(cudaIpcGetMemHandle(&w.desc, m->d_share_desc));
+  for (int which = 0; which < 2; which++) {
+    const Store* s = &m->store[which];
+    PeerStoreWire& sw = w.st[which];
+    sw.gen = s->layout_gen;
+    if (s->d_vec == nullptr || s->d_row_slot == nullptr) continue;  // nothing stored yet: every row is absent
+    sw.present = 1;
+    sw.row_slot_cap = s->row_slot_cap;
+    sw.cap_slots = s->cap_slots;
+    ORYX_CUDA(cudaIpcGetMemHandle(&sw.vec, s->d_vec));
+    ORYX_CUDA(cudaIpcGetMemHandle(&sw.row_slot, s->d_row_slot));
+  }
+  std::memset(out_handle, 0, ORYX_PEER_STORES_HANDLE_BYTES);
+  std::memcpy(out_handle, &w, sizeof(w));
+  return ORYX_OK;
+}
+
+int32_t oryx_peer_stores_connect(oryx_peer_stores* p, const void* handles) {
+  ORYX_ARG(p && handles, "null argument");
+  Model* m = p->m;
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
+  for (int r = 0; r < p->world; r++) peer_rank_close(&p->peer[r]);
+  for (int r = 0; r < p->world; r++) {
+    PeerRank& pr = p->peer[r];
+    if (r == p->rank) {  // own stores: used directly, re-read on every call
+      pr.connected = true;
+      continue;
+    }
+    PeerWire w;
+    std::memcpy(&w, reinterpret_cast<const unsigned char*>(handles) + (size_t)r * ORYX_PEER_STORES_HANDLE_BYTES, sizeof(w));
+    if (w.magic != kPeerMagic || w.version != 1 || w.rank != r) {
+      set_error("entry %d of the handle table is not rank %d's oryx_peer_stores_handle", r, r);
+      return ORYX_E_INVALID;
+    }
+    if (w.features != m->cfg.features || w.fpad != m->store[ORYX_Y].fpad) {
+      set_error("rank %d stores %d features, this rank %d", r, w.features, m->cfg.features);
+      return ORYX_E_INVALID;
+    }
+    auto open = [&](const cudaIpcMemHandle_t& h, void** ptr, const char* what) -> int32_t {
+      cudaError_t e = cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("cannot map %s of rank %d into rank %d (cudaIpcOpenMemHandle: %s)", what, r, p->rank, cudaGetErrorString(e));
+        return ORYX_E_CUDA;
+      }
+      return ORYX_OK;
+    };
+    void* d = nullptr;
+    ORYX_TRY(open(w.desc, &d, "the layout descriptor"));
+    pr.desc = reinterpret_cast<unsigned long long*>(d);
+    pr.opened_desc = true;
+    for (int which = 0; which < 2; which++) {
+      pr.gen[which] = w.st[which].gen;
+      if (!w.st[which].present) continue;
+      ORYX_TRY(open(w.st[which].vec, &pr.vec[which], "a vector array"));
+      pr.opened_vec[which] = true;
+      ORYX_TRY(open(w.st[which].row_slot, &pr.row_slot[which], "a row->slot table"));
+      pr.opened_rs[which] = true;
+      pr.row_slot_cap[which] = w.st[which].row_slot_cap;
+      pr.cap_slots[which] = w.st[which].cap_slots;
+    }
+    pr.connected = true;
+  }
+  return ORYX_OK;
+}
+
+int32_t oryx_peer_stores_destroy(oryx_peer_stores* p) {
+  if (!p) return ORYX_OK;
+  ScopedDevice dev(p->m->device);
+  for (int r = 0; r < p->world; r++) peer_rank_close(&p->peer[r]);
+  cudaFreeHost(p->h_gens);
+  cudaGetLastError();
+  delete p;
+  return ORYX_OK;
+}
+
+int32_t oryx_fold_in_rows_peers(oryx_solver* sh, oryx_peer_stores* p, int64_t xu_row_stride, int64_t yi_row_stride,
+                                int32_t implicit, int32_t xu_which, const int64_t* xu_rows, const int64_t* yi_rows,
+                                const double* values, int64_t n, float* out, uint8_t* out_valid) {
+  ORYX_ARG(sh && p && xu_rows && yi_rows && values && out && out_valid, "null argument");
+  ORYX_ARG(xu_which == ORYX_X || xu_which == ORYX_Y, "xu_which must be ORYX_X or ORYX_Y");
+  ORYX_ARG(xu_row_stride > 0 && yi_row_stride > 0, "row strides must be positive");
+  ORYX_ARG(n >= 0, "n must be >= 0");
+  if (n == 0) return ORYX_OK;
+  Solver* s = reinterpret_cast<Solver*>(sh);
+  Model* m = p->m;
+  const int f = solver_n(s);
+  ORYX_ARG(f == m->cfg.features, "solver and model disagree on the number of features");
+  ORYX_ARG(solver_device(s) == m->device, "solver and model live on different devices");
+  for (int r = 0; r < p->world; r++) ORYX_ARG(p->peer[r].connected, "oryx_peer_stores_connect has not succeeded");
+  ScopedDevice dev(m->device);
+  if (!dev.ok) return ORYX_E_CUDA;
+  std::lock_guard<std::mutex> lk(solver_mutex(s));
+  std::shared_lock<std::shared_mutex> model_lock(m->mu);  // the own stores must not move while rows are gathered
+  cudaStream_t st = solver_stream(s);
+  // a peer whose arrays moved since the handles were exchanged must not be read through the old mapping
+  for (int r = 0; r < p->world; r++) {
+    if (r == p->rank) continue;
+    ORYX_CUDA(cudaMemcpyAsync(p->h_gens + 2 * r, p->peer[r].desc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  }
+  ORYX_CUDA(cudaStreamSynchronize(st));
+  for (int r = 0; r < p->world; r++) {
+    if (r == p->rank) continue;
+    for (int which = 0; which < 2; which++) {
+      if (p->h_gens[2 * r + which] != p->peer[r].gen[which]) {
+        set_error("the %s store of rank %d moved after its handle was exchanged: exchange fresh oryx_peer_stores handles",
+                  which == ORYX_X ? "X" : "Y", r);
+        return ORYX_E_INVALID;
+      }
+    }
+  }
+  const int yi_which = xu_which == ORYX_X ? ORYX_Y : ORYX_X;
+  auto view = [&](int which) {
+    PeerView v{};
+    v.world = p->world;
+    for (int r = 0; r < p->world; r++) {
+      if (r == p->rank) {
+        const Store* own = &m->store[which];
+        v.vec[r] = own->d_vec;
+        v.row_slot[r] = own->d_vec ? own->d_row_slot : nullptr;
+        v.row_slot_cap[r] = own->row_slot_cap;
+        v.cap_slots[r] = own->cap_slots;
+      } else {
+        v.vec[r] = reinterpret_cast<const float*>(p->peer[r].vec[which]);
+        v.row_slot[r] = reinterpret_cast<const int32_t*>(p->peer[r].row_slot[which]);
+        v.row_slot_cap[r] = p->peer[r].row_slot_cap[which];
+        v.cap_slots[r] = p->peer[r].cap_slots[which];
+      }
+    }
+    return v;
+  };
+  const PeerView vx = view(xu_which), vy = view(yi_which);
+  const int fpad = m->store[ORYX_Y].fpad;
+  FoldBuffers b{};
+  ORYX_TRY(fold_prepare(solver_fold_scratch(s), f, n, true, &b));
+  const int64_t cm = b.c_max;
+  return fold_pipeline(s, b, f, implicit, n, true, out, out_valid, [&](int64_t off, int64_t c, int par) -> cudaError_t {
+    // the index buffers hold [2 x c_max] 64-bit global rows here: xu rows, then yi rows
+    long long* h = reinterpret_cast<long long*>(b.h_idx[par]);
+    std::memcpy(h, xu_rows + off, (size_t)c * sizeof(long long));
+    std::memcpy(h + cm, yi_rows + off, (size_t)c * sizeof(long long));
+    long long* d = reinterpret_cast<long long*>(b.d_idx);
+    cudaError_t e = cudaMemcpyAsync(d, h, (size_t)cm * 2 * sizeof(long long), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(b.d_val, values + off, (size_t)c * sizeof(double), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    const unsigned g = (unsigned)((c * 32 + 255) / 256);
+    gather_rows_peers_kernel<<<g, 256, 0, st>>>(vx, (long long)xu_row_stride, fpad, f, d, c, b.d_xu, b.d_has_xu);
+    gather_rows_peers_kernel<<<g, 256, 0, st>>>(vy, (long long)yi_row_stride, fpad, f, d + cm, c, b.d_yi, b.d_has_yi);
+    m->launches += 2;
+    return cudaGetLastError();
+  });
+}
 
 int32_t oryx_fold_in_batch(oryx_solver* sh, int32_t implicit, const float* xu, const uint8_t* has_xu,
                            const float* yi, const double* values, int64_t n, float* out, uint8_t* out_valid) {

@@ -155,6 +155,16 @@ __global__ void compact_move_kernel(float4* __restrict__ vec, int f4, const int3
   }
 }
 
+// The store's device arrays moved (or went away): peers that mapped them (peer_stores.cu) must notice.
+void layout_changed(Model* m, Store* s) {
+  s->layout_gen++;
+  if (m->d_share_desc) {
+    const int which = (int)(s - &m->store[0]);
+    cudaMemcpy(m->d_share_desc + which, &s->layout_gen, sizeof(unsigned long long), cudaMemcpyHostToDevice);
+    cudaGetLastError();
+  }
+}
+
 int32_t grow(Model* m, Store* s, int64_t need) {
   if (need <= s->cap_slots) return ORYX_OK;
   int64_t cap = std::max<int64_t>(need, s->cap_slots + s->cap_slots / 2);
@@ -194,6 +204,7 @@ int32_t grow(Model* m, Store* s, int64_t need) {
   cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(s->d_block_part);
   s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np; s->d_block_part = nbp;
   s->cap_slots = cap;
+  layout_changed(m, s);
   return ORYX_OK;
 }
 
@@ -272,6 +283,7 @@ int32_t assign_slots(Model* m, Store* s, const int32_t* rows, int64_t n, int32_t
     cudaFree(s->d_row_slot);
     s->d_row_slot = nrs;
     s->row_slot_cap = cap;
+    layout_changed(m, s);
   }
   // Count new slots needed first so the device buffers can grow before any kernel runs.
   int64_t fresh = 0;
@@ -317,7 +329,7 @@ int32_t store_init(Model* m, int which, int64_t capacity_hint) {
   s->features = m->cfg.features;
   s->fpad = round_up(m->cfg.features, 4);
   s->hashed = (which == ORYX_Y) && m->num_hashes > 0;
-  s->track_row_slot = which == ORYX_Y;
+  s->track_row_slot = true;  // Y: known-items exclusion lists; both: rows gathered by peers (peer_stores.cu)
   ORYX_CUDA(cudaMalloc(&s->d_absmax_bits, sizeof(unsigned int)));
   ORYX_CUDA(cudaMemset(s->d_absmax_bits, 0, sizeof(unsigned int)));
   if (capacity_hint > 0) ORYX_TRY(grow(m, s, capacity_hint));
@@ -654,6 +666,7 @@ int32_t store_compact(Model* m, int which) {
   ORYX_CUDA(cudaStreamSynchronize(st));
   cudaFree(s->d_vec); cudaFree(s->d_slot_row); cudaFree(s->d_slot_part); cudaFree(d_src);
   s->d_vec = nv; s->d_slot_row = nr; s->d_slot_part = np;
+  layout_changed(m, s);
   s->cap_slots = cap;  // unchanged, so d_block_part keeps its size
   s->n_slots = live;
   s->free_slots.clear();

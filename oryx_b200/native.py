@@ -99,6 +99,12 @@ SIGNATURES = {
     "oryx_fold_in_rows": [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, _i32p, _i32p, _f64p, C.c_int64, _f32p, _u8p],
     "oryx_fold_in_rows_sharded": [C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                   _i64p, _i64p, _f64p, C.c_int64, _f32p, _u8p],
+    "oryx_peer_stores_create": [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)],
+    "oryx_peer_stores_handle": [C.c_void_p, C.c_char_p],
+    "oryx_peer_stores_connect": [C.c_void_p, C.c_char_p],
+    "oryx_peer_stores_destroy": [C.c_void_p],
+    "oryx_fold_in_rows_peers": [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _i64p, _i64p, _f64p,
+                                C.c_int64, _f32p, _u8p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
@@ -470,6 +476,39 @@ class Exchange:
             pass
 
 
+class PeerStores:
+    """This rank's view of every rank's X and Y stores when the ranks are separate processes
+    (oryx_peer_stores_*): exchange `handle()`s (e.g. with torch.distributed.all_gather), `connect`, then
+    `Solver.fold_in_rows_peers` gathers rows of any rank by global row id over NVLink."""
+
+    HANDLE_BYTES = 512
+
+    def __init__(self, model: "Model", world: int, rank: int):
+        self._h = C.c_void_p()
+        self.world, self.rank = world, rank
+        _check(lib().oryx_peer_stores_create(model._h, world, rank, C.byref(self._h)))
+
+    def handle(self) -> bytes:
+        buf = C.create_string_buffer(self.HANDLE_BYTES)
+        _check(lib().oryx_peer_stores_handle(self._h, buf))
+        return buf.raw
+
+    def connect(self, handles):
+        """handles: `world` handles of HANDLE_BYTES in rank order (the own entry is ignored)."""
+        _check(lib().oryx_peer_stores_connect(self._h, b"".join(handles)))
+
+    def close(self):
+        if self._h:
+            lib().oryx_peer_stores_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def merge_topn_device(d_scores: int, d_rows: int, d_n: int, n_lists: int, how_many: int, row_stride: int,
                       d_out_rows: int, d_out_scores: int, d_out_n: int, stream: int):
     _check(lib().oryx_merge_topn_device(C.c_void_p(d_scores), C.c_void_p(d_rows), C.c_void_p(d_n), n_lists,
@@ -560,6 +599,20 @@ class Solver:
         _check(lib().oryx_fold_in_rows_sharded(self._h, arr, len(models), xu_row_stride, yi_row_stride, int(implicit),
                                                xu_which, _ptr(xr, C.c_int64), _ptr(yr, C.c_int64),
                                                _ptr(vals, C.c_double), n, _ptr(out, C.c_float), _ptr(valid, C.c_uint8)))
+        return out, valid
+
+    def fold_in_rows_peers(self, peers: "PeerStores", xu_row_stride: int, yi_row_stride: int, implicit: bool,
+                           xu_which: int, xu_rows, yi_rows, values):
+        """fold_in_rows over stores sharded by rows across PROCESSES (global int64 rows; oryx_fold_in_rows_peers)."""
+        xr = np.ascontiguousarray(xu_rows, dtype=np.int64)
+        yr = np.ascontiguousarray(yi_rows, dtype=np.int64)
+        vals = np.ascontiguousarray(values, dtype=np.float64)
+        n = xr.size
+        out = np.empty((n, self.n), dtype=np.float32)
+        valid = np.zeros(n, dtype=np.uint8)
+        _check(lib().oryx_fold_in_rows_peers(self._h, peers._h, xu_row_stride, yi_row_stride, int(implicit), xu_which,
+                                             _ptr(xr, C.c_int64), _ptr(yr, C.c_int64), _ptr(vals, C.c_double), n,
+                                             _ptr(out, C.c_float), _ptr(valid, C.c_uint8)))
         return out, valid
 
     def fold_in_rows(self, model: "Model", implicit: bool, xu_which: int, xu_rows, yi_rows, values):

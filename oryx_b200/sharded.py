@@ -203,6 +203,22 @@ def allreduce_gram(dist, torch, gram_partial):
     return gram_partial
 
 
+def connect_peer_stores(ob, dist, torch, model, rank: int, world: int, peers=None):
+    """Every rank (one process per GPU) describes its X and Y stores to the others and maps theirs
+    (oryx_peer_stores_*): returns a ``PeerStores`` for ``Solver.fold_in_rows_peers``.  Collective: all ranks call
+    it together -- also again, with ``peers`` = the previous object, after any rank's store was reallocated."""
+    peers = peers if peers is not None else ob.PeerStores(model, world, rank)
+    mine = torch.frombuffer(bytearray(peers.handle()), dtype=torch.uint8)
+    cuda = dist.get_backend() == "nccl"
+    if cuda:
+        mine = mine.to(torch.device("cuda", torch.cuda.current_device()))
+    gathered = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(gathered, mine)
+    peers.connect([bytes(g.cpu().numpy().tobytes()) for g in gathered])
+    dist.barrier()  # nobody gathers before every rank has mapped what it needs
+    return peers
+
+
 def merge_batch_topn(shard_results, row_stride: int, how_many: int):
     """Merge of per-shard batched answers (the host half of a sharded oryx_topn_batch).
 
