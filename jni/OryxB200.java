@@ -73,5 +73,20 @@ public final class OryxB200 {
   public static native void exchangeDestroy(long exchange);
 
   /** {rowsX, rowsY, slotsX, slotsY, deviceBytes, queries, kernelLaunches}. */
+  /** One JVM per GPU: export this model's X and Y stores, map the other ranks' (oryx_peer_stores_*). */
+  public static native long peerStoresCreate(long model, int world, int rank);
+  /** ORYX_PEER_STORES_HANDLE_BYTES (512) bytes for the other processes. */
+  public static native byte[] peerStoresHandle(long peers);
+  /** world x 512 bytes in rank order. */
+  public static native void peerStoresConnect(long peers, byte[] handlesInRankOrder);
+  public static native void peerStoresDestroy(long peers);
+  /** computeUpdatedXu over rows that live in any rank's stores (global row ids); null rows = no result. */
+  public static native float[][] foldInRowsPeers(long solver, long peers, int features, long xuRowStride, long yiRowStride,
+                                                 boolean implicit, int xuWhich, long[] xuRows, long[] yiRows, double[] values);
+  /** ALSSpeedModelManager.buildUpdates aggregation (sort by timestamp, sum-with-NaN / last-wins per (user, item))
+   *  on the model's GPU; returns the number of groups written to the three output arrays. */
+  public static native long aggregateInteractions(long model, int[] userRows, int[] itemRows, double[] strengths,
+                                                  long[] timestamps, boolean implicit, int[] outUserRows, int[] outItemRows,
+                                                  double[] outStrengths);
   public static native long[] stats(long model);
 }

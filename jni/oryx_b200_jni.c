@@ -611,6 +611,106 @@ JNIEXPORT void JNICALL FN(exchangeDestroy)(JNIEnv* env, jclass cls, jlong exchan
   oryx_exchange_destroy((oryx_exchange*)(intptr_t)exchange);
 }
 
+/* ---- stores of other processes (one JVM per GPU): oryx_peer_stores_* + oryx_fold_in_rows_peers */
+
+JNIEXPORT jlong JNICALL FN(peerStoresCreate)(JNIEnv* env, jclass cls, jlong model, jint world, jint rank) {
+  (void)cls;
+  oryx_peer_stores* p = NULL;
+  int32_t st = oryx_peer_stores_create((oryx_model*)(intptr_t)model, world, rank, &p);
+  if (st != ORYX_OK) { throw_for_status(env, st); return 0; }
+  return (jlong)(intptr_t)p;
+}
+
+JNIEXPORT jbyteArray JNICALL FN(peerStoresHandle)(JNIEnv* env, jclass cls, jlong peers) {
+  (void)cls;
+  jbyte buf[ORYX_PEER_STORES_HANDLE_BYTES];
+  int32_t st = oryx_peer_stores_handle((oryx_peer_stores*)(intptr_t)peers, buf);
+  if (st != ORYX_OK) { throw_for_status(env, st); return NULL; }
+  jbyteArray out = (*env)->NewByteArray(env, ORYX_PEER_STORES_HANDLE_BYTES);
+  if (out) (*env)->SetByteArrayRegion(env, out, 0, ORYX_PEER_STORES_HANDLE_BYTES, buf);
+  return out;
+}
+
+JNIEXPORT void JNICALL FN(peerStoresConnect)(JNIEnv* env, jclass cls, jlong peers, jbyteArray handles_in_rank_order) {
+  (void)cls;
+  void* h = pin(env, handles_in_rank_order);
+  int32_t st = h ? oryx_peer_stores_connect((oryx_peer_stores*)(intptr_t)peers, h) : ORYX_E_INVALID;
+  unpin(env, handles_in_rank_order, h);
+  if (!h) throw_named(env, "java/lang/IllegalArgumentException", "null handle table");
+  else if (st != ORYX_OK) throw_for_status(env, st);
+}
+
+JNIEXPORT void JNICALL FN(peerStoresDestroy)(JNIEnv* env, jclass cls, jlong peers) {
+  (void)env; (void)cls;
+  oryx_peer_stores_destroy((oryx_peer_stores*)(intptr_t)peers);
+}
+
+JNIEXPORT jobjectArray JNICALL FN(foldInRowsPeers)(JNIEnv* env, jclass cls, jlong solver, jlong peers, jint features,
+                                                    jlong xu_row_stride, jlong yi_row_stride, jboolean implicit,
+                                                    jint xu_which, jlongArray xu_rows, jlongArray yi_rows,
+                                                    jdoubleArray values) {
+  (void)cls;
+  const jsize n = len(env, values);
+  if (len(env, xu_rows) != n || len(env, yi_rows) != n) {
+    throw_named(env, "java/lang/IllegalArgumentException", "row / value arrays differ in length");
+    return NULL;
+  }
+  float* res = (float*)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1) * (size_t)features);
+  uint8_t* valid = (uint8_t*)calloc((size_t)(n > 0 ? n : 1), 1);
+  jobjectArray out = NULL;
+  if (!res || !valid) {
+    throw_named(env, "java/lang/OutOfMemoryError", "foldInRowsPeers");
+  } else {
+    int64_t* xr = (int64_t*)pin(env, xu_rows);
+    int64_t* yr = (int64_t*)pin(env, yi_rows);
+    double* v = (double*)pin(env, values);
+    int32_t st = oryx_fold_in_rows_peers((oryx_solver*)(intptr_t)solver, (oryx_peer_stores*)(intptr_t)peers, xu_row_stride,
+                                         yi_row_stride, implicit ? 1 : 0, xu_which, xr, yr, v, n, res, valid);
+    unpin(env, values, v);
+    unpin(env, yi_rows, yr);
+    unpin(env, xu_rows, xr);
+    if (st != ORYX_OK) throw_for_status(env, st);
+    else out = unpack_rows(env, res, valid, n, features);
+  }
+  free(res); free(valid);
+  return out;
+}
+
+/* ---- ALSSpeedModelManager.buildUpdates aggregation (SMM:141-171) on the model's GPU.  Returns the number of
+ * surviving (user, item) groups; the three output arrays (length >= n) receive them ordered by (user, item). */
+JNIEXPORT jlong JNICALL FN(aggregateInteractions)(JNIEnv* env, jclass cls, jlong model, jintArray user_rows,
+                                                   jintArray item_rows, jdoubleArray strengths, jlongArray timestamps,
+                                                   jboolean implicit, jintArray out_user_rows, jintArray out_item_rows,
+                                                   jdoubleArray out_strengths) {
+  (void)cls;
+  const jsize n = len(env, strengths);
+  if (len(env, user_rows) != n || len(env, item_rows) != n || len(env, timestamps) != n || len(env, out_user_rows) < n ||
+      len(env, out_item_rows) < n || len(env, out_strengths) < n) {
+    throw_named(env, "java/lang/IllegalArgumentException", "input arrays differ in length or outputs are too short");
+    return 0;
+  }
+  int64_t out_n = 0;
+  int32_t* ur = (int32_t*)pin(env, user_rows);
+  int32_t* ir = (int32_t*)pin(env, item_rows);
+  double* sv = (double*)pin(env, strengths);
+  int64_t* ts = (int64_t*)pin(env, timestamps);
+  int32_t* our = (int32_t*)(*env)->GetPrimitiveArrayCritical(env, out_user_rows, NULL);
+  int32_t* oir = (int32_t*)(*env)->GetPrimitiveArrayCritical(env, out_item_rows, NULL);
+  double* osv = (double*)(*env)->GetPrimitiveArrayCritical(env, out_strengths, NULL);
+  int32_t st = ORYX_E_NOMEM;
+  if (our && oir && osv && (n == 0 || (ur && ir && sv && ts)))
+    st = oryx_aggregate_interactions((oryx_model*)(intptr_t)model, ur, ir, sv, ts, n, implicit ? 1 : 0, our, oir, osv, &out_n);
+  if (osv) (*env)->ReleasePrimitiveArrayCritical(env, out_strengths, osv, 0);  /* 0: copy back */
+  if (oir) (*env)->ReleasePrimitiveArrayCritical(env, out_item_rows, oir, 0);
+  if (our) (*env)->ReleasePrimitiveArrayCritical(env, out_user_rows, our, 0);
+  unpin(env, timestamps, ts);
+  unpin(env, strengths, sv);
+  unpin(env, item_rows, ir);
+  unpin(env, user_rows, ur);
+  if (st != ORYX_OK) { throw_for_status(env, st); return 0; }
+  return (jlong)out_n;
+}
+
 JNIEXPORT jlongArray JNICALL FN(stats)(JNIEnv* env, jclass cls, jlong model) {
   (void)cls;
   oryx_stats s;

@@ -29,6 +29,8 @@ struct JNINativeInterface_ {
   jsize (*GetArrayLength)(JNIEnv*, jarray);
   void* (*GetPrimitiveArrayCritical)(JNIEnv*, jarray, jboolean*);
   void (*ReleasePrimitiveArrayCritical)(JNIEnv*, jarray, void*, jint);
+  jbyteArray (*NewByteArray)(JNIEnv*, jsize);
+  void (*SetByteArrayRegion)(JNIEnv*, jbyteArray, jsize, jsize, const jbyte*);
   jintArray (*NewIntArray)(JNIEnv*, jsize);
   jlongArray (*NewLongArray)(JNIEnv*, jsize);
   jfloatArray (*NewFloatArray)(JNIEnv*, jsize);
