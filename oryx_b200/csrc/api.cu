@@ -949,20 +949,21 @@ int32_t oryx_merge_topn_packed(const void* d_records, int32_t n_lists, int32_t r
 // Development aid (not part of the public header): arm == 1 allocates/re-arms the timestamp buffer the
 // scan kernel fills; arm == 0 synchronises and copies out 8 globaltimer values (ns):
 // [0] earliest CTA start, [1]/[2] earliest/latest end of a CTA's scan, [3] merge start,
-// [4] selection done, [5] exact re-score done, [6] merge end.
+// [4] selection done, [5] exact re-score done, [6] merge end; [8]-[10] inside the small-k selection: list maxima
+// loaded, cut found, candidates gathered.  `out` holds 16 values.
 int32_t oryx_debug_scan_timestamps(oryx_model* mh, int32_t arm, unsigned long long* out) {
   Model* m = reinterpret_cast<Model*>(mh);
   ORYX_DEVICE(m);
   if (arm) {
-    if (!m->d_debug_ts) ORYX_CUDA(cudaMalloc(&m->d_debug_ts, 8 * sizeof(unsigned long long)));
-    unsigned long long init[8] = {~0ull, ~0ull, 0, 0, 0, 0, 0, 0};
+    if (!m->d_debug_ts) ORYX_CUDA(cudaMalloc(&m->d_debug_ts, 16 * sizeof(unsigned long long)));
+    unsigned long long init[16] = {~0ull, ~0ull, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     ORYX_CUDA(cudaDeviceSynchronize());
     ORYX_CUDA(cudaMemcpy(m->d_debug_ts, init, sizeof(init), cudaMemcpyHostToDevice));
     return ORYX_OK;
   }
   ORYX_ARG(out && m->d_debug_ts, "not armed");
   ORYX_CUDA(cudaDeviceSynchronize());
-  ORYX_CUDA(cudaMemcpy(out, m->d_debug_ts, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  ORYX_CUDA(cudaMemcpy(out, m->d_debug_ts, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return ORYX_OK;
 }
 

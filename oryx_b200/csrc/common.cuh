@@ -75,6 +75,74 @@ __device__ __forceinline__ float key_float(uint32_t k) {
 __device__ __forceinline__ double exact_step(double acc, float a, float b) {
   return __dadd_rn(acc, (double)__fmul_rn(a, b));
 }
+
+// The same value -- VectorMath.dot(a, b) over n terms, bit for bit -- computed by a whole warp WITHOUT walking
+// the chain, whenever the chain provably never rounds.  (A dependent binary64 add per term costs ~45 ns on this
+// part: 12 us per 256-feature row in the finishing kernel, most of its run time.)
+//   t_j = fl32(a_j b_j) = +-m_j 2^(e_j - 150), m_j < 2^24: lane l takes the contiguous terms [l c, (l+1) c),
+//   scales them to integers v_j = +-m_j 2^(e_j - e_min) (e_min: smallest exponent of a non-zero term) and the warp
+//   forms every prefix sum P_j = v_0 + ... + v_j in int64, exactly (refused when the exponents spread too far for
+//   that).  If every P_j fits a binary64 significand (bit length minus trailing zeros <= 53), then by induction
+//   the reference's running sum equals P_j 2^(e_min - 150) after every step -- no addition ever rounds -- and the
+//   result is (double)P_{n-1} scaled by a power of two.  For Gaussian data all but ~1 row in 10^4 qualify.
+// Returns false (all lanes) when it cannot tell: NaN / infinite terms, too wide a spread, a prefix that would
+// round.  The caller then walks the chain with exact_step.  `a`, `b`: any memory space; n <= 2048.
+__device__ __forceinline__ bool warp_exact_dot(const float* __restrict__ a, const float* __restrict__ b, int n, int lane,
+                                               double* out) {
+  const int c = (n + 31) >> 5;
+  const int j0 = lane * c, j1 = min(n, j0 + c);
+  // pass 1: exponent range of the non-zero terms
+  int emin = 1 << 20, emax = 0;
+  bool bad = n > 2048;
+  for (int j = j0; j < j1; j++) {
+    const uint32_t bits = __float_as_uint(__fmul_rn(a[j], b[j]));
+    const int ex = (int)((bits >> 23) & 255u);
+    if (ex == 255) bad = true;
+    if ((bits & 0x7fffffffu) != 0u) {
+      const int e = ex == 0 ? 1 : ex;
+      emin = min(emin, e);
+      emax = max(emax, e);
+    }
+  }
+  emin = __reduce_min_sync(0xffffffffu, emin);
+  emax = __reduce_max_sync(0xffffffffu, emax);
+  if (__any_sync(0xffffffffu, bad)) return false;
+  if (emax == 0) {  // every term is zero: 0.0 + (+-0.0) + ... = +0.0
+    *out = 0.0;
+    return true;
+  }
+  // int64 headroom: |v_j| < 2^(24 + spread), n of them
+  if (emax - emin > 62 - 24 - (32 - __clz(n))) return false;
+  auto term = [&](int jj) -> long long {
+    const uint32_t bits = __float_as_uint(__fmul_rn(a[jj], b[jj]));
+    if ((bits & 0x7fffffffu) == 0u) return 0;
+    const int ex = (int)((bits >> 23) & 255u);
+    const long long m = (long long)((bits & 0x7fffffu) | (ex == 0 ? 0u : 0x800000u));
+    const long long v = m << ((ex == 0 ? 1 : ex) - emin);
+    return (bits & 0x80000000u) ? -v : v;
+  };
+  // pass 2: lane totals and their warp scan; pass 3: every prefix must fit a binary64 significand
+  long long run = 0;
+  for (int j = j0; j < j1; j++) run += term(j);
+  long long incl = run;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const long long t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  long long p = incl - run;  // sum of the lanes in front
+  bool ok = true;
+  for (int j = j0; j < j1; j++) {
+    p += term(j);
+    const unsigned long long m = (unsigned long long)(p < 0 ? -p : p);
+    ok = ok && (p == 0 || (64 - __clzll((long long)m)) - (__ffsll((long long)m) - 1) <= 53);
+  }
+  if (!__all_sync(0xffffffffu, ok)) return false;
+  const long long total = __shfl_sync(0xffffffffu, incl, 31);
+  // 2^(emin - 150) >= 2^-149: a normal binary64; the product is exact
+  *out = (double)total * __longlong_as_double((long long)(1023 + emin - 150) << 52);
+  return true;
+}
 #endif
 
 // ---- the device-resident feature-vector store (one per X / Y).

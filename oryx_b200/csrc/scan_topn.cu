@@ -428,49 +428,86 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
 constexpr int kSmallKMax = 32;
 constexpr int kGatherCap = 1024;  // = kFinishThreads: one thread per gathered entry
 
-// k-th largest of n 32-bit keys in shared memory, by one warp (bisection, hardware warp reduce).
-// Returns the largest t with count(key >= t) >= k, or 1 if fewer than k keys are non-zero.
-__device__ __forceinline__ uint32_t warp_kth_largest_key(const uint32_t* keys, int n, int k, int lane) {
-  uint32_t lo = 1u, hi = 0xffffffffu;
-  while (hi - lo > 1u) {
-    const uint32_t mid = lo + ((hi - lo) >> 1);
-    int c = 0;
-    for (int i = lane; i < n; i += 32) c += keys[i] >= mid ? 1 : 0;
-    c = __reduce_add_sync(0xffffffffu, c);
-    if (c >= k) lo = mid; else hi = mid;
+// k-th largest of n 32-bit keys in shared memory, by the whole CTA: radix select, four passes of eight bits,
+// most significant first, a 256-bin histogram in shared memory per pass.  Returns (to every thread) the largest t
+// with count(key >= t) >= k, or 1 if fewer than k keys are non-zero.  (A 32-step bisection by one warp took
+// 9.7 us of the finishing kernel's 27: device timestamps, round 2.)
+__device__ __forceinline__ uint32_t cta_kth_largest_key(const uint32_t* keys, int n, int k, unsigned int* hist /*[256]*/) {
+  constexpr int T = kFinishThreads;
+  const int tid = threadIdx.x;
+  __shared__ unsigned int s_prefix, s_mask, s_remaining;
+  if (tid == 0) { s_prefix = 0u; s_mask = 0u; s_remaining = (unsigned)k; }
+  for (int pass = 0; pass < 4; pass++) {
+    const int shift = 24 - 8 * pass;
+    for (int b = tid; b < 256; b += T) hist[b] = 0u;
+    __syncthreads();
+    const unsigned prefix = s_prefix, mask = s_mask;
+    for (int i = tid; i < n; i += T) {
+      const unsigned key = keys[i];
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {
+      // lane l owns bins [255-8l-7, 255-8l]; walk from the top bin down
+      unsigned local[8];
+      unsigned sum = 0;
+#pragma unroll
+      for (int q = 0; q < 8; q++) { local[q] = hist[255 - 8 * tid - q]; sum += local[q]; }
+      unsigned incl = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (tid >= d) incl += t;
+      }
+      const unsigned excl_sum = incl - sum;
+      const unsigned remaining = s_remaining;
+      // exactly one lane owns the crossing: the keys matching the prefix number >= remaining >= 1 (n >= k)
+      if (excl_sum < remaining && incl >= remaining) {
+        unsigned cum = excl_sum;
+        int digit = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          if (cum + local[q] >= remaining) { digit = 255 - 8 * tid - q; break; }
+          cum += local[q];
+        }
+        s_prefix = prefix | ((unsigned)digit << shift);
+        s_mask = mask | (255u << shift);
+        s_remaining = remaining - cum;
+      }
+    }
+    __syncthreads();
   }
-  return lo;
+  return max(s_prefix, 1u);  // the k-th largest key itself; 0 = fewer than k non-zero keys
 }
 
 // Returns the number selected (written to out[0..) in descending order), or -1 if the gather buffer
 // overflowed (pathological ties) and the caller must use the general path.
 __device__ int select_small_k(const ScanParams& p, int n_lists, uint32_t* s_max /*[n_lists]*/,
-                              unsigned long long* s_ent /*[kGatherCap]*/, unsigned long long* out) {
+                              unsigned long long* s_ent /*[kGatherCap]*/, unsigned int* hist /*[256]*/,
+                              unsigned long long* out) {
   constexpr int T = kFinishThreads;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int k = p.k;
-  __shared__ uint32_t s_m;
   __shared__ unsigned int s_count;
   for (int i = tid; i < n_lists; i += T) s_max[i] = __ldcg(p.list_max + i);
   if (tid == 0) s_count = 0u;
   __syncthreads();
-  if (warp == 0) {
-    const uint32_t m = n_lists >= k ? warp_kth_largest_key(s_max, n_lists, k, lane) : 1u;
-    if (lane == 0) s_m = m;
-  }
-  __syncthreads();
-  const uint32_t m = s_m;
-  const int64_t total = (int64_t)n_lists * k;
-  for (int64_t i = tid; i < total; i += T) {
-    const int list = (int)(i / k);
-    if (s_max[list] < m) continue;  // nothing in this list can make the cut: never read it
-    const uint2 e = __ldcg(&p.cand[i]);
-    if (e.x != 0u && e.x >= m) {
-      const unsigned pos = atomicAdd(&s_count, 1u);
-      if (pos < (unsigned)kGatherCap) s_ent[pos] = ((unsigned long long)e.x << 32) | (unsigned long long)e.y;
+  if (p.debug_ts && tid == 0) p.debug_ts[8] = global_ns();
+  const uint32_t m = n_lists >= k ? cta_kth_largest_key(s_max, n_lists, k, hist) : 1u;
+  if (p.debug_ts && tid == 0) p.debug_ts[9] = global_ns();
+  // one warp per list (k <= 32: a lane per entry); a list whose maximum misses the cut is never read
+  for (int list = warp; list < n_lists; list += T / 32) {
+    if (s_max[list] < m) continue;
+    if (lane < k) {
+      const uint2 e = __ldcg(&p.cand[(int64_t)list * k + lane]);
+      if (e.x != 0u && e.x >= m) {
+        const unsigned pos = atomicAdd(&s_count, 1u);
+        if (pos < (unsigned)kGatherCap) s_ent[pos] = ((unsigned long long)e.x << 32) | (unsigned long long)e.y;
+      }
     }
   }
   __syncthreads();
+  if (p.debug_ts && tid == 0) p.debug_ts[10] = global_ns();
   const int n = (int)s_count;
   if (n > kGatherCap) return -1;
   // rank-sort: words are unique, rank = number of larger words
@@ -613,7 +650,7 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
   if (p.debug_ts && tid == 0) p.debug_ts[3] = global_ns();
 
   int nsel = -1;
-  if (k <= kSmallKMax) nsel = select_small_k(p, n_lists, s_max, s_ent, sel);
+  if (k <= kSmallKMax) nsel = select_small_k(p, n_lists, s_max, s_ent, hist, sel);
   if (nsel < 0) {
     __syncthreads();
     nsel = select_radix(total, k, hist, sel,
@@ -626,8 +663,7 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
   if (p.debug_ts && tid == 0) p.debug_ts[4] = global_ns();
 
   // Exact re-score: VectorMath.dot / CosineAverageFunction.applyAsDouble arithmetic.  One warp per
-  // selected row: the lanes stage the row in shared memory with coalesced loads (one round trip),
-  // lane 0 then walks it in index order.
+  // selected row: the lanes stage the row in shared memory with coalesced loads (one round trip).
   if (warp < rescore_warps) {
     for (int i = warp; i < nsel; i += rescore_warps) {
       const int32_t slot = (int32_t)(uint32_t)sel[i];
@@ -635,15 +671,22 @@ topn_finish_kernel(const __grid_constant__ ScanParams p, int n_lists, int kind, 
       float4* rb4 = reinterpret_cast<float4*>(rowbuf + (size_t)warp * fpad);
       for (int j = lane; j < p.f4; j += 32) rb4[j] = y4[j];
       __syncwarp();
+      const int32_t row_id = lane == 0 ? __ldg(p.slot_row + slot) : 0;  // issued before the sums, used after them
+      const float* y = rowbuf + (size_t)warp * fpad;
+      // the whole warp computes the chain's value when the chain provably never rounds (common.cuh) ...
+      double dot = 0.0, tot = 0.0;
+      bool fast = warp_exact_dot(s_q, y, p.features, lane, &dot);
+      if (kind == ORYX_COSINE) fast = warp_exact_dot(y, y, p.features, lane, &tot) && fast;
       if (lane == 0) {
-        const int32_t row_id = __ldg(p.slot_row + slot);  // issued before the chain, used after it
-        const float* y = rowbuf + (size_t)warp * fpad;
-        double dot = 0.0, tot = 0.0;
+        if (!fast) {  // ... otherwise lane 0 walks it
+          dot = 0.0;
+          tot = 0.0;
 #pragma unroll 8
-        for (int j = 0; j < p.features; j++) {
-          const float yv = y[j];
-          dot = exact_step(dot, s_q[j], yv);
-          if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+          for (int j = 0; j < p.features; j++) {
+            const float yv = y[j];
+            dot = exact_step(dot, s_q[j], yv);
+            if (kind == ORYX_COSINE) tot = exact_step(tot, yv, yv);
+          }
         }
         sel_exact[i] = (kind == ORYX_COSINE) ? __ddiv_rn(dot, __dsqrt_rn(tot)) : dot;
         sel_row[i] = row_id;

@@ -213,6 +213,37 @@ def test_nan_and_ties():
         assert list(scores) == [1.0, 1.0, 1.0, -1.0] and sorted(rows[:3]) == [0, 1, 3] and rows[3] == 5
 
 
+@pytest.mark.parametrize("f", [7, 64, 250, 256])
+def test_exact_rescore_over_wide_dynamic_ranges(f):
+    """The finishing kernel computes VectorMath.dot's value with the whole warp when the binary64 chain provably
+    never rounds, and walks the chain otherwise (common.cuh warp_exact_dot).  Rows whose terms span 2^-70 .. 2^70
+    (chains that DO round, int64 headroom exceeded), subnormal products, exact cancellations, zero rows and signed
+    zeros must all come back with the oracle's bits."""
+    rng = np.random.default_rng(0xB2000900 + f)
+    n = 4000
+    y = rng.standard_normal((n, f)).astype(np.float32)
+    scale = np.exp2(rng.integers(-35, 36, (n, f))).astype(np.float32)
+    y[:1500] *= scale[:1500]                                  # wide spread: most of these chains round
+    y[1500:1600] *= np.float32(2.0 ** -80)                    # products deep in the subnormal range
+    y[1600:1700, : f // 2] = -y[1600:1700, f - f // 2:][:, ::-1] if f % 2 == 0 else y[1600:1700, : f // 2]
+    y[1700:1710] = 0.0
+    y[1710:1720] = -0.0
+    y[1720:1800] = np.round(y[1720:1800] * 8) / 8              # short significands: nothing ever rounds
+    qs = [rng.standard_normal(f).astype(np.float32),
+          (rng.standard_normal(f) * np.exp2(rng.integers(-35, 36, f))).astype(np.float32),
+          np.full(f, 2.0 ** -70, np.float32),
+          np.where(np.arange(f) % 2 == 0, 1.0, -1.0).astype(np.float32)]
+    with ob.Model(f) as m:
+        m.upsert(ob.Y, np.arange(n, dtype=np.int32), y)
+        for q in qs:
+            for kind in (ob.DOT, ob.COSINE):
+                for hm in (10, 200):
+                    with np.errstate(all="ignore"):
+                        exp = oracle.topn(kind, q, y, hm)
+                        allsc = oracle.scores_all(kind, q, y) if hasattr(oracle, "scores_all") else None
+                    _assert_same_topn(m.topn(kind, q, hm), exp, allsc)
+
+
 @pytest.mark.parametrize("rate,cores,f", [(0.5, 32, 20), (0.3, 32, 50), (0.1, 8, 128), (1.0, 8, 10), (0.5, 1, 16)])
 def test_lsh_bit_exact_and_filtered_topn(rate, cores, f):
     h, bits = ob.lsh_plan(rate, cores)

@@ -84,11 +84,12 @@ stamps = []
 for i in range(5):
     L.oryx_debug_scan_timestamps(m._h, 1, None)
     m.topn_device(ob.DOT, d_q[i].data_ptr(), HM, d_rows.data_ptr(), d_sc.data_ptr(), d_n.data_ptr(), stream.cuda_stream)
-    ts = (C.c_ulonglong * 8)()
+    ts = (C.c_ulonglong * 16)()
     L.oryx_debug_scan_timestamps(m._h, 0, ts)
     t = [int(x) for x in ts]
     stamps.append({"scan_first_end_us": (t[1] - t[0]) / 1e3, "scan_last_end_us": (t[2] - t[0]) / 1e3,
                    "finish_start_us": (t[3] - t[0]) / 1e3, "select_done_us": (t[4] - t[0]) / 1e3,
-                   "rescore_done_us": (t[5] - t[0]) / 1e3, "finish_end_us": (t[6] - t[0]) / 1e3})
+                   "rescore_done_us": (t[5] - t[0]) / 1e3, "finish_end_us": (t[6] - t[0]) / 1e3,
+                   "select_phases_us_after_finish_start": [(t[i] - t[3]) / 1e3 for i in (8, 9, 10, 4)]})
 print(json.dumps(stamps, indent=1))
 m.close()
