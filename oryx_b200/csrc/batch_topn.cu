@@ -9,10 +9,11 @@
 // Y is read once per batch instead of once per query, so the work is a dense contraction S = Q Y^T
 // (2*nq*N*F flops) and belongs on tcgen05.  The 4096 x 10M score matrix is never materialised:
 //
-//   1. convert   Y (fp32 store) and Q -> bf16 scratch, K padded to 64; per-row norms give a rigorous
-//                bound on what bf16 rounding can do to a score:
-//                |s_bf16 - s| <= delta_q = 2^-7 (1 + 2^-9) ||q|| max_j ||y_j||  (unit roundoff of bf16 is
-//                2^-8 per operand; Cauchy-Schwarz over the products; fp32 accumulation adds < 1 %).
+//   1. convert   Y (fp32 store) and Q -> bf16 scratch, K padded to 64; the conversions also MEASURE what the
+//                rounding took away, which gives a rigorous bound on what it can do to a score:
+//                s_bf16 - s = bf(q).(bf(y) - y) + (bf(q) - q).y, hence
+//                |s_bf16 - s| <= delta_q = ||bf(q)|| max_j ||y_j - bf(y_j)|| + ||q - bf(q)|| max_j ||y_j||
+//                (+ fp32 accumulation), about 2.5 x below the worst case 2^-7 ||q|| max ||y|| of round 1.
 //   2. score     batch_score_kernel: persistent, warp-specialised.  One warp drives TMA
 //                (cp.async.bulk.tensor, 128-byte swizzle), one thread issues tcgen05.mma
 //                (cta_group::1, kind::f16, M=128 queries x N=256 items x K=16, accumulators in TMEM,
@@ -137,7 +138,7 @@ __global__ void convert_y_kernel(const float* __restrict__ y, int64_t n, int fpa
   const int lane = threadIdx.x & 31;
   const int64_t w0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
-  float local_max = 0.f;
+  float local_max = 0.f, local_res = 0.f;
   for (int64_t row = w0; row < n; row += stride) {
     const float* src = y + row * fpad;
     __nv_bfloat16* dst = out + row * kpad;
@@ -146,15 +147,27 @@ __global__ void convert_y_kernel(const float* __restrict__ y, int64_t n, int fpa
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     const float scale = normalize ? rsqrtf(ss) : 1.0f;  // zero row: inf -> NaN entries, never selected
+    float rs = 0.f;  // squared norm of what the rounding to bf16 took away from this row
     for (int j = lane; j < kpad; j += 32) {
       float v = j < features ? src[j] * scale : 0.f;
       if (normalize && j >= features) v = 0.f;
-      dst[j] = __float2bfloat16_rn(v);
+      const __nv_bfloat16 b = __float2bfloat16_rn(v);
+      dst[j] = b;
+      const float d = v - __bfloat162float(b);  // exact in binary32
+      rs = fmaf(d, d, rs);
     }
-    if (ss == ss) local_max = fmaxf(local_max, normalize ? 1.0002f : ss);  // tombstones are NaN rows: ignore
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+    if (ss == ss) {  // tombstones are NaN rows: ignore
+      local_max = fmaxf(local_max, normalize ? 1.0002f : ss);
+      local_res = fmaxf(local_res, rs);
+    }
   }
   // sqrt is monotone: keep the max of squared norms (non-negative floats order like their bit patterns)
-  if (lane == 0) atomicMax(max_norm_bits, __float_as_uint(local_max));
+  if (lane == 0) {
+    atomicMax(max_norm_bits, __float_as_uint(local_max));
+    atomicMax(max_norm_bits + 1, __float_as_uint(local_res));
+  }
 }
 
 // The same conversion for a list of slots that just changed (upsert / remove): keeps the shadow current
@@ -175,8 +188,20 @@ __global__ void convert_rows_kernel(const float* __restrict__ y, const int32_t* 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
   const float scale = normalize ? rsqrtf(ss) : 1.0f;
-  for (int j = lane; j < kpad; j += 32) dst[j] = __float2bfloat16_rn(j < features ? src[j] * scale : 0.f);
-  if (lane == 0 && ss == ss) atomicMax(max_norm_bits, __float_as_uint(normalize ? 1.0002f : ss));
+  float rs = 0.f;
+  for (int j = lane; j < kpad; j += 32) {
+    const float v = j < features ? src[j] * scale : 0.f;
+    const __nv_bfloat16 b = __float2bfloat16_rn(v);
+    dst[j] = b;
+    const float d = v - __bfloat162float(b);
+    rs = fmaf(d, d, rs);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+  if (lane == 0 && ss == ss) {
+    atomicMax(max_norm_bits, __float_as_uint(normalize ? 1.0002f : ss));
+    atomicMax(max_norm_bits + 1, __float_as_uint(rs));
+  }
 }
 
 // One warp per query: the row in slots[i] of a store (zeros for a negative slot) -> packed [nq x f].
@@ -189,21 +214,34 @@ __global__ void gather_queries_kernel(const float* __restrict__ vec, int fpad, i
   for (int j = lane; j < f; j += 32) out[(size_t)w * f + j] = slot >= 0 ? vec[(int64_t)slot * fpad + j] : 0.f;
 }
 
-// Q fp32 [nq x features] -> bf16 [nq_pad x kpad] (zero padded rows and columns), and ||q|| per row.
+// Q fp32 [nq x features] -> bf16 [nq_pad x kpad] (zero padded rows and columns), and per row the three norms
+// the error bound needs: qnorm[row] = ||q||, qnorm[nq_pad + row] = ||q - bf16(q)||, qnorm[2 nq_pad + row] = ||bf16(q)||.
 __global__ void convert_q_kernel(const float* __restrict__ q, int nq, int nq_pad, int features, int kpad,
                                  __nv_bfloat16* __restrict__ out, float* __restrict__ qnorm) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= nq_pad) return;
-  float ss = 0.f;
+  float ss = 0.f, rs = 0.f, bs = 0.f;
   for (int j = lane; j < kpad; j += 32) {
     float v = (row < nq && j < features) ? q[(size_t)row * features + j] : 0.f;
     ss = fmaf(v, v, ss);
-    out[(size_t)row * kpad + j] = __float2bfloat16_rn(v);
+    const __nv_bfloat16 b = __float2bfloat16_rn(v);
+    out[(size_t)row * kpad + j] = b;
+    const float bf = __bfloat162float(b), d = v - bf;  // d: exact in binary32
+    rs = fmaf(d, d, rs);
+    bs = fmaf(bf, bf, bs);
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-  if (lane == 0) qnorm[row] = sqrtf(ss);
+  for (int o = 16; o > 0; o >>= 1) {
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    rs += __shfl_xor_sync(0xffffffffu, rs, o);
+    bs += __shfl_xor_sync(0xffffffffu, bs, o);
+  }
+  if (lane == 0) {
+    qnorm[row] = sqrtf(ss);
+    qnorm[nq_pad + row] = sqrtf(rs);
+    qnorm[2 * nq_pad + row] = sqrtf(bs);
+  }
 }
 
 // ---------------------------------------------------------------- step 2: tensor-core scoring
@@ -432,7 +470,7 @@ constexpr int kTileCap = 2048;       // tiles above the first cut
 __global__ void __launch_bounds__(kThrThreads)
 batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, const float* __restrict__ tmax,
                        int64_t tmax_stride, int n_tiles, int k_base, const int32_t* __restrict__ excl_offsets,
-                       const float* __restrict__ qnorm,
+                       const float* __restrict__ qnorm, int nq_pad,
                        const unsigned int* __restrict__ max_norm_sq_bits, int32_t* __restrict__ cand, int cand_cap,
                        int32_t* __restrict__ cand_n, float* __restrict__ cut_out) {
   __shared__ float s_top[kThrThreads * kTopPerThread];
@@ -451,7 +489,15 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, cons
     return;
   }
   // rigorous bound on |bf16 score - exact score| for this query (see file header)
-  const float delta = 0.0078125f * 1.01f * qnorm[q] * sqrtf(__uint_as_float(*max_norm_sq_bits));
+  // s_bf - s = bf(q) . (bf(y) - y) + (bf(q) - q) . y, so |s_bf - s| <= ||bf(q)|| R + ||q - bf(q)|| Ymax with
+  // R = the largest ||y - bf(y)|| and Ymax the largest ||y|| over the shadow's rows (both measured when the
+  // shadow was built) -- about 2.5 x tighter than the worst case 2^-7 ||q|| Ymax; plus 2^-13 ||q|| Ymax for the
+  // fp32 accumulation of up to 256 terms (4 x the 2^-23-per-add figure, truncating adds included) and 0.2 % for
+  // the fp32 norms themselves.  The refine step's bf16 pre-filter needs ||q|| R + its own fp32 accumulation
+  // <= delta, which holds because ||q|| <= ||bf(q)|| + ||q - bf(q)|| and R <= Ymax.
+  const float ymax = sqrtf(__uint_as_float(max_norm_sq_bits[0])), rmax = sqrtf(__uint_as_float(max_norm_sq_bits[1]));
+  const float delta = 1.002f * (qnorm[nq_pad + q] * ymax + qnorm[2 * nq_pad + q] * (rmax + 1e-6f * ymax)) +
+                      1.2207e-4f * qnorm[q] * ymax;
 
   // pass A (tiles): every thread keeps the 4 largest values of its strided share
   float top[kTopPerThread];
@@ -606,8 +652,8 @@ __device__ __forceinline__ bool excluded_slot(const int32_t* excl, int n, int32_
 // One CTA per query, one warp per candidate sub-block, two stages:
 //   A. score the sub-block's 32 rows against the bf16 shadow of Y (the very rows the tensor cores saw,
 //      256 bytes each at 128 features; fp32 query, fp32 accumulate) and keep the rows whose score
-//      reaches the query's cut T' - 2 delta.  |q . bf16(y) - q . y| <= delta / 2, so every row with an
-//      exact score >= T' - delta -- every possible top-k member -- passes;
+//      reaches the query's cut T' - 2 delta.  |q . bf16(y) - q . y| <= ||q|| max ||y - bf(y)|| <= delta, so every
+//      row with an exact score >= T' - delta -- every possible top-k member -- passes;
 //   B. the survivors (one or two per sub-block) are scored from the fp32 rows, the whole warp on one
 //      row, and offered to the shared top-k array.
 // Then the exact finishing pass: same selection rule and the same exact arithmetic as scan_topn.cu,
@@ -984,8 +1030,8 @@ static int32_t batch_topn_run_pass(Model* m, int kind, const float* queries, int
   bs.y_cap_rows = (int64_t)(bs.bytes[0] / ((size_t)kpad * 2));
   ORYX_TRY(scratch(bs, 1, (size_t)nq_pad * kpad * 2, &d_qbf.p));
   ORYX_TRY(scratch(bs, 2, (size_t)nq * F * 4, &d_q.p));
-  ORYX_TRY(scratch(bs, 3, (size_t)nq_pad * 4, &d_qnorm.p));
-  ORYX_TRY(scratch(bs, 4, 4, &d_maxn.p));
+  ORYX_TRY(scratch(bs, 3, (size_t)nq_pad * 12, &d_qnorm.p));
+  ORYX_TRY(scratch(bs, 4, 8, &d_maxn.p));
   ORYX_TRY(scratch(bs, 5, ((size_t)nq_pad * n_sub + (size_t)tmax_floats) * 4, &d_bmax.p));
   d_tmax.p = reinterpret_cast<float*>(d_bmax.p) + (size_t)nq_pad * n_sub;
   ORYX_TRY(scratch(bs, 6, (size_t)nq * cand_cap * 4, &d_cand.p));
@@ -1023,7 +1069,7 @@ static int32_t batch_topn_run_pass(Model* m, int kind, const float* queries, int
   }
   ORYX_CUDA(cudaEventRecord(ev[0], st));
   if (!y_fresh) {
-    ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 4, st));
+    ORYX_CUDA(cudaMemsetAsync(d_maxn.p, 0, 8, st));
     convert_y_kernel<<<m->num_sms * 8, 256, 0, st>>>(s->d_vec, n, fpad, F, kpad, normalized,
                                                     (__nv_bfloat16*)d_ybf.p, (unsigned int*)d_maxn.p);
     bs.y_version = s->version;
@@ -1070,7 +1116,7 @@ static int32_t batch_topn_run_pass(Model* m, int kind, const float* queries, int
 
   batch_threshold_kernel<<<nq, kThrThreads, 0, st>>>((const float*)d_bmax.p, bmax_stride, (const float*)d_tmax.p,
                                                     tmax_stride, n_ytiles, k, excl_offsets ? (const int32_t*)d_eo.p : nullptr,
-                                                    (const float*)d_qnorm.p,
+                                                    (const float*)d_qnorm.p, nq_pad,
                                                     (const unsigned int*)d_maxn.p, (int32_t*)d_cand.p, cand_cap,
                                                     (int32_t*)d_candn.p, (float*)d_cut.p);
   ORYX_CUDA(cudaGetLastError());
