@@ -260,6 +260,33 @@ def sharded_parity_and_gram(ob, torch, dist, dev, rank: int, world: int, threads
     torch.cuda.synchronize()
     allreduce_ms = e0.elapsed_time(e1)
     gram_ms = model.debug_gram_ms()
+    # the same sum as ONE kernel over peer memory (oryx_gram_allreduce_device): no NCCL call; bits equal on every rank
+    peer = None
+    if hasattr(pipe, "x"):
+        try:
+            d_p = torch.from_numpy(g_local).to(dev)
+            d_st = torch.zeros(1, dtype=torch.int32, device=dev)
+            st_ptr = torch.cuda.current_stream(dev).cuda_stream
+            pipe.x.gram_allreduce_device(d_p.clone().data_ptr(), f, d_st.data_ptr(), st_ptr)   # warm-up
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0.record()
+            pipe.x.gram_allreduce_device(d_p.data_ptr(), f, d_st.data_ptr(), st_ptr)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            same = torch.tensor([d_p.cpu().numpy().tobytes() == d_g.cpu().numpy().tobytes()], dtype=torch.int32, device=dev)
+            ref = d_p.clone()
+            dist.broadcast(ref, 0)
+            same_everywhere = torch.tensor([int(torch.equal(ref, d_p))], dtype=torch.int32, device=dev)
+            dist.all_reduce(same_everywhere, op=dist.ReduceOp.MIN)
+            peer = {"peer_memory_kernel_ms_max_over_ranks": float(t.item()), "status": int(d_st.item()),
+                    "max_rel_diff_vs_nccl_sum": float((d_p - d_g).abs().max().item() / d_g.abs().max().item()),
+                    "bits_equal_to_nccl_sum_on_rank0": bool(same.item()),
+                    "bits_equal_on_every_rank": bool(same_everywhere.item())}
+        except Exception as e:  # noqa: BLE001
+            peer = {"error": repr(e)}
     gram_rel = gram_oracle_rel = None
     if rank == 0:
         with ob.Model(f, device=dev.index, capacity_hint=len(y_all)) as whole:
@@ -322,7 +349,7 @@ def sharded_parity_and_gram(ob, torch, dist, dev, rank: int, world: int, threads
             "parity_note": f"{rows_per_rank} rows x {f} f per rank, LSH sample-rate 0.3/32 cores ({H} hashes, {bits} bits), {nq} queries "
                            f"(dot and cosine), before and after oryx_items_compact, merged global rows and binary64 scores "
                            f"bit-equal to oracle.topn over the concatenation; exchange: {exchange}",
-            "gram_allreduce": {"per_shard_gram_ms": gram_ms, "nccl_allreduce_ms": allreduce_ms, "bytes": f * f * 8,
+            "gram_allreduce": {"per_shard_gram_ms": gram_ms, "nccl_allreduce_ms": allreduce_ms, "peer_memory": peer, "bytes": f * f * 8,
                                "max_rel_diff_vs_single_model_gram": gram_rel, "max_rel_err_vs_oracle": gram_oracle_rel,
                                "rows_total": rows_per_rank * world}}
 

@@ -58,6 +58,9 @@ public final class OryxB200 {
 
   /** VectorMath.transposeTimesSelf summed over the store (getYTYSolver / getXTXSolver); null if empty. */
   public static native double[] gram(long model, int which, int features);
+  /** Gram of a store sharded over the box's GPUs: this shard's Gram summed with the other ranks' by one kernel over
+   *  peer memory; every rank calls it (from its own thread) and receives the same matrix. */
+  public static native double[] gramSharded(long model, long exchange, int which, int features);
   /** LinearSystemSolver.getSolver; throws SingularMatrixSolverException(apparentRank, message). */
   public static native long solverCreate(double[] gramRowMajor, int features, int device);
   public static native void solverDestroy(long solver);

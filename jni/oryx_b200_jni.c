@@ -452,6 +452,21 @@ JNIEXPORT jdoubleArray JNICALL FN(gram)(JNIEnv* env, jclass cls, jlong model, ji
   return used > 0 ? out : NULL;   /* FeatureVectors.getVTV returns null for an empty store */
 }
 
+/* The global Gram of a store sharded over the GPUs of this box: the shard's Gram, then ONE kernel over peer memory
+ * that adds every rank's matrix (ALSServingModel.java:362-368 across GPUs).  Every rank calls it; never null. */
+JNIEXPORT jdoubleArray JNICALL FN(gramSharded)(JNIEnv* env, jclass cls, jlong model, jlong exchange, jint which, jint features) {
+  (void)cls;
+  if (features < 1) { throw_named(env, "java/lang/IllegalArgumentException", "features must be >= 1"); return NULL; }
+  jdoubleArray out = (*env)->NewDoubleArray(env, features * features);
+  if (!out) return NULL;
+  int64_t used = 0;
+  double* o = (double*)pin(env, out);
+  int32_t st = oryx_gram_sharded((oryx_model*)(intptr_t)model, (oryx_exchange*)(intptr_t)exchange, which, o, &used);
+  if (o) (*env)->ReleasePrimitiveArrayCritical(env, out, o, 0);
+  if (st != ORYX_OK) { throw_for_status(env, st); return NULL; }
+  return out;
+}
+
 JNIEXPORT jlong JNICALL FN(solverCreate)(JNIEnv* env, jclass cls, jdoubleArray gram, jint features, jint device) {
   (void)cls;
   oryx_solver* s = NULL;

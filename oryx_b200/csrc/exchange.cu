@@ -16,6 +16,7 @@
 // in order, which keeps a fast rank from overwriting a record a slow rank has not merged yet.
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -29,6 +30,12 @@ struct oryx_exchange {
   unsigned long long* d_done = nullptr;       // [0] last sequence this rank finished merging, [1] last local record copied out
   unsigned long long seq = 0;
   bool connected = false;
+  // Gram all-reduce (oryx_gram_allreduce_device): a second region of the same inbox allocation, so the one
+  // handle the ranks exchange covers it too.  [2 parities][world][kGramSlotBytes]
+  size_t gram_off = 0;
+  unsigned long long gram_seq = 0;
+  int32_t* d_gram_status = nullptr;
+  std::mutex gram_mu;
 };
 
 namespace oryx {
@@ -201,6 +208,66 @@ __global__ void __launch_bounds__(kExchangeThreads, 1) exchange_merge_kernel(con
   }
 }
 
+// ---- YtY = sum of the shards' Grams (ALSServingModel.java:362-368) as ONE kernel over peer memory.
+// Every rank's F x F binary64 partial is cut into slices; CTA c stores slice c of the local matrix into every
+// rank's inbox (plain stores over NVLink), fences, raises flag (parity, rank, c) there, waits for the world's flags
+// of slice c in its OWN inbox and adds the slices in rank order -- so every rank ends up with the same bits.
+// No NCCL call and no host round trip; CTAs depend on nothing but their own slice.  A rank's all-reduce kernels run
+// in stream order and never release dependents early, so when a rank has seen every peer's flags of sequence s,
+// every peer has finished reading sequence s-1: two parities suffice.
+constexpr int kGramMaxFeatures = 256;
+constexpr int kGramMaxSlices = 64;
+constexpr size_t kGramPayloadBytes = (size_t)kGramMaxFeatures * kGramMaxFeatures * sizeof(double);
+constexpr size_t kGramSlotBytes = kGramPayloadBytes + 1024;  // payload | [kGramMaxSlices] u64 flags | pad
+constexpr int kGramThreads = 256;
+
+struct GParams {
+  double* local;                        // in: this rank's partial; out: the sum
+  unsigned char* peers[ORYX_MAX_WORLD];  // base of each rank's Gram region
+  unsigned long long seq, timeout_ns;
+  int world, rank, parity, n_elems, per_slice;
+  int32_t* status;                      // 0 ok, -2 a peer never arrived
+};
+
+__global__ void __launch_bounds__(kGramThreads) gram_allreduce_kernel(const __grid_constant__ GParams p) {
+  __shared__ int s_timeout;
+  const int tid = threadIdx.x, c = blockIdx.x;
+  const int e0 = c * p.per_slice, e1 = min(p.n_elems, e0 + p.per_slice);
+  const size_t slot = ((size_t)p.parity * p.world + p.rank) * kGramSlotBytes;
+  if (tid == 0) s_timeout = 0;
+  // 1. publish slice c to every rank (the own inbox included: the reduction reads all slots alike)
+  for (int r = 0; r < p.world; r++) {
+    double* dst = reinterpret_cast<double*>(p.peers[r] + slot);
+    for (int e = e0 + tid; e < e1; e += kGramThreads) dst[e] = p.local[e];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < p.world) {
+    unsigned long long* flag = reinterpret_cast<unsigned long long*>(p.peers[tid] + slot + kGramPayloadBytes) + c;
+    st_release_sys(flag, p.seq);
+  }
+  // 2. wait for slice c of every rank in the own inbox
+  const unsigned char* in = p.peers[p.rank] + (size_t)p.parity * p.world * kGramSlotBytes;
+  if (tid < p.world) {
+    const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(in + (size_t)tid * kGramSlotBytes + kGramPayloadBytes) + c;
+    const unsigned long long t0 = global_ns_x();
+    while (ld_acquire_sys(flag) != p.seq) {
+      if (global_ns_x() - t0 > p.timeout_ns) { atomicExch(&s_timeout, 1); break; }
+    }
+  }
+  __syncthreads();
+  if (s_timeout) {
+    if (tid == 0) *p.status = -2;
+    return;
+  }
+  // 3. add the slices in rank order
+  for (int e = e0 + tid; e < e1; e += kGramThreads) {
+    double acc = 0.0;
+    for (int r = 0; r < p.world; r++) acc += __ldcg(reinterpret_cast<const double*>(in + (size_t)r * kGramSlotBytes) + e);
+    p.local[e] = acc;
+  }
+}
+
 // Selects a device for the duration of a call and puts the caller's device back afterwards.
 struct ScopedDevice {
   int prev = -1;
@@ -239,9 +306,12 @@ int32_t oryx_exchange_create(int32_t device, int32_t world, int32_t rank, int32_
   x->rank = rank;
   x->max_how_many = max_how_many;
   x->rec_bytes = record_slot_bytes(max_how_many);
-  const size_t inbox_bytes = 2 * (size_t)world * x->rec_bytes;
+  x->gram_off = (2 * (size_t)world * x->rec_bytes + 255) & ~(size_t)255;
+  const size_t inbox_bytes = x->gram_off + 2 * (size_t)world * kGramSlotBytes;
   ORYX_CUDA(cudaMalloc(&x->inbox, inbox_bytes));
   ORYX_CUDA(cudaMemset(x->inbox, 0, inbox_bytes));
+  ORYX_CUDA(cudaMalloc(&x->d_gram_status, sizeof(int32_t)));
+  ORYX_CUDA(cudaMemset(x->d_gram_status, 0, sizeof(int32_t)));
   ORYX_CUDA(cudaMalloc(&x->d_local, 2 * x->rec_bytes));
   ORYX_CUDA(cudaMemset(x->d_local, 0, 2 * x->rec_bytes));
   ORYX_CUDA(cudaMalloc(&x->d_done, 2 * sizeof(unsigned long long)));
@@ -325,6 +395,7 @@ int32_t oryx_exchange_destroy(oryx_exchange* x) {
   cudaFree(x->inbox);
   cudaFree(x->d_local);
   cudaFree(x->d_done);
+  cudaFree(x->d_gram_status);
   cudaGetLastError();
   delete x;
   return ORYX_OK;
@@ -385,6 +456,71 @@ int32_t oryx_topn_sharded_device(oryx_model* mh, oryx_exchange* x, int32_t kind,
   ORYX_CUDA(cudaLaunchKernelEx(&cfg, exchange_merge_kernel, p));
   reinterpret_cast<Model*>(mh)->launches++;
   return ORYX_OK;
+}
+
+int32_t oryx_gram_allreduce_device(oryx_exchange* x, double* d_gram, int32_t features, int32_t* d_status, void* stream) {
+  ORYX_ARG(x && d_gram && d_status, "null argument");
+  ORYX_ARG(x->connected, "exchange is not connected to its peers yet");
+  ORYX_ARG(features >= 1 && features <= kGramMaxFeatures, "features beyond the peer-memory Gram all-reduce (256): use NCCL");
+  ORYX_SCOPED_DEVICE(x->device);
+  static const unsigned long long timeout_ns = [] {
+    const char* e = std::getenv("ORYX_EXCHANGE_TIMEOUT_MS");
+    long long ms = e ? std::atoll(e) : 20000;
+    if (ms < 1) ms = 1;
+    return (unsigned long long)ms * 1000000ull;
+  }();
+  std::lock_guard<std::mutex> lk(x->gram_mu);
+  GParams p{};
+  p.local = d_gram;
+  for (int r = 0; r < x->world; r++) p.peers[r] = x->peer_inbox[r] + x->gram_off;
+  p.seq = ++x->gram_seq;
+  p.timeout_ns = timeout_ns;
+  p.world = x->world;
+  p.rank = x->rank;
+  p.parity = (int)(p.seq & 1);
+  p.n_elems = features * features;
+  const int n_slices = std::max(1, std::min(kGramMaxSlices, (p.n_elems + 255) / 256));
+  p.per_slice = (p.n_elems + n_slices - 1) / n_slices;
+  p.status = d_status;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  ORYX_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+  gram_allreduce_kernel<<<n_slices, kGramThreads, 0, st>>>(p);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
+int32_t oryx_gram_sharded(oryx_model* mh, oryx_exchange* x, int32_t which, double* out, int64_t* out_rows_used) {
+  ORYX_ARG(mh && x && out, "null argument");
+  Model* m = reinterpret_cast<Model*>(mh);
+  ORYX_ARG(m->device == x->device, "model and exchange live on different devices");
+  const int F = m->cfg.features;
+  // this rank's partial (tensor-core kernel and its error check included); a copy stays in m->d_gram
+  ORYX_TRY(oryx_gram(mh, which, out, out_rows_used));
+  ORYX_SCOPED_DEVICE(x->device);
+  QueryCtx* c = nullptr;
+  ORYX_TRY(ctx_acquire(m, &c));
+  int32_t rc = ORYX_OK;
+  {
+    std::lock_guard<std::mutex> gram_lock(m->gram_mu);  // m->d_gram is this model's Gram buffer
+    cudaStream_t st = c->stream;
+    int32_t status = 0;
+    // (an empty shard's Gram is all zeros: the reference skips null partitions, ASM:365-366)
+    rc = oryx_gram_allreduce_device(x, m->d_gram, F, x->d_gram_status, st);
+    if (rc == ORYX_OK &&
+        (cudaMemcpyAsync(out, m->d_gram, (size_t)F * F * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+         cudaMemcpyAsync(&status, x->d_gram_status, sizeof(status), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+         cudaStreamSynchronize(st) != cudaSuccess)) {
+      set_error("Gram all-reduce failed: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = ORYX_E_CUDA;
+    }
+    if (rc == ORYX_OK && status != 0) {
+      set_error("Gram all-reduce: a peer did not arrive within ORYX_EXCHANGE_TIMEOUT_MS");
+      rc = ORYX_E_CUDA;
+    }
+  }
+  if (rc != ORYX_OK) cudaStreamSynchronize(c->stream);
+  ctx_release(m, c);
+  return rc;
 }
 
 }  // extern "C"

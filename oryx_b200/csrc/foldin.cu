@@ -341,11 +341,11 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     // pinned staging -> the caller's (pageable, often freshly allocated) array: a few threads, because one
     // core's memcpy and first-touch page faults were what the whole call waited for
     const size_t bytes = (size_t)c * f * sizeof(float);
-    const int n_thr = bytes >= ((size_t)16 << 20) ? 4 : 1;
+    const int n_thr = bytes >= ((size_t)64 << 20) ? 8 : bytes >= ((size_t)16 << 20) ? 4 : 1;
     if (n_thr == 1) {
       std::memcpy(out + off * f, b.h_out[par], bytes);
     } else {
-      std::thread workers[4];
+      std::thread workers[8];
       const size_t piece = (bytes / n_thr + 4095) & ~(size_t)4095;
       for (int t = 0; t < n_thr; t++) {
         const size_t lo = std::min(bytes, piece * t), hi = std::min(bytes, piece * (t + 1));

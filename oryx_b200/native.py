@@ -106,6 +106,8 @@ SIGNATURES = {
     "oryx_fold_in_rows_peers": [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _i64p, _i64p, _f64p,
                                 C.c_int64, _f32p, _u8p],
     "oryx_gram": [C.c_void_p, C.c_int32, _f64p, _i64p],
+    "oryx_gram_allreduce_device": [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p],
+    "oryx_gram_sharded": [C.c_void_p, C.c_void_p, C.c_int32, _f64p, _i64p],
     "oryx_solver_create": [_f64p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), _i32p],
     "oryx_solver_destroy": [C.c_void_p],
     "oryx_solve_f2f": [C.c_void_p, _f32p, _f32p],
@@ -463,6 +465,19 @@ class Exchange:
              d_scores: int, d_n: int, stream: int):
         _check(lib().oryx_topn_sharded_device(model._h, self._h, kind, d_query, how_many, row_stride, d_rows,
                                               d_scores, d_n, stream))
+
+    def gram_allreduce_device(self, d_gram: int, features: int, d_status: int, stream: int):
+        """Sum of the ranks' features x features float64 device matrices over peer memory, in place
+        (oryx_gram_allreduce_device).  d_status: device int32, 0 = ok."""
+        _check(lib().oryx_gram_allreduce_device(self._h, C.c_void_p(d_gram), features, C.c_void_p(d_status),
+                                                C.c_void_p(stream)))
+
+    def gram_sharded(self, model: "Model", which: int = Y):
+        """The global Gram of a row-sharded store: this rank's oryx_gram, then the peer-memory all-reduce."""
+        out = np.zeros((model.features, model.features), dtype=np.float64)
+        used = C.c_int64()
+        _check(lib().oryx_gram_sharded(model._h, self._h, which, _ptr(out, C.c_double), C.byref(used)))
+        return out, used.value
 
     def close(self):
         if self._h:

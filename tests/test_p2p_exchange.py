@@ -170,3 +170,61 @@ def test_sharded_batch_merges_to_the_unsharded_answer():
         k = int(cnt[i])
         assert np.array_equal(d_rows[i, :k].cpu().numpy(), rows[i, :k])
         assert d_scores[i, :k].cpu().numpy().tobytes() == scores[i, :k].tobytes()
+
+
+def _gram_allreduce(world):
+    """oryx_gram_sharded / oryx_gram_allreduce_device: per-shard Grams summed by one kernel over peer memory equal
+    the oracle's Gram of the whole matrix; every rank holds the same bits."""
+    import threading
+    f, n_per = 48, 30000
+    ys = [random_model(n_per, f, 0xB2000700 + r) for r in range(world)]
+    models, xs = [], []
+    for r in range(world):
+        with torch.cuda.device(r):
+            m = ob.Model(f, device=r)
+            m.upsert(ob.Y, np.arange(n_per, dtype=np.int32), ys[r])
+            models.append(m)
+            xs.append(ob.Exchange(r, world, r, 16))
+    ob.Exchange.connect_local(xs)
+    want = oracle.transpose_times_self(np.concatenate(ys))
+    for rep in range(3):   # parities alternate; the third call reuses the first one's slots
+        got = [None] * world
+        def run(r):
+            got[r] = xs[r].gram_sharded(models[r], ob.Y)
+        ts = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        for r in range(world):
+            g, used = got[r]
+            assert used == n_per
+            assert np.max(np.abs(g - want)) <= 1e-12 * np.max(np.abs(want))
+            assert g.tobytes() == got[0][0].tobytes()      # rank order of the additions: identical everywhere
+    # the device form, on matrices of the caller
+    d = [torch.full((f, f), float(r + 1), dtype=torch.float64, device=torch.device("cuda", r)) for r in range(world)]
+    st = [torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", r)) for r in range(world)]
+    for r in range(world):
+        with torch.cuda.device(r):
+            xs[r].gram_allreduce_device(d[r].data_ptr(), f, st[r].data_ptr(), torch.cuda.current_stream().cuda_stream)
+    for r in range(world):
+        with torch.cuda.device(r):
+            torch.cuda.synchronize()
+        assert int(st[r].item()) == 0
+        assert torch.all(d[r] == world * (world + 1) / 2).item()
+    for x in xs:
+        x.close()
+    for m in models:
+        m.close()
+
+
+def test_gram_allreduce_world_1():
+    _gram_allreduce(1)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_gram_allreduce_two_gpus():
+    _gram_allreduce(2)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs four GPUs")
+def test_gram_allreduce_four_gpus():
+    _gram_allreduce(4)
