@@ -26,7 +26,7 @@ void ctx_destroy(QueryCtx* c) {
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   cudaFree(c->d_query); cudaFree(c->d_excl); cudaFree(c->d_cand); cudaFree(c->d_list_max); cudaFree(c->d_counter); cudaFree(c->d_finish_seq);
-  cudaFree(c->d_main_index); cudaFree(c->d_worklist); cudaFree(c->d_out_n);
+  cudaFree(c->d_main_index); cudaFree(c->d_worklist); cudaFree(c->d_worklist_ctl); cudaFree(c->d_out_n);
   cudaFree(c->d_tmp[0]); cudaFree(c->d_tmp[1]);
   cudaFreeHost(c->h_query); cudaFreeHost(c->h_excl); cudaFreeHost(c->h_out_n);
 }

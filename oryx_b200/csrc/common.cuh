@@ -238,6 +238,8 @@ struct QueryCtx {
   int32_t* d_worklist = nullptr;
   int64_t worklist_cap = 0;
   int worklist_flip = 0;
+  unsigned int* d_worklist_ctl = nullptr;  // [0] CTAs of this context's list kernels that have completed, ever
+  unsigned int worklist_seq = 0;           // ... and how many were launched (mod 2^32)
   int32_t* d_out_rows = nullptr;  // [max_k]
   double* d_out_scores = nullptr; // [max_k]
   int32_t* d_out_n = nullptr;
@@ -375,7 +377,8 @@ int32_t lsh_hash_rows_device(Model* m, const float* d_rows, int64_t n, int strid
                              cudaStream_t stream, int32_t* d_zero_counter = nullptr, bool early_start = false);
 int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_worklist, cudaStream_t stream);
 int32_t lsh_query_worklist_device(Model* m, const float* d_query, int32_t* d_main_index, int32_t* d_worklist,
-                                  int32_t* d_other_count, cudaStream_t stream);
+                                  int32_t* d_other_count, unsigned int* d_done_ctas, unsigned int* expected_total,
+                                  cudaStream_t stream);
 int32_t lsh_candidates_device(Model* m, const int32_t* d_main_index, int32_t* d_out, int32_t* d_out_n,
                               cudaStream_t stream);
 

@@ -257,15 +257,19 @@ __global__ void lsh_worklist_kernel(const int32_t* __restrict__ block_part, int6
 //
 // The list's count must be zero at launch: lists alternate per query and this kernel zeroes the count of the
 // OTHER list (its scan has completed: this kernel is released by that scan's finishing kernel), which the
-// next query appends to.  The scan that follows is launched as a programmatic dependent and does NOT call
-// griddepcontrol.wait (that would make it wait for the previous query's finishing kernel as well): this kernel
-// therefore never releases its dependents early, and every thread fences its writes before it exits -- the
-// scan's CTAs are launched after the last of these exits and read the list and the index from L2.
+// next query appends to.  The scan that follows is launched as a programmatic dependent and normally does NOT
+// call griddepcontrol.wait (that would make it wait for the previous query's finishing kernel as well): this
+// kernel never releases its dependents early, every thread fences its writes, and every CTA then adds one to a
+// per-context counter with a release reduction (fire and forget: nobody waits for its round trip).  The scan's
+// CTAs -- launched after the last CTA of this grid has exited -- read the counter with an acquire load: the
+// expected total (all CTAs of all list kernels this context ever launched) means every write of this grid is
+// visible to them; should it ever fall short (nothing in the launch order itself promises otherwise), they fall
+// back to griddepcontrol.wait.
 __global__ void __launch_bounds__(256)
 lsh_query_worklist_kernel(const float* __restrict__ q, int features, const float* __restrict__ hash_vectors,
                           int hv_stride, int num_hashes, const int32_t* __restrict__ block_part, int64_t n_blocks,
                           int max_bits, int32_t* __restrict__ main_index_out, int32_t* __restrict__ worklist,
-                          int32_t* __restrict__ other_count) {
+                          int32_t* __restrict__ other_count, unsigned int* __restrict__ done_ctas) {
   __shared__ int s_bits;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   if (threadIdx.x == 0) s_bits = 0;
@@ -318,7 +322,9 @@ lsh_query_worklist_kernel(const float* __restrict__ q, int features, const float
       if (want) worklist[1 + base + __popc(ball & ((1u << lane) - 1u))] = (int32_t)b;
     }
   }
-  __threadfence();  // see above: the dependent scan relies on this instead of griddepcontrol.wait
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(done_ctas) : "memory");
 }
 
 }  // namespace
@@ -403,7 +409,8 @@ int32_t lsh_worklist_device(Model* m, const int32_t* d_main_index, int32_t* d_wo
 // Hash the query at d_query and list the candidate blocks of Y in `d_worklist` (count at [0], which must be
 // zero: see lsh_query_worklist_kernel); `d_other_count` is the count of the context's other list.
 int32_t lsh_query_worklist_device(Model* m, const float* d_query, int32_t* d_main_index, int32_t* d_worklist,
-                                  int32_t* d_other_count, cudaStream_t stream) {
+                                  int32_t* d_other_count, unsigned int* d_done_ctas, unsigned int* expected_total,
+                                  cudaStream_t stream) {
   Store* s = &m->store[ORYX_Y];
   const int64_t n_blocks = (s->n_slots + kBlockRows - 1) / kBlockRows;
   const int threads = 256;
@@ -423,7 +430,8 @@ int32_t lsh_query_worklist_device(Model* m, const float* d_query, int32_t* d_mai
   ORYX_CUDA(cudaLaunchKernelEx(&cfg, lsh_query_worklist_kernel, d_query, m->cfg.features,
                                (const float*)m->d_hash_vectors, s->fpad, m->num_hashes,
                                (const int32_t*)s->d_block_part, n_blocks, m->max_bits, d_main_index, d_worklist,
-                               d_other_count));
+                               d_other_count, d_done_ctas));
+  *expected_total += (unsigned int)grid;
   m->launches++;
   return ORYX_OK;
 }

@@ -66,6 +66,8 @@ struct ScanParams {
   uint2* cand;            // scratch [n_lists x k]
   uint32_t* list_max;     // scratch [n_lists]: largest key of each published list (0 = empty list)
   unsigned int* counter;  // dynamic tile counter; zero at launch, reset by the finishing kernel
+  const unsigned int* worklist_flag;  // CTAs of the context's list kernels completed so far ...
+  unsigned int worklist_seq;          // ... and the total once this query's list is complete
   int32_t* out_rows;
   double* out_scores;
   int32_t* out_n;
@@ -211,8 +213,18 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
   // the whole chain in front of it -- the previous query's finishing kernel included (measured, round 2: 29 us
   // between two pipelined filtered scans = that kernel's duration).  Its inputs are complete anyway: the kernel
   // that hashes the query and builds the list never releases its dependents early, so this grid is launched
-  // only after every thread of it has fenced its writes and exited; they are read with ld.global.cg below.
-  if ((LSH && p.worklist == nullptr) || p.n_excl > 0) pdl_wait_primary();
+  // only after every thread of it has fenced its writes and exited.  Every CTA of the list kernel counts itself
+  // with a release reduction; reading the expected total here (acquire) makes all of that grid's writes visible,
+  // and a shortfall -- never observed -- sends the CTA to griddepcontrol.wait.  List and index are read with
+  // ld.global.cg.
+  __shared__ unsigned int s_list_seen;
+  const bool guarded = LSH && p.worklist != nullptr && p.n_excl == 0;
+  if (!guarded && (LSH || p.n_excl > 0)) pdl_wait_primary();
+  if (guarded && tid == 0) {  // one acquire load per CTA, in flight while the CTA sets itself up
+    unsigned int seen;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.worklist_flag) : "memory");
+    s_list_seen = seen;
+  }
   const int32_t* excl = p.excl_in_smem ? s_excl_buf : p.excl;
   if (p.excl_in_smem) {
     for (int i = tid; i < p.n_excl; i += T) s_excl_buf[i] = __ldg(p.excl + i);
@@ -221,6 +233,10 @@ scan_topn_kernel(const __grid_constant__ ScanParams p) {
   for (int i = tid; i < p.k; i += T) cand_arr[i] = 0ull;  // empty sentinels
   if (tid == 0) s_thr_key = 0u;
   __syncthreads();
+  if (guarded && s_list_seen != p.worklist_seq) {  // not expected; the formal guarantee
+    if (p.debug_ts && tid == 0) atomicAdd(p.debug_ts + 11, 1ull);
+    pdl_wait_primary();
+  }
 
   const int f4 = p.f4;
   float4 qv[NV];
@@ -856,13 +872,18 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
         ORYX_CUDA(cudaMemsetAsync(ctx->d_worklist, 0, 2 * (size_t)cap * sizeof(int32_t), stream));  // both counts start at zero
         ctx->worklist_cap = cap;
       }
+      if (ctx->d_worklist_ctl == nullptr) {
+        ORYX_CUDA(cudaMalloc(&ctx->d_worklist_ctl, 4 * sizeof(unsigned int)));
+        ORYX_CUDA(cudaMemsetAsync(ctx->d_worklist_ctl, 0, 4 * sizeof(unsigned int), stream));
+      }
       // One launch hashes the query and lists its candidate blocks.  It depends on nothing earlier in the
       // stream, so it starts while the previous query's finishing kernel still runs; the previous scan (the
       // only reader of main_index and of the work lists) has completed by then, because the finishing kernel
       // that releases us is itself only launched when its scan has exited.
       worklist = ctx->d_worklist + (size_t)(ctx->worklist_flip ^= 1) * ctx->worklist_cap;
       ORYX_TRY(lsh_query_worklist_device(m, rq.d_query, ctx->d_main_index, worklist,
-                                         ctx->d_worklist + (size_t)(ctx->worklist_flip ^ 1) * ctx->worklist_cap, stream));
+                                         ctx->d_worklist + (size_t)(ctx->worklist_flip ^ 1) * ctx->worklist_cap,
+                                         ctx->d_worklist_ctl, &ctx->worklist_seq, stream));
     } else {
       ORYX_TRY(lsh_hash_rows_device(m, rq.d_query, 1, s->fpad, ctx->d_main_index, stream, nullptr, false));
     }
@@ -873,6 +894,8 @@ int32_t scan_topn_launch(Model* m, QueryCtx* ctx, const TopnRequest& rq, cudaStr
   p.slot_part = s->d_slot_part;
   p.block_part = s->d_block_part;
   p.worklist = worklist;
+  p.worklist_flag = worklist ? ctx->d_worklist_ctl : nullptr;
+  p.worklist_seq = ctx->worklist_seq;
   p.q = rq.d_query;
   p.excl = rq.d_excl;
   p.n_excl = rq.n_excl;
