@@ -155,6 +155,20 @@ def c4_gram_foldin(ob, torch, dev, threads: int, n_items: int = 10_000_000, f: i
     out, valid = solver.fold_in_rows(model, True, ob.X, ur, ir, vals)
     fold_wall = time.perf_counter() - t0
     ft = solver.debug_fold_in_timings()
+    # the same call into a page-locked result array (what a JNI direct buffer registered once, or pinned memory of any
+    # host runtime, gives): the rows are copied straight into it
+    pinned_wall = pinned_same = None
+    try:
+        pin = torch.empty((n_updates, f), dtype=torch.float32, pin_memory=True)
+        out_p, valid_p = solver.fold_in_rows(model, True, ob.X, ur, ir, vals, out=pin.numpy())
+        t0 = time.perf_counter()
+        out_p, valid_p = solver.fold_in_rows(model, True, ob.X, ur, ir, vals, out=pin.numpy())
+        pinned_wall = time.perf_counter() - t0
+        vm = valid == 1
+        pinned_same = bool(np.array_equal(valid_p, valid) and np.array_equal(out_p[vm], out[vm]))
+        del pin, out_p
+    except Exception as e:  # noqa: BLE001
+        pinned_same = repr(e)
     e_solver = oracle.Solver(g)
     npar = 512
     eo, ev = oracle.fold_in_batch(e_solver, True, x_sub[:npar], np.ones(npar, np.uint8), y_sub[ir[:npar]], vals[:npar])
@@ -181,6 +195,8 @@ def c4_gram_foldin(ob, torch, dev, threads: int, n_items: int = 10_000_000, f: i
         },
         "fold_in": {
             "fold_in_device_ms": k_ms, "chunks": ft["chunks"], "wall_ms_host_buffers_out": 1000.0 * fold_wall,
+            "wall_ms_page_locked_out": 1000.0 * pinned_wall if pinned_wall is not None else None,
+            "page_locked_result_identical": pinned_same,
             "interactions_per_sec_device": n_updates / (k_ms / 1000.0) if k_ms > 0 else None,
             "roofline_hbm": {"achieved": fold_bytes / (k_ms / 1000.0) / 1e9 if k_ms > 0 else None, "peak": pk["hbm_gbs"], "unit": "GB/s",
                              "frac": fold_bytes / (k_ms / 1000.0) / 1e9 / pk["hbm_gbs"] if k_ms > 0 else None,

@@ -335,9 +335,25 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
   const auto wall0 = std::chrono::steady_clock::now();
   double kernel_ms = 0;
   int chunks = 0;
+  // A caller whose result array is page-locked (cudaHostAlloc / cudaHostRegister: a JNI direct buffer registered
+  // once, a torch pinned tensor) gets the rows copied straight into it; pageable arrays go through the pinned
+  // staging buffers and a multi-threaded memcpy.
+  bool direct = false;
+  {
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, out) == cudaSuccess) direct = attr.type == cudaMemoryTypeHost;
+    else cudaGetLastError();
+  }
   auto finalize = [&](int64_t off, int64_t c, int par) -> cudaError_t {
     cudaError_t e = cudaEventSynchronize(fs->ev_copied[par]);
     if (e != cudaSuccess) return e;
+    if (direct) {
+      std::memcpy(out_valid + off, b.h_valid[par], (size_t)c);
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, fs->ev_k0[par], fs->ev_k1[par]) == cudaSuccess) kernel_ms += ms;
+      else cudaGetLastError();
+      return cudaSuccess;
+    }
     // pinned staging -> the caller's (pageable, often freshly allocated) array: a few threads, because one
     // core's memcpy and first-touch page faults were what the whole call waited for
     const size_t bytes = (size_t)c * f * sizeof(float);
@@ -376,7 +392,7 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     if ((e = cudaEventRecord(fs->ev_k1[par], st)) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_done[par], st)) != cudaSuccess) break;
     if ((e = cudaStreamWaitEvent(fs->copy_stream, fs->ev_done[par], 0)) != cudaSuccess) break;
-    if ((e = cudaMemcpyAsync(b.h_out[par], b.d_out[par], (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, fs->copy_stream)) != cudaSuccess) break;
+    if ((e = cudaMemcpyAsync(direct ? out + off * f : b.h_out[par], b.d_out[par], (size_t)c * f * sizeof(float), cudaMemcpyDeviceToHost, fs->copy_stream)) != cudaSuccess) break;
     if ((e = cudaMemcpyAsync(b.h_valid[par], b.d_valid[par], (size_t)c, cudaMemcpyDeviceToHost, fs->copy_stream)) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_copied[par], fs->copy_stream)) != cudaSuccess) break;
     if (prev_off >= 0 && (e = finalize(prev_off, prev_c, par ^ 1)) != cudaSuccess) break;

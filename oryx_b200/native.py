@@ -630,13 +630,17 @@ class Solver:
                                              _ptr(out, C.c_float), _ptr(valid, C.c_uint8)))
         return out, valid
 
-    def fold_in_rows(self, model: "Model", implicit: bool, xu_which: int, xu_rows, yi_rows, values):
-        """computeUpdatedXu for n interactions whose vectors are rows of the model's device stores."""
+    def fold_in_rows(self, model: "Model", implicit: bool, xu_which: int, xu_rows, yi_rows, values, out=None):
+        """computeUpdatedXu for n interactions whose vectors are rows of the model's device stores.
+        `out`: optional C-contiguous float32 [n x features] array to receive the rows; when it is page-locked
+        (e.g. the numpy view of a torch pinned tensor) the library copies into it directly."""
         xr = np.ascontiguousarray(xu_rows, dtype=np.int32)
         yr = np.ascontiguousarray(yi_rows, dtype=np.int32)
         vals = np.ascontiguousarray(values, dtype=np.float64)
         n = xr.size
-        out = np.empty((n, self.n), dtype=np.float32)
+        if out is None:
+            out = np.empty((n, self.n), dtype=np.float32)
+        assert out.dtype == np.float32 and out.shape == (n, self.n) and out.flags["C_CONTIGUOUS"]
         valid = np.zeros(n, dtype=np.uint8)
         _check(lib().oryx_fold_in_rows(self._h, model._h, int(implicit), xu_which, _ptr(xr, C.c_int32),
                                        _ptr(yr, C.c_int32), _ptr(vals, C.c_double), n, _ptr(out, C.c_float),

@@ -25,5 +25,12 @@ res = []
 for _ in range(3):
     t0 = time.perf_counter(); out, valid = s.fold_in_rows(m, True, ob.X, ur, ir, vals); wall = time.perf_counter() - t0
     t = s.debug_fold_in_timings(); t["wall_ms_python"] = wall * 1e3; res.append(t)
-print(json.dumps({"features": f, "interactions": n, "runs": res}))
+pin = torch.empty((n, f), dtype=torch.float32, pin_memory=True)
+pres = []
+for _ in range(3):
+    t0 = time.perf_counter(); out_p, valid_p = s.fold_in_rows(m, True, ob.X, ur, ir, vals, out=pin.numpy()); wall = time.perf_counter() - t0
+    t = s.debug_fold_in_timings(); t["wall_ms_python"] = wall * 1e3; pres.append(t)
+ok = valid == 1
+same = bool(np.array_equal(valid_p, valid) and np.array_equal(out_p[ok], out[ok]))
+print(json.dumps({"features": f, "interactions": n, "runs": res, "runs_page_locked_result": pres, "page_locked_result_identical": same}))
 s.close(); m.close()
