@@ -626,7 +626,10 @@ def run_ours(args):
                        "exchange_matches_nccl_path": exchange_check if world > 1 else None,
                        "parity_vs_oracle_sharded": (extras or {}).get("parity_vs_oracle_sharded") if world > 1 else None},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic,
+                         "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel, recorded in "
+                                           "profiles/scan_traffic.json (read from there, not re-measured in this run)" if traffic else None,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes,
                          "frac_of_nominal_8000": achieved / 8000.0},
             "cpu_baseline": cpu_baseline,
