@@ -299,7 +299,8 @@ def sharded_parity_and_gram(ob, torch, dist, dev, rank: int, world: int, threads
             dist.all_reduce(same_everywhere, op=dist.ReduceOp.MIN)
             peer = {"peer_memory_kernel_ms_max_over_ranks": float(t.item()), "status": int(d_st.item()),
                     "max_rel_diff_vs_nccl_sum": float((d_p - d_g).abs().max().item() / d_g.abs().max().item()),
-                    "bits_equal_to_nccl_sum_on_rank0": bool(same.item()),
+                    "same_bits_as_nccl_sum": bool(same.item()),
+                    "note": "ranks are added in rank order; NCCL's own order differs for N > 2, so its sum may differ in the last bit",
                     "bits_equal_on_every_rank": bool(same_everywhere.item())}
         except Exception as e:  # noqa: BLE001
             peer = {"error": repr(e)}
