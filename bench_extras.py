@@ -20,7 +20,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-FP64_NOMINAL_TFLOPS = 37.0   # B200 (HGX) binary64 FMA peak, nominal; no measured figure exists for it
+FP64_NOMINAL_TFLOPS = 37.0   # B200 binary64 peak: nominal 37; measured here 36.6 (DFMA) / 37.1 (DMMA m8n8k4), tools/fp64_probe.cu
 
 
 def peaks() -> dict:
@@ -203,7 +203,7 @@ def c4_gram_foldin(ob, torch, dev, threads: int, n_items: int = 10_000_000, f: i
                              "algorithmic_bytes": fold_bytes},
             "roofline_fp64": {"achieved": fold_flops / (k_ms / 1000.0) / 1e12 if k_ms > 0 else None, "peak": FP64_NOMINAL_TFLOPS,
                               "unit": "TFLOP/s", "frac": fold_flops / (k_ms / 1000.0) / 1e12 / FP64_NOMINAL_TFLOPS if k_ms > 0 else None,
-                              "peak_kind": "nominal binary64 FMA rate (no measured figure)"},
+                              "peak_kind": "binary64 rate: nominal 37, measured 36.6 DFMA / 37.1 DMMA on this pool (profiles/r02_fp64_probe.txt)"},
             "valid_flags_match_oracle": fold_ok, "max_rel_err_vs_oracle": fold_rel, "parity_rows": npar,
             "valid_fraction": float(valid.mean()),
         },

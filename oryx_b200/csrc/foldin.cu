@@ -14,6 +14,7 @@
 // derives from the same QR factors; everything else is the reference's operation sequence.
 #include <algorithm>
 #include <chrono>
+#include <mutex>
 #include <thread>
 
 #include "common.cuh"
@@ -132,16 +133,23 @@ __device__ __forceinline__ double target_qui(bool implicit, double value, double
 }
 
 // One CTA = 128 interactions x all F outputs.  Phase 1: one thread per interaction computes Qui with the
-// exact sequential arithmetic and the scalar dQui.  Phase 2: binary64 GEMM
-// X[k][r] = sum_c inv[r][c] * b[k][c], tiled 128 (interactions) x 64 (outputs) x 16 (c); a thread owns 8
-// interactions x 4 outputs (32 binary64 accumulators), and both operand tiles are read with 128-bit
-// loads laid out so that a warp touches at most two 128-byte wavefronts per load (the 4 x 4 version with
-// 64-bit loads spent three cycles in the load/store unit for every cycle of binary64 FMA).  The sum over c
-// runs in index order with one FMA per term, for every output.
+// exact sequential arithmetic and the scalar dQui.  Phase 2: the binary64 product
+// X[k][r] = sum_c b[k][c] * inv[r][c] on the FP64 tensor cores (mma.sync m8n8k4, round 2): CTA tile 128
+// (interactions) x 64 (outputs) x 32 (c), a warp owns 16 interactions x 64 outputs = 2 x 8 accumulator tiles
+// (32 binary64 registers per thread) and reads one A and one B element per tile and k-step from shared memory.
+// Both operand tiles sit in shared memory the way they sit in global memory ([interaction][c] and [output][c]),
+// with a row stride of kFoldK + 4 doubles (= 4 mod 16): tile stores are contiguous per warp and the 32 lanes of a
+// fragment load hit the 16 bank pairs exactly twice, the minimum.
+// The scalar-FMA version issued 32 DFMA + 6 LDS.128 per thread for 1024 multiply-adds and kept the binary64 pipe
+// 37 % busy; a DMMA carries 256 multiply-adds.  Sums over c run in index order, four terms per instruction.
 constexpr int kFoldK = 32;                 // c per tile
 constexpr int kFoldOut = 64;               // outputs per tile
-constexpr int kFoldBLd = kRowsPerCta + 2;  // padded row strides (doubles), multiples of 2 for 128-bit loads
-constexpr int kFoldILd = kFoldOut + 2;
+constexpr int kFoldLd = kFoldK + 4;        // padded row stride (doubles), = 4 mod 16
+
+__device__ __forceinline__ void dmma_m8n8k4(double (&d)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
+}
 
 __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restrict__ inv, int f, int implicit,
                                                          const float* __restrict__ xu,
@@ -154,8 +162,13 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   __shared__ uint8_t s_valid[kRowsPerCta];
   __shared__ uint8_t s_has[kRowsPerCta];
   extern __shared__ __align__(16) unsigned char fold_smem[];
-  double (*Bs)[kFoldBLd] = reinterpret_cast<double (*)[kFoldBLd]>(fold_smem);                                   // b tile: [c][k]
-  double (*Is)[kFoldILd] = reinterpret_cast<double (*)[kFoldILd]>(fold_smem + sizeof(double) * kFoldK * kFoldBLd);  // inverse tile: [c][r]
+  // { b tile [k][c], inverse tile [r][c] }  (a second buffer, so that tile t + 1 could be stored while other warps
+  // still read tile t, measured slower: 8.2-8.4 ms against 8.0 ms at 1 M x 256)
+  constexpr size_t kBufDoubles = (size_t)(kRowsPerCta + kFoldOut) * kFoldLd;
+  auto b_tile = [&](int buf) { return reinterpret_cast<double (*)[kFoldLd]>(fold_smem + sizeof(double) * kBufDoubles * buf); };
+  auto i_tile = [&](int buf) {
+    return reinterpret_cast<double (*)[kFoldLd]>(fold_smem + sizeof(double) * (kBufDoubles * buf + (size_t)kRowsPerCta * kFoldLd));
+  };
   const int tid = threadIdx.x;
   const int64_t k0 = (int64_t)blockIdx.x * kRowsPerCta;
 
@@ -185,70 +198,107 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   }
   __syncthreads();
 
-  const int tx = tid & 15, ty = tid >> 4;  // ty -> interactions 8 ty .. 8 ty + 7; tx -> outputs 2 tx, 2 tx + 1, 32 + 2 tx, 33 + 2 tx
-  for (int r0 = 0; r0 < f; r0 += kFoldOut) {
-    double acc[8][4];
+  const int warp = tid >> 5, lane = tid & 31;
+  const int fr = lane >> 2, fc = lane & 3;  // fragment coordinates: row (or column) 0..7, k index 0..3
+  // Operand tiles travel global -> registers -> shared memory, one tile ahead: the loads of tile t + 1 are issued
+  // (all 24 of a thread at once) before the DMMAs of tile t and waited for only when tile t + 1 is stored.
+  constexpr int kRowsPerPass = 256 / kFoldK;                     // tile rows covered by one pass of the CTA's threads
+  constexpr int kBLoads = kRowsPerCta / kRowsPerPass, kILoads = kFoldOut / kRowsPerPass;
+  const int lc = tid % kFoldK, lr = tid / kFoldK;  // this thread's column of a tile and its first row (rows lr + kRowsPerPass u)
+  float yreg[kBLoads];
+  double ireg[kILoads];
+  auto load_tile = [&](int r0, int c0) {
+    const bool c_ok = c0 + lc < f;
 #pragma unroll
-    for (int i = 0; i < 8; i++)
-#pragma unroll
-      for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
-    for (int c0 = 0; c0 < f; c0 += kFoldK) {
-      __syncthreads();
-      // b tile: b[k][c] = (float)((double)yi[k][c] * dQui[k])  (ALSUtils.java:93-95)
-      for (int e = tid; e < kFoldK * kRowsPerCta; e += 256) {
-        int kk = e / kFoldK, c = e % kFoldK;
-        int64_t k = k0 + kk;
-        double v = 0.0;
-        if (k < n && c0 + c < f) {
-          float bf = (float)((double)yi[k * f + c0 + c] * s_dq[kk]);
-          v = (double)bf;
-        }
-        Bs[c][kk] = v;
-      }
-      // inverse tile: inv[r][c] (row-major)
-      for (int e = tid; e < kFoldK * kFoldOut; e += 256) {
-        int r = e / kFoldK, c = e % kFoldK;
-        Is[c][r] = (r0 + r < f && c0 + c < f) ? inv[(size_t)(r0 + r) * f + c0 + c] : 0.0;
-      }
-      __syncthreads();
-#pragma unroll
-      for (int c = 0; c < kFoldK; c++) {
-        double bv[8], iv[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const double2 t = *reinterpret_cast<const double2*>(&Bs[c][ty * 8 + 2 * i]);
-          bv[2 * i] = t.x;
-          bv[2 * i + 1] = t.y;
-        }
-        const double2 i0 = *reinterpret_cast<const double2*>(&Is[c][2 * tx]);
-        const double2 i1 = *reinterpret_cast<const double2*>(&Is[c][32 + 2 * tx]);
-        iv[0] = i0.x; iv[1] = i0.y; iv[2] = i1.x; iv[3] = i1.y;
-#pragma unroll
-        for (int i = 0; i < 8; i++)
-#pragma unroll
-          for (int j = 0; j < 4; j++) acc[i][j] = fma(bv[i], iv[j], acc[i][j]);
-      }
+    for (int u = 0; u < kBLoads; u++) {
+      const int64_t k = k0 + lr + kRowsPerPass * u;
+      yreg[u] = (k < n && c_ok) ? __ldg(yi + k * f + c0 + lc) : 0.f;
     }
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-      int kk = ty * 8 + i;
-      int64_t k = k0 + kk;
+    for (int u = 0; u < kILoads; u++) {
+      const int r = r0 + lr + kRowsPerPass * u;
+      ireg[u] = (r < f && c_ok) ? __ldg(inv + (size_t)r * f + c0 + lc) : 0.0;
+    }
+  };
+  auto store_tile = [&](int buf) {
+    double (*Bs)[kFoldLd] = b_tile(buf);
+    double (*Is)[kFoldLd] = i_tile(buf);
+#pragma unroll
+    for (int u = 0; u < kBLoads; u++) {
+      const int kk = lr + kRowsPerPass * u;
+      // b[k][c] = (float)((double)yi[k][c] * dQui[k])  (ALSUtils.java:93-95)
+      Bs[kk][lc] = (double)(float)((double)yreg[u] * s_dq[kk]);
+    }
+#pragma unroll
+    for (int u = 0; u < kILoads; u++) Is[lr + kRowsPerPass * u][lc] = ireg[u];  // inverse tile: inv[r][c] (row-major)
+  };
+  load_tile(0, 0);
+  for (int r0 = 0; r0 < f; r0 += kFoldOut) {
+    double acc[2][8][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+    for (int c0 = 0; c0 < f; c0 += kFoldK) {
+      __syncthreads();  // every warp is done with the previous tile
+      store_tile(0);
+      __syncthreads();
+      // next tile of this output block, or the first tile of the next one: its global loads fly during the DMMAs
+      const bool wrap = c0 + kFoldK >= f;
+      const int nr0 = wrap ? r0 + kFoldOut : r0, nc0 = wrap ? 0 : c0 + kFoldK;
+      if (nr0 < f) load_tile(nr0, nc0);
+      double (*Bs)[kFoldLd] = b_tile(0);
+      double (*Is)[kFoldLd] = i_tile(0);
+#pragma unroll
+      for (int kc = 0; kc < kFoldK / 4; kc++) {
+        const double a0 = Bs[warp * 16 + fr][4 * kc + fc];      // A (row-major 8 x 4): lane holds A[row fr][k fc]
+        const double a1 = Bs[warp * 16 + 8 + fr][4 * kc + fc];
+        double bfrag[8];
+#pragma unroll
+        for (int nt = 0; nt < 8; nt++) bfrag[nt] = Is[8 * nt + fr][4 * kc + fc];  // B (col-major 4 x 8): lane holds B[k fc][col fr]
+#pragma unroll
+        for (int nt = 0; nt < 8; nt++) {
+          dmma_m8n8k4(acc[0][nt], a0, bfrag[nt]);
+          dmma_m8n8k4(acc[1][nt], a1, bfrag[nt]);
+        }
+      }
+    }
+    // C fragment (8 x 8): lane holds C[row fr][columns 2 fc, 2 fc + 1]
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++) {
+      const int kk = warp * 16 + 8 * mt + fr;
+      const int64_t k = k0 + kk;
       if (k >= n) continue;
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        int r = r0 + (j < 2 ? 0 : 32) + 2 * tx + (j & 1);
-        if (r >= f) continue;
-        float dxu = (float)acc[i][j];  // Solver.java:40-42
-        float res = 0.0f;
-        if (s_valid[kk]) res = s_has[kk] ? __fadd_rn(xu[k * f + r], dxu) : dxu;  // ALSUtils.java:98-104
-        out[k * f + r] = res;
+      for (int nt = 0; nt < 8; nt++) {
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const int r = r0 + 8 * nt + 2 * fc + j;
+          if (r >= f) continue;
+          float dxu = (float)acc[mt][nt][j];  // Solver.java:40-42
+          float res = 0.0f;
+          if (s_valid[kk]) res = s_has[kk] ? __fadd_rn(xu[k * f + r], dxu) : dxu;  // ALSUtils.java:98-104
+          out[k * f + r] = res;
+        }
       }
     }
   }
 }
 
-constexpr size_t kFoldSmem = sizeof(double) * kFoldK * (kFoldBLd + kFoldILd);
-constexpr int64_t kFoldChunk = 1 << 17;  // interactions per pipeline stage
+constexpr size_t kFoldSmem = sizeof(double) * kFoldLd * (kRowsPerCta + kFoldOut);
+// Interactions per pipeline stage: whole waves of the kernel (2 CTAs of 128 interactions per SM), four of them --
+// a power-of-two chunk left the last wave of every launch 46 % full on 148 SMs.
+int64_t fold_chunk() {
+  static const int64_t chunk = [] {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+      cudaGetLastError();
+      sms = 148;
+    }
+    return (int64_t)sms * 2 * kRowsPerCta * 4;
+  }();
+  return chunk;
+}
 
 int32_t fold_buf(FoldScratch* fs, int i, size_t bytes, void** out) {
   if (fs->d_bytes[i] < bytes) {
@@ -293,7 +343,7 @@ struct FoldBuffers {
 };
 
 int32_t fold_prepare(FoldScratch* fs, int f, int64_t n, bool need_idx, FoldBuffers* b) {
-  const int64_t c_max = std::min<int64_t>(kFoldChunk, n);
+  const int64_t c_max = std::min<int64_t>(fold_chunk(), n);
   b->c_max = c_max;
   void* p = nullptr;
   ORYX_TRY(fold_buf(fs, 0, (size_t)c_max * f * 4, &p)); b->d_xu = (float*)p;
@@ -379,8 +429,9 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
   };
   int64_t prev_off = -1, prev_c = 0;
   cudaError_t e = cudaSuccess;
-  for (int64_t off = 0; off < n; off += kFoldChunk, chunks++) {
-    const int64_t c = std::min<int64_t>(kFoldChunk, n - off);
+  const int64_t chunk = fold_chunk();
+  for (int64_t off = 0; off < n; off += chunk, chunks++) {
+    const int64_t c = std::min<int64_t>(chunk, n - off);
     const int par = chunks & 1;
     e = stage(off, c, par);
     if (e != cudaSuccess) break;
