@@ -132,8 +132,41 @@ __device__ __forceinline__ double target_qui(bool implicit, double value, double
   return value;
 }
 
-// One CTA = 128 interactions x all F outputs.  Phase 1: one thread per interaction computes Qui with the
-// exact sequential arithmetic and the scalar dQui.  Phase 2: the binary64 product
+// Step 1 of a fold-in chunk, one warp per interaction (memory-bound): Qui = dot(Xu, Yi) with the reference's exact
+// arithmetic (the whole warp when the chain provably never rounds, lane 0 otherwise: common.cuh warp_exact_dot),
+// computeTargetQui, dQui, the null verdict, and b = (float)((double)Yi * dQui) (ALSUtils.java:93-95) written over Yi
+// in the chunk's scratch.  Keeping this inside the GEMM kernel cost it a tenth of its time in per-thread binary64
+// chains and made every CTA redo the b tile -- a DMUL and three conversions per element -- once per output block.
+__global__ void __launch_bounds__(256) fold_prep_kernel(int f, int implicit, const float* __restrict__ xu,
+                                                        const uint8_t* __restrict__ has_xu, float* __restrict__ yi_to_b,
+                                                        const uint8_t* __restrict__ has_yi,
+                                                        const double* __restrict__ values, int64_t n,
+                                                        uint8_t* __restrict__ out_valid) {
+  const int64_t k = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (k >= n) return;
+  const uint8_t has = has_xu ? has_xu[k] : 1;
+  float* y = yi_to_b + k * f;
+  double qui = 0.0;
+  if (has) {
+    const float* x = xu + k * f;
+    if (!warp_exact_dot(x, y, f, lane, &qui)) {
+      if (lane == 0) {
+        qui = 0.0;
+        for (int j = 0; j < f; j++) qui = exact_step(qui, x[j], y[j]);
+      }
+      qui = __shfl_sync(0xffffffffu, qui, 0);
+    }
+  }
+  const double target = target_qui(implicit != 0, values[k], has ? qui : 0.5);
+  // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81) or the target is NaN (:90-92)
+  const bool valid = target == target && (has_yi == nullptr || has_yi[k]);
+  const double dq = valid ? target - qui : 0.0;
+  for (int j = lane; j < f; j += 32) y[j] = (float)((double)y[j] * dq);
+  if (lane == 0) out_valid[k] = valid ? 1 : 0;
+}
+
+// Step 2.  One CTA = 128 interactions x all F outputs: the binary64 product
 // X[k][r] = sum_c b[k][c] * inv[r][c] on the FP64 tensor cores (mma.sync m8n8k4, round 2): CTA tile 128
 // (interactions) x 64 (outputs) x 32 (c), a warp owns 16 interactions x 64 outputs = 2 x 8 accumulator tiles
 // (32 binary64 registers per thread) and reads one A and one B element per tile and k-step from shared memory.
@@ -151,14 +184,12 @@ __device__ __forceinline__ void dmma_m8n8k4(double (&d)[2], double a, double b) 
                : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restrict__ inv, int f, int implicit,
+__global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restrict__ inv, int f,
                                                          const float* __restrict__ xu,
                                                          const uint8_t* __restrict__ has_xu,
-                                                         const float* __restrict__ yi,
-                                                         const uint8_t* __restrict__ has_yi,
-                                                         const double* __restrict__ values, int64_t n,
-                                                         float* __restrict__ out, uint8_t* __restrict__ out_valid) {
-  __shared__ double s_dq[kRowsPerCta];
+                                                         const float* __restrict__ bmat,  // b of fold_prep_kernel
+                                                         int64_t n, float* __restrict__ out,
+                                                         const uint8_t* __restrict__ valid_in) {
   __shared__ uint8_t s_valid[kRowsPerCta];
   __shared__ uint8_t s_has[kRowsPerCta];
   extern __shared__ __align__(16) unsigned char fold_smem[];
@@ -173,28 +204,9 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   const int64_t k0 = (int64_t)blockIdx.x * kRowsPerCta;
 
   if (tid < kRowsPerCta) {
-    int64_t k = k0 + tid;
-    double dq = 0.0;
-    uint8_t valid = 0, has = 0;
-    if (k < n) {
-      has = has_xu ? has_xu[k] : 1;
-      const float* y = yi + k * f;
-      double qui = 0.0;
-      if (has) {
-        const float* x = xu + k * f;
-        for (int j = 0; j < f; j++) qui = exact_step(qui, x[j], y[j]);
-      }
-      double target = target_qui(implicit != 0, values[k], has ? qui : 0.5);
-      // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81) or the target is NaN (:90-92)
-      if (target == target && (has_yi == nullptr || has_yi[k])) {
-        valid = 1;
-        dq = target - qui;
-      }
-    }
-    s_dq[tid] = dq;
-    s_valid[tid] = valid;
-    s_has[tid] = has;
-    if (k < n) out_valid[k] = valid;
+    const int64_t k = k0 + tid;
+    s_valid[tid] = k < n ? valid_in[k] : 0;
+    s_has[tid] = k < n ? (has_xu ? has_xu[k] : 1) : 0;
   }
   __syncthreads();
 
@@ -212,7 +224,7 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
 #pragma unroll
     for (int u = 0; u < kBLoads; u++) {
       const int64_t k = k0 + lr + kRowsPerPass * u;
-      yreg[u] = (k < n && c_ok) ? __ldg(yi + k * f + c0 + lc) : 0.f;
+      yreg[u] = (k < n && c_ok) ? __ldg(bmat + k * f + c0 + lc) : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < kILoads; u++) {
@@ -226,8 +238,7 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
 #pragma unroll
     for (int u = 0; u < kBLoads; u++) {
       const int kk = lr + kRowsPerPass * u;
-      // b[k][c] = (float)((double)yi[k][c] * dQui[k])  (ALSUtils.java:93-95)
-      Bs[kk][lc] = (double)(float)((double)yreg[u] * s_dq[kk]);
+      Bs[kk][lc] = (double)yreg[u];
     }
 #pragma unroll
     for (int u = 0; u < kILoads; u++) Is[lr + kRowsPerPass * u][lc] = ireg[u];  // inverse tile: inv[r][c] (row-major)
@@ -263,21 +274,31 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
         }
       }
     }
-    // C fragment (8 x 8): lane holds C[row fr][columns 2 fc, 2 fc + 1]
+    // C fragment (8 x 8): lane holds C[row fr][columns 2 fc, 2 fc + 1].  The old vectors are fetched first, all
+    // sixteen of an accumulator row at once (one at a time, every add waited out its own global load).
 #pragma unroll
     for (int mt = 0; mt < 2; mt++) {
       const int kk = warp * 16 + 8 * mt + fr;
       const int64_t k = k0 + kk;
       if (k >= n) continue;
+      const bool valid = s_valid[kk] != 0, has = s_has[kk] != 0;
+      float old[8][2];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++)
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const int r = r0 + 8 * nt + 2 * fc + j;
+          old[nt][j] = (valid && has && r < f) ? __ldg(xu + k * f + r) : 0.f;
+        }
 #pragma unroll
       for (int nt = 0; nt < 8; nt++) {
 #pragma unroll
         for (int j = 0; j < 2; j++) {
           const int r = r0 + 8 * nt + 2 * fc + j;
           if (r >= f) continue;
-          float dxu = (float)acc[mt][nt][j];  // Solver.java:40-42
+          const float dxu = (float)acc[mt][nt][j];  // Solver.java:40-42
           float res = 0.0f;
-          if (s_valid[kk]) res = s_has[kk] ? __fadd_rn(xu[k * f + r], dxu) : dxu;  // ALSUtils.java:98-104
+          if (valid) res = has ? __fadd_rn(old[nt][j], dxu) : dxu;  // ALSUtils.java:98-104
           out[k * f + r] = res;
         }
       }
@@ -437,8 +458,11 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     if (e != cudaSuccess) break;
     const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
     if ((e = cudaEventRecord(fs->ev_k0[par], st)) != cudaSuccess) break;
-    fold_in_kernel<<<grid, 256, kFoldSmem, st>>>(solver_inverse(s), f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
-                                         use_has_yi ? b.d_has_yi : nullptr, b.d_val, c, b.d_out[par], b.d_valid[par]);
+    fold_prep_kernel<<<(unsigned)((c * 32 + 255) / 256), 256, 0, st>>>(f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
+                                                                      use_has_yi ? b.d_has_yi : nullptr, b.d_val, c,
+                                                                      b.d_valid[par]);
+    fold_in_kernel<<<grid, 256, kFoldSmem, st>>>(solver_inverse(s), f, b.d_xu, b.d_has_xu, b.d_yi, c, b.d_out[par],
+                                                 b.d_valid[par]);
     if ((e = cudaGetLastError()) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_k1[par], st)) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_done[par], st)) != cudaSuccess) break;
