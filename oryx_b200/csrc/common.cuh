@@ -289,6 +289,7 @@ struct FoldScratch {
   double last_kernel_ms = 0, last_wall_ms = 0;
   int64_t last_n = 0;
   int last_chunks = 0;
+  int gemm_ctas_per_sm = 0;  // occupancy of fold_gemm_async_kernel on this device (development aid)
 };
 void fold_scratch_free(FoldScratch* fs);
 

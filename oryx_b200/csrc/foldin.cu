@@ -306,6 +306,132 @@ __global__ void __launch_bounds__(256, 2) fold_in_kernel(const double* __restric
   }
 }
 
+// The same product when rows are 16-byte aligned (features a multiple of 4: every production size): operand tiles
+// go global -> shared memory with cp.async, three stages deep, so a tile costs its threads eight copy instructions and
+// ONE barrier; b stays binary32 in shared memory (row stride 36 floats = 4 mod 32: a fragment load touches 32
+// distinct banks) and is widened when the fragment is loaded.  Out-of-range rows and columns are zero-filled by the
+// copy itself (src-size 0).
+constexpr int kAsyncStages = 3;
+constexpr int kFoldBLdF = kFoldK + 4;  // floats
+constexpr size_t kAsyncStageBytes = (size_t)kRowsPerCta * kFoldBLdF * sizeof(float) + (size_t)kFoldOut * kFoldLd * sizeof(double);
+constexpr size_t kFoldAsyncSmem = kAsyncStages * kAsyncStageBytes;
+
+__device__ __forceinline__ void cp_async_16_zfill(void* smem_dst, const void* gmem_src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src),
+               "r"(src_bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 2) fold_gemm_async_kernel(const double* __restrict__ inv, int f,
+                                                                 const float* __restrict__ xu,
+                                                                 const uint8_t* __restrict__ has_xu,
+                                                                 const float* __restrict__ bmat, int64_t n,
+                                                                 float* __restrict__ out,
+                                                                 const uint8_t* __restrict__ valid_in) {
+  __shared__ uint8_t s_valid[kRowsPerCta];
+  __shared__ uint8_t s_has[kRowsPerCta];
+  extern __shared__ __align__(16) unsigned char fold_smem[];
+  auto b_tile = [&](int st) { return reinterpret_cast<float (*)[kFoldBLdF]>(fold_smem + kAsyncStageBytes * st); };
+  auto i_tile = [&](int st) {
+    return reinterpret_cast<double (*)[kFoldLd]>(fold_smem + kAsyncStageBytes * st + (size_t)kRowsPerCta * kFoldBLdF * sizeof(float));
+  };
+  const int tid = threadIdx.x;
+  const int64_t k0 = (int64_t)blockIdx.x * kRowsPerCta;
+  if (tid < kRowsPerCta) {
+    const int64_t k = k0 + tid;
+    s_valid[tid] = k < n ? valid_in[k] : 0;
+    s_has[tid] = k < n ? (has_xu ? has_xu[k] : 1) : 0;
+  }
+  const int warp = tid >> 5, lane = tid & 31;
+  const int fr = lane >> 2, fc = lane & 3;
+  const int n_ctiles = (f + kFoldK - 1) / kFoldK, n_rblocks = (f + kFoldOut - 1) / kFoldOut;
+  const int n_tiles = n_ctiles * n_rblocks;
+  // tile t = (output block t / n_ctiles, c block t % n_ctiles)
+  auto issue = [&](int t) {
+    if (t < n_tiles) {
+      const int r0 = (t / n_ctiles) * kFoldOut, c0 = (t % n_ctiles) * kFoldK;
+      float (*Bs)[kFoldBLdF] = b_tile(t % kAsyncStages);
+      double (*Is)[kFoldLd] = i_tile(t % kAsyncStages);
+#pragma unroll
+      for (int u = 0; u < 4; u++) {  // b: 128 rows x 8 chunks of 4 floats
+        const int e = tid + 256 * u, row = e >> 3, ch = e & 7;
+        const int64_t k = k0 + row;
+        const int c = c0 + 4 * ch;
+        const int bytes = (k < n && c < f) ? min(16, (f - c) * 4) : 0;
+        cp_async_16_zfill(&Bs[row][4 * ch], bmat + (bytes ? k * f + c : 0), bytes);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {  // inverse: 64 rows x 16 chunks of 2 doubles
+        const int e = tid + 256 * u, row = e >> 4, ch = e & 15;
+        const int r = r0 + row, c = c0 + 2 * ch;
+        const int bytes = (r < f && c < f) ? min(16, (f - c) * 8) : 0;
+        cp_async_16_zfill(&Is[row][2 * ch], inv + (bytes ? (size_t)r * f + c : 0), bytes);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");  // an empty group past the end keeps the counting uniform
+  };
+  issue(0);
+  issue(1);
+  double acc[2][8][2];
+  for (int t = 0; t < n_tiles; t++) {
+    const int cb = t % n_ctiles;
+    if (cb == 0) {
+#pragma unroll
+      for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+        for (int nt = 0; nt < 8; nt++) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
+    }
+    asm volatile("cp.async.wait_group 1;" ::: "memory");  // tile t has landed (this thread's share)
+    __syncthreads();                                       // ... everybody's; and tile t - 1 has been read by all
+    issue(t + 2);                                          // into the stage tile t - 1 used
+    float (*Bs)[kFoldBLdF] = b_tile(t % kAsyncStages);
+    double (*Is)[kFoldLd] = i_tile(t % kAsyncStages);
+#pragma unroll
+    for (int kc = 0; kc < kFoldK / 4; kc++) {
+      const double a0 = (double)Bs[warp * 16 + fr][4 * kc + fc];
+      const double a1 = (double)Bs[warp * 16 + 8 + fr][4 * kc + fc];
+      double bfrag[8];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++) bfrag[nt] = Is[8 * nt + fr][4 * kc + fc];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++) {
+        dmma_m8n8k4(acc[0][nt], a0, bfrag[nt]);
+        dmma_m8n8k4(acc[1][nt], a1, bfrag[nt]);
+      }
+    }
+    if (cb == n_ctiles - 1) {
+      const int r0 = (t / n_ctiles) * kFoldOut;
+#pragma unroll
+      for (int mt = 0; mt < 2; mt++) {
+        const int kk = warp * 16 + 8 * mt + fr;
+        const int64_t k = k0 + kk;
+        if (k >= n) continue;
+        const bool valid = s_valid[kk] != 0, has = s_has[kk] != 0;
+        float old[8][2];
+#pragma unroll
+        for (int nt = 0; nt < 8; nt++)
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            const int r = r0 + 8 * nt + 2 * fc + j;
+            old[nt][j] = (valid && has && r < f) ? __ldg(xu + k * f + r) : 0.f;
+          }
+#pragma unroll
+        for (int nt = 0; nt < 8; nt++) {
+#pragma unroll
+          for (int j = 0; j < 2; j++) {
+            const int r = r0 + 8 * nt + 2 * fc + j;
+            if (r >= f) continue;
+            const float dxu = (float)acc[mt][nt][j];  // Solver.java:40-42
+            float res = 0.0f;
+            if (valid) res = has ? __fadd_rn(old[nt][j], dxu) : dxu;  // ALSUtils.java:98-104
+            out[k * f + r] = res;
+          }
+        }
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 constexpr size_t kFoldSmem = sizeof(double) * kFoldLd * (kRowsPerCta + kFoldOut);
 // Interactions per pipeline stage: whole waves of the kernel (2 CTAs of 128 interactions per SM), four of them --
 // a power-of-two chunk left the last wave of every launch 46 % full on 148 SMs.
@@ -403,6 +529,24 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
   FoldScratch* fs = solver_fold_scratch(s);
   cudaStream_t st = solver_stream(s);
   ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(fold_in_kernel), kFoldSmem));
+  ORYX_TRY(ensure_max_dynamic_smem(reinterpret_cast<const void*>(fold_gemm_async_kernel), kFoldAsyncSmem));
+  {
+    // two CTAs of 108 KB each per SM need the largest shared-memory carve-out; ask for it once per device
+    static std::once_flag once[64];
+    const int dev = solver_device(s);
+    if (dev >= 0 && dev < 64) {
+      std::call_once(once[dev], [fs] {
+        cudaFuncSetAttribute(reinterpret_cast<const void*>(fold_gemm_async_kernel),
+                             cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fold_gemm_async_kernel, 256, kFoldAsyncSmem) == cudaSuccess)
+          fs->gemm_ctas_per_sm = per_sm;
+        cudaGetLastError();
+      });
+    }
+  }
+  // rows of b, of the inverse and of the outputs are 16-byte aligned when the row length is a multiple of 4
+  const bool async_gemm = (f & 3) == 0 && std::getenv("ORYX_FOLD_NO_ASYNC") == nullptr;
   const auto wall0 = std::chrono::steady_clock::now();
   double kernel_ms = 0;
   int chunks = 0;
@@ -461,8 +605,13 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     fold_prep_kernel<<<(unsigned)((c * 32 + 255) / 256), 256, 0, st>>>(f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
                                                                       use_has_yi ? b.d_has_yi : nullptr, b.d_val, c,
                                                                       b.d_valid[par]);
-    fold_in_kernel<<<grid, 256, kFoldSmem, st>>>(solver_inverse(s), f, b.d_xu, b.d_has_xu, b.d_yi, c, b.d_out[par],
-                                                 b.d_valid[par]);
+    if (async_gemm) {
+      fold_gemm_async_kernel<<<grid, 256, kFoldAsyncSmem, st>>>(solver_inverse(s), f, b.d_xu, b.d_has_xu, b.d_yi, c,
+                                                               b.d_out[par], b.d_valid[par]);
+    } else {
+      fold_in_kernel<<<grid, 256, kFoldSmem, st>>>(solver_inverse(s), f, b.d_xu, b.d_has_xu, b.d_yi, c, b.d_out[par],
+                                                   b.d_valid[par]);
+    }
     if ((e = cudaGetLastError()) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_k1[par], st)) != cudaSuccess) break;
     if ((e = cudaEventRecord(fs->ev_done[par], st)) != cudaSuccess) break;
@@ -926,6 +1075,7 @@ int32_t oryx_debug_fold_in_timings(oryx_solver* sh, double* out4) {
   out4[1] = fs->last_chunks;
   out4[2] = (double)fs->last_n;
   out4[3] = fs->last_wall_ms;
+  out4[4] = (double)fs->gemm_ctas_per_sm;
   return ORYX_OK;
 }
 

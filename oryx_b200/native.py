@@ -597,9 +597,10 @@ class Solver:
 
     def debug_fold_in_timings(self) -> dict:
         """Of this solver's last fold-in call: device ms of fold_in_kernel (all chunks), chunks, n, wall ms."""
-        t = np.zeros(4, dtype=np.float64)
+        t = np.zeros(5, dtype=np.float64)
         _check(lib().oryx_debug_fold_in_timings(self._h, _ptr(t, C.c_double)))
-        return {"kernel_ms": float(t[0]), "chunks": int(t[1]), "n": int(t[2]), "wall_ms": float(t[3])}
+        return {"kernel_ms": float(t[0]), "chunks": int(t[1]), "n": int(t[2]), "wall_ms": float(t[3]),
+                "gemm_ctas_per_sm": int(t[4])}
 
     def fold_in_rows_sharded(self, models, xu_row_stride: int, yi_row_stride: int, implicit: bool, xu_which: int,
                              xu_rows, yi_rows, values):
