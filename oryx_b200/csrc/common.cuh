@@ -143,6 +143,71 @@ __device__ __forceinline__ bool warp_exact_dot(const float* __restrict__ a, cons
   *out = (double)total * __longlong_as_double((long long)(1023 + emin - 150) << 52);
   return true;
 }
+
+// The same test and result for terms the lanes already hold in registers: lane l owns the cnt <= 8 consecutive terms
+// t[0..cnt) of a chain of n <= 256 terms (lane l's terms come before lane l + 1's).  Used where the row is loaded once
+// and needed again (fold_prep_kernel).
+__device__ __forceinline__ bool warp_exact_sum_regs(const float (&t)[8], int cnt, int n, int lane, double* out) {
+  int emin = 1 << 20, emax = 0;
+  bool bad = false;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    if (i < cnt) {
+      const uint32_t bits = __float_as_uint(t[i]);
+      const int ex = (int)((bits >> 23) & 255u);
+      if (ex == 255) bad = true;
+      if ((bits & 0x7fffffffu) != 0u) {
+        const int e = ex == 0 ? 1 : ex;
+        emin = min(emin, e);
+        emax = max(emax, e);
+      }
+    }
+  }
+  emin = __reduce_min_sync(0xffffffffu, emin);
+  emax = __reduce_max_sync(0xffffffffu, emax);
+  if (__any_sync(0xffffffffu, bad)) return false;
+  if (emax == 0) {
+    *out = 0.0;
+    return true;
+  }
+  if (emax - emin > 62 - 24 - (32 - __clz(n))) return false;
+  long long v[8];
+  long long run = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    v[i] = 0;
+    if (i < cnt) {
+      const uint32_t bits = __float_as_uint(t[i]);
+      if ((bits & 0x7fffffffu) != 0u) {
+        const int ex = (int)((bits >> 23) & 255u);
+        const long long m = (long long)((bits & 0x7fffffu) | (ex == 0 ? 0u : 0x800000u));
+        const long long x = m << ((ex == 0 ? 1 : ex) - emin);
+        v[i] = (bits & 0x80000000u) ? -x : x;
+      }
+    }
+    run += v[i];
+  }
+  long long incl = run;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const long long up = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += up;
+  }
+  long long p = incl - run;
+  bool ok = true;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    if (i < cnt) {
+      p += v[i];
+      const unsigned long long m = (unsigned long long)(p < 0 ? -p : p);
+      ok = ok && (p == 0 || (64 - __clzll((long long)m)) - (__ffsll((long long)m) - 1) <= 53);
+    }
+  }
+  if (!__all_sync(0xffffffffu, ok)) return false;
+  const long long total = __shfl_sync(0xffffffffu, incl, 31);
+  *out = (double)total * __longlong_as_double((long long)(1023 + emin - 150) << 52);
+  return true;
+}
 #endif
 
 // ---- the device-resident feature-vector store (one per X / Y).

@@ -147,9 +147,38 @@ __global__ void __launch_bounds__(256) fold_prep_kernel(int f, int implicit, con
   if (k >= n) return;
   const uint8_t has = has_xu ? has_xu[k] : 1;
   float* y = yi_to_b + k * f;
+  const float* x = xu + k * f;
+  if (f <= 256) {
+    // rows of up to 256 features live in registers: lane l holds the c = ceil(f / 32) consecutive elements from l c on,
+    // loaded once for the dot product and for b
+    const int c = (f + 31) >> 5, j0 = lane * c;
+    const int cnt = max(0, min(c, f - j0));
+    float yr[8], t[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      yr[i] = i < cnt ? y[j0 + i] : 0.f;
+      t[i] = (has && i < cnt) ? __fmul_rn(x[j0 + i], yr[i]) : 0.f;
+    }
+    double qui = 0.0;
+    if (has && !warp_exact_sum_regs(t, cnt, f, lane, &qui)) {
+      if (lane == 0) {
+        qui = 0.0;
+        for (int j = 0; j < f; j++) qui = exact_step(qui, x[j], y[j]);
+      }
+      qui = __shfl_sync(0xffffffffu, qui, 0);
+    }
+    const double target = target_qui(implicit != 0, values[k], has ? qui : 0.5);
+    // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81) or the target is NaN (:90-92)
+    const bool valid = target == target && (has_yi == nullptr || has_yi[k]);
+    const double dq = valid ? target - qui : 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (i < cnt) y[j0 + i] = (float)((double)yr[i] * dq);
+    if (lane == 0) out_valid[k] = valid ? 1 : 0;
+    return;
+  }
   double qui = 0.0;
   if (has) {
-    const float* x = xu + k * f;
     if (!warp_exact_dot(x, y, f, lane, &qui)) {
       if (lane == 0) {
         qui = 0.0;
