@@ -457,6 +457,55 @@ constexpr int kTopPerThread = 4;     // 256 x 4 = 1024 >= largest k
 constexpr int kCollectCap = 4096;    // sub-blocks above the first cut, staged in shared memory
 constexpr int kTileCap = 2048;       // tiles above the first cut
 
+// k-th largest of n floats in shared memory (n >= k >= 1), by the whole CTA: radix select over order-preserving
+// 32-bit keys, four passes of eight bits, one 256-bin histogram per pass.  Returns the value to every thread.
+// (The threshold step used a 55-step bitonic sort for the first cut and an n x n rank count for the second.)
+__device__ float cta_kth_largest_float(const float* vals, int n, int k, unsigned int* hist /*[256]*/) {
+  const int tid = threadIdx.x, T = blockDim.x;
+  __shared__ unsigned int s_prefix, s_mask, s_remaining;
+  __syncthreads();  // callers' writes to vals[] and earlier users of hist[] / the selection state
+  if (tid == 0) { s_prefix = 0u; s_mask = 0u; s_remaining = (unsigned)k; }
+  for (int pass = 0; pass < 4; pass++) {
+    const int shift = 24 - 8 * pass;
+    for (int b = tid; b < 256; b += T) hist[b] = 0u;
+    __syncthreads();
+    const unsigned prefix = s_prefix, mask = s_mask;
+    for (int i = tid; i < n; i += T) {
+      const unsigned key = float_key(vals[i]);
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {
+      unsigned local[8];
+      unsigned sum = 0;
+#pragma unroll
+      for (int q = 0; q < 8; q++) { local[q] = hist[255 - 8 * tid - q]; sum += local[q]; }
+      unsigned incl = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (tid >= d) incl += t;
+      }
+      const unsigned excl_sum = incl - sum;
+      const unsigned remaining = s_remaining;
+      if (excl_sum < remaining && incl >= remaining) {  // exactly one lane owns the crossing
+        unsigned cum = excl_sum;
+        int digit = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          if (cum + local[q] >= remaining) { digit = 255 - 8 * tid - q; break; }
+          cum += local[q];
+        }
+        s_prefix = prefix | ((unsigned)digit << shift);
+        s_mask = mask | (255u << shift);
+        s_remaining = remaining - cum;
+      }
+    }
+    __syncthreads();
+  }
+  return key_float(s_prefix);
+}
+
 // One CTA per query.  cand[q][0..cand_cap) receives candidate sub-block ids, cand_n[q] their number
 // (or -1 when too many qualified: the host re-runs that query unbatched).
 //
@@ -478,7 +527,7 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, cons
   __shared__ int32_t s_id[kCollectCap];
   __shared__ int32_t s_tile[kTileCap];
   __shared__ unsigned int s_count, s_out, s_ntile;
-  __shared__ float s_lb, s_t;
+  __shared__ unsigned int s_hist[256];
   const int q = blockIdx.x, tid = threadIdx.x;
   // The maxima include rows the query excludes (exclusions are applied row by row in the refine step),
   // so the rank that guarantees k ALLOWED rows at or above the cut is k + the number of excluded rows:
@@ -535,29 +584,11 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, cons
   }
 #pragma unroll
   for (int j = 0; j < kTopPerThread; j++) s_top[tid * kTopPerThread + j] = top[j];
-  if (tid == 0) { s_count = 0u; s_out = 0u; s_ntile = 0u; s_lb = -INFINITY; }
+  if (tid == 0) { s_count = 0u; s_out = 0u; s_ntile = 0u; }
   __syncthreads();
-  // lower bound of Tc: the k-th largest of these 1024 values -- bitonic sort, descending (a rank
-  // count over 1024 x 1024 pairs per query cost more than everything else in this kernel)
-  {
-    constexpr int m = kThrThreads * kTopPerThread;
-    for (int kk2 = 2; kk2 <= m; kk2 <<= 1) {
-      for (int j = kk2 >> 1; j > 0; j >>= 1) {
-        for (int i = tid; i < m; i += kThrThreads) {
-          const int ixj = i ^ j;
-          if (ixj > i) {
-            const float a = s_top[i], b = s_top[ixj];
-            const bool desc = (i & kk2) == 0;
-            if ((a < b) == desc) { s_top[i] = b; s_top[ixj] = a; }
-          }
-        }
-        __syncthreads();
-      }
-    }
-    if (tid == 0) s_lb = s_top[min(k, m) - 1];
-  }
-  __syncthreads();
-  const float lb = s_lb;  // -inf when fewer than k finite tile maxima exist: then everything is collected
+  // lower bound of Tc: the k-th largest of these 1024 values (radix select)
+  const float lb = cta_kth_largest_float(s_top, kThrThreads * kTopPerThread, min(k, kThrThreads * kTopPerThread), s_hist);
+  // (-inf when fewer than k finite tile maxima exist: then everything is collected)
   const float cut1 = lb - 2.0f * delta;
 
   // pass B (tiles): the tiles at or above the first cut ...
@@ -605,22 +636,8 @@ batch_threshold_kernel(const float* __restrict__ bmax, int64_t bmax_stride, cons
     return;
   }
   // exact k-th largest sub-block maximum T' among the collected ones (they include everything >= lb)
-  {
-    const int kk = min(k, n);
-    if (tid == 0) s_t = -INFINITY;
-    __syncthreads();
-    for (int e = tid; e < n; e += kThrThreads) {
-      const float v = s_val[e];
-      int rank = 0;
-      for (int j = 0; j < n; j++) {
-        const float u = s_val[j];
-        rank += (u > v || (u == v && j < e)) ? 1 : 0;
-      }
-      if (rank == kk - 1) s_t = v;
-    }
-    __syncthreads();
-  }
-  const float cut2 = (n >= k) ? s_t - 2.0f * delta : -INFINITY;
+  const float t_prime = n >= k ? cta_kth_largest_float(s_val, n, k, s_hist) : -INFINITY;  // n, k are CTA-uniform
+  const float cut2 = (n >= k) ? t_prime - 2.0f * delta : -INFINITY;
   int32_t* out = cand + (int64_t)q * cand_cap;
   for (int e = tid; e < n; e += kThrThreads) {
     if (s_val[e] >= cut2) {
