@@ -214,6 +214,23 @@ __global__ void __launch_bounds__(T, 1) gram_fast_kernel(const float* __restrict
 
 }  // namespace
 
+// Both kernels above add every row chunk's partial into G with binary64 atomics, entry (r, c) and its mirror (c, r)
+// separately: the two receive the same partials but not necessarily in the same order, so they could differ in the
+// last bit (seen once in ~20 runs of the test suite).  G is symmetric by definition: the lower triangle is copied
+// from the upper one once the sums are complete.
+__global__ void gram_symmetrise_kernel(double* __restrict__ g, int features) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= features * features) return;
+  const int r = e / features, c = e - r * features;
+  if (r > c) g[e] = g[(size_t)c * features + r];
+}
+
+int32_t gram_symmetrise(double* d_out, int F, cudaStream_t stream) {
+  gram_symmetrise_kernel<<<(unsigned)((F * F + 255) / 256), 256, 0, stream>>>(d_out, F);
+  ORYX_CUDA(cudaGetLastError());
+  return ORYX_OK;
+}
+
 constexpr int64_t kGramFastMinRows = 1 << 16;
 
 int32_t gram_fast_launch(Model* m, Store* s, double* d_out, cudaStream_t stream) {
@@ -257,7 +274,10 @@ int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream, boo
       return gram_tc_launch(m, s, d_out, stream);
     }
   }
-  if (s->n_slots >= kGramFastMinRows) return gram_fast_launch(m, s, d_out, stream);
+  if (s->n_slots >= kGramFastMinRows) {
+    ORYX_TRY(gram_fast_launch(m, s, d_out, stream));
+    return gram_symmetrise(d_out, F, stream);
+  }
   const int nb = (F + kTile - 1) / kTile;
   const int n_blocks = nb * (nb + 1) / 2;
   // enough row chunks to fill the GPU a few times over, but chunks no shorter than 256 rows
@@ -271,7 +291,7 @@ int32_t gram_launch(Model* m, int which, double* d_out, cudaStream_t stream, boo
   gram_exact_kernel<<<grid, 256, 0, stream>>>(s->d_vec, s->d_slot_row, s->n_slots, s->fpad, F, nb, rows_per_chunk, d_out);
   m->launches++;
   ORYX_CUDA(cudaGetLastError());
-  return ORYX_OK;
+  return gram_symmetrise(d_out, F, stream);
 }
 
 }  // namespace oryx
