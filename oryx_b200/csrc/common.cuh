@@ -208,6 +208,74 @@ __device__ __forceinline__ bool warp_exact_sum_regs(const float (&t)[8], int cnt
   *out = (double)total * __longlong_as_double((long long)(1023 + emin - 150) << 52);
   return true;
 }
+
+// The same for a chain of n <= 64 terms held by a GROUP of eight lanes (lane g of the group owns the cnt <= 8
+// consecutive terms from 8-lane-aligned position g * ceil(n / 8) on): four short chains per warp, so that short rows do
+// not leave three quarters of a warp idle.  All 32 lanes must call it; results are per group.
+__device__ __forceinline__ bool group8_exact_sum_regs(const float (&t)[8], int cnt, int n, int lane, double* out) {
+  const int g = lane & 7;
+  const unsigned gmask = 0xffu << (lane & 24);
+  int emin = 1 << 20, emax = 0;
+  bool bad = false;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    if (i < cnt) {
+      const uint32_t bits = __float_as_uint(t[i]);
+      const int ex = (int)((bits >> 23) & 255u);
+      if (ex == 255) bad = true;
+      if ((bits & 0x7fffffffu) != 0u) {
+        const int e = ex == 0 ? 1 : ex;
+        emin = min(emin, e);
+        emax = max(emax, e);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    emin = min(emin, __shfl_xor_sync(0xffffffffu, emin, o));
+    emax = max(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+  }
+  const bool any_bad = (__ballot_sync(0xffffffffu, bad) & gmask) != 0u;
+  const bool all_zero = emax == 0;
+  const bool too_wide = !all_zero && emax - emin > 62 - 24 - (32 - __clz(n));
+  long long v[8];
+  long long run = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    v[i] = 0;
+    if (i < cnt && !all_zero && !too_wide) {
+      const uint32_t bits = __float_as_uint(t[i]);
+      if ((bits & 0x7fffffffu) != 0u) {
+        const int ex = (int)((bits >> 23) & 255u);
+        const long long m = (long long)((bits & 0x7fffffu) | (ex == 0 ? 0u : 0x800000u));
+        const long long x = m << ((ex == 0 ? 1 : ex) - emin);
+        v[i] = (bits & 0x80000000u) ? -x : x;
+      }
+    }
+    run += v[i];
+  }
+  long long incl = run;
+#pragma unroll
+  for (int d = 1; d < 8; d <<= 1) {
+    const long long up = __shfl_up_sync(0xffffffffu, incl, d, 8);
+    if (g >= d) incl += up;
+  }
+  long long p = incl - run;
+  bool ok = true;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    if (i < cnt) {
+      p += v[i];
+      const unsigned long long m = (unsigned long long)(p < 0 ? -p : p);
+      ok = ok && (p == 0 || (64 - __clzll((long long)m)) - (__ffsll((long long)m) - 1) <= 53);
+    }
+  }
+  const bool all_ok = (__ballot_sync(0xffffffffu, ok) & gmask) == gmask;
+  const long long total = __shfl_sync(0xffffffffu, incl, 7, 8);
+  if (any_bad || too_wide || !all_ok) return false;
+  *out = all_zero ? 0.0 : (double)total * __longlong_as_double((long long)(1023 + emin - 150) << 52);
+  return true;
+}
 #endif
 
 // ---- the device-resident feature-vector store (one per X / Y).

@@ -142,8 +142,48 @@ __global__ void __launch_bounds__(256) fold_prep_kernel(int f, int implicit, con
                                                         const uint8_t* __restrict__ has_yi,
                                                         const double* __restrict__ values, int64_t n,
                                                         uint8_t* __restrict__ out_valid) {
-  const int64_t k = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  if (f <= 64) {
+    // short rows: four interactions per warp, eight lanes each (lane g of a group holds the c = ceil(f / 8)
+    // consecutive elements from g c on).  Every lane stays in the warp-wide shuffles; lanes past the end idle.
+    const int64_t kq = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 4 + (lane >> 3);
+    const bool live = kq < n;
+    const int g = lane & 7, c = (f + 7) >> 3, j0 = g * c;
+    const int cnt = live ? max(0, min(c, f - j0)) : 0;
+    const uint8_t has = live ? (has_xu ? has_xu[kq] : 1) : 0;
+    float* y = yi_to_b + (live ? kq : 0) * f;
+    const float* x = xu + (live ? kq : 0) * f;
+    float yr[8], t[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      yr[i] = i < cnt ? y[j0 + i] : 0.f;
+      t[i] = (has && i < cnt) ? __fmul_rn(x[j0 + i], yr[i]) : 0.f;
+    }
+    double qui = 0.0;
+    const bool fast = group8_exact_sum_regs(t, cnt, f, lane, &qui);
+    if (has && !fast) {  // the group's first lane walks the chain (lanes of one group agree on `fast`)
+      if (g == 0) {
+        qui = 0.0;
+        for (int j = 0; j < f; j++) qui = exact_step(qui, x[j], y[j]);
+      }
+    }
+    {
+      const double q0 = __shfl_sync(0xffffffffu, qui, 0, 8);  // all lanes execute the shuffle
+      if (has && !fast) qui = q0;
+    }
+    if (!has) qui = 0.0;
+    if (!live) return;
+    const double target = target_qui(implicit != 0, values[kq], has ? qui : 0.5);
+    // computeUpdatedXu returns null when Yi is null (ALSUtils.java:79-81) or the target is NaN (:90-92)
+    const bool valid = target == target && (has_yi == nullptr || has_yi[kq]);
+    const double dq = valid ? target - qui : 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (i < cnt) y[j0 + i] = (float)((double)yr[i] * dq);
+    if (g == 0) out_valid[kq] = valid ? 1 : 0;
+    return;
+  }
+  const int64_t k = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (k >= n) return;
   const uint8_t has = has_xu ? has_xu[k] : 1;
   float* y = yi_to_b + k * f;
@@ -631,7 +671,8 @@ int32_t fold_pipeline(Solver* s, const FoldBuffers& b, int f, int implicit, int6
     if (e != cudaSuccess) break;
     const unsigned grid = (unsigned)((c + kRowsPerCta - 1) / kRowsPerCta);
     if ((e = cudaEventRecord(fs->ev_k0[par], st)) != cudaSuccess) break;
-    fold_prep_kernel<<<(unsigned)((c * 32 + 255) / 256), 256, 0, st>>>(f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
+    // one warp per interaction, or per four interactions when rows are short (f <= 64)
+    fold_prep_kernel<<<(unsigned)(((f <= 64 ? (c + 3) / 4 : c) * 32 + 255) / 256), 256, 0, st>>>(f, implicit, b.d_xu, b.d_has_xu, b.d_yi,
                                                                       use_has_yi ? b.d_has_yi : nullptr, b.d_val, c,
                                                                       b.d_valid[par]);
     if (async_gemm) {
